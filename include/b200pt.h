@@ -1,0 +1,136 @@
+/*
+ * b200pt.h — C ABI of the B200 path-tracing backend (libb200pt.so).
+ *
+ * Drop-in for the compute pass of CobaltCrabby/ray_tracer: everything the reference binds and
+ * dispatches for shaders/raytrace.comp has one entry point here. Buffers are taken in the
+ * reference's own layouts, byte for byte; re-layout for the GPU is internal.
+ *
+ *   reference interface (file:line)                               entry point
+ *   -----------------------------------------------------------   --------------------------------
+ *   init_image: W x H storage image            vk_engine.cpp:1375-1399   b200pt_create / b200pt_resize
+ *   prepare_storage_buffers + copy_buffer x6   vk_engine.cpp:680-758,1401-1444   b200pt_upload_scene
+ *   update_buffer(materials)  (UI button)      vk_engine.cpp:1545,1446-1475      b200pt_update_materials
+ *   update_buffer(spheres)                     vk_engine.cpp:1572                b200pt_update_spheres
+ *   update_buffer(objects)                     vk_engine.cpp:1594-1603           b200pt_update_objects
+ *   load_images_from_file -> TextureBuffer[64] vk_engine.cpp:1155, vk_textures.cpp:103-200  b200pt_upload_texture
+ *   run_compute: push constants + vkCmdDispatch  vk_engine.cpp:1623-1676         b200pt_render
+ *   draw(): progressive frame loop             vk_engine.cpp:1774-1815           b200pt_render_frames
+ *   run_graphics: sampling the compute image   vk_engine.cpp:1678-1737           b200pt_read_* / b200pt_device_*_ptr
+ *   VK_CHECK (print + abort)                   vk_engine.cpp:20-27               int status + b200pt_last_error
+ *
+ * Conventions: every call returns 0 on success, non-zero on failure (never aborts); the text of
+ * the last failure is b200pt_last_error(ctx). Host input buffers are copied during the call and
+ * may be freed afterwards. One context per GPU; calls on one context must be serialised by the
+ * caller (the reference is single-threaded with one queue). Work is asynchronous on the
+ * context's CUDA stream; b200pt_sync or any b200pt_read_* waits for it.
+ * There is no CPU fallback: without a CUDA device b200pt_create fails.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200pt_ctx b200pt_ctx;
+
+/* sizes of the reference's buffer elements (std140; src/vk_engine.h:49-189) */
+#define B200PT_SPHERE_BYTES 32
+#define B200PT_MATERIAL_BYTES 64
+#define B200PT_TRIPOINT_BYTES 32
+#define B200PT_TRIANGLE_BYTES 48
+#define B200PT_OBJECT_BYTES 80
+#define B200PT_BVHNODE_BYTES 32
+#define B200PT_PUSHCONSTANT_BYTES 208
+#define B200PT_MAX_TEXTURES 64 /* src/vk_engine.h:204 */
+
+/* status codes */
+#define B200PT_OK 0
+#define B200PT_ERR_ARG 1
+#define B200PT_ERR_CUDA 2
+#define B200PT_ERR_STATE 3
+
+int b200pt_version(void);
+/* non-context failures (e.g. b200pt_create) */
+const char* b200pt_global_error(void);
+
+/* Context = device buffers + W x H outputs on CUDA device `device`. */
+int b200pt_create(int device, int width, int height, b200pt_ctx** out);
+int b200pt_destroy(b200pt_ctx* ctx);
+int b200pt_resize(b200pt_ctx* ctx, int width, int height);
+const char* b200pt_last_error(b200pt_ctx* ctx);
+
+/* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the context's own stream). */
+int b200pt_set_stream(b200pt_ctx* ctx, void* cuda_stream);
+int b200pt_sync(b200pt_ctx* ctx);
+
+/* The six storage buffers, reference layout, element counts (not bytes). */
+int b200pt_upload_scene(b200pt_ctx* ctx, const void* spheres, uint32_t n_spheres, const void* materials,
+                        uint32_t n_materials, const void* tri_points, uint32_t n_points, const void* triangles,
+                        uint32_t n_triangles, const void* objects, uint32_t n_objects, const void* bvh_nodes,
+                        uint32_t n_nodes);
+/* In-place updates, same element counts as uploaded (the reference's update_buffer never resizes). */
+int b200pt_update_materials(b200pt_ctx* ctx, const void* materials, uint32_t n);
+int b200pt_update_spheres(b200pt_ctx* ctx, const void* spheres, uint32_t n);
+int b200pt_update_objects(b200pt_ctx* ctx, const void* objects, uint32_t n);
+/* RGBA8 (sRGB-encoded) texels for TextureBuffer[slot]; stored for the texture extension (the HEAD
+ * shader never samples: SURVEY.md §0). */
+int b200pt_upload_texture(b200pt_ctx* ctx, uint32_t slot, const void* rgba8, uint32_t width, uint32_t height);
+
+/* One reference dispatch: main() of raytrace.comp for every pixel with the 208-byte push-constant
+ * block; read-modify-writes the float storage image (the reference's image is rgba8; see
+ * b200pt_read_rgba8). Honours progressive, singleRender, raysPerPixel, sampleLimit, bounceLimit,
+ * debug, frameCount. */
+int b200pt_render(b200pt_ctx* ctx, const void* push_constants_208);
+
+/* Throughput entry: progressive frames first_frame .. first_frame+n_frames-1 (frameCount = f,
+ * raysPerPixel samples each); accum.rgb += outColor_f (non-finite -> magenta, raytrace.comp:579-581),
+ * accum.a += 1. Frames are summed in frame order, so the result does not depend on how many frames
+ * are in flight. frame_stride > 1 renders first_frame, first_frame+stride, ... (multi-GPU sample split). */
+int b200pt_render_frames(b200pt_ctx* ctx, const void* push_constants_208, uint32_t first_frame, uint32_t n_frames,
+                         uint32_t frame_stride);
+/* Row band [row_begin, row_end) only (interactive multi-GPU tile split); other rows untouched. */
+int b200pt_render_frames_rows(b200pt_ctx* ctx, const void* push_constants_208, uint32_t first_frame,
+                              uint32_t n_frames, uint32_t frame_stride, uint32_t row_begin, uint32_t row_end);
+int b200pt_clear(b200pt_ctx* ctx); /* zero accumulator, storage image and counters */
+
+/* Outputs. Accumulator and image are W*H float4, row 0 first (row 0 is the top of the screen). */
+int b200pt_read_accum_f32(b200pt_ctx* ctx, float* host_rgba);
+int b200pt_read_image_f32(b200pt_ctx* ctx, float* host_rgba);
+int b200pt_write_image_f32(b200pt_ctx* ctx, const float* host_rgba);
+int b200pt_read_rgba8(b200pt_ctx* ctx, uint8_t* host_rgba8); /* unorm8 round-to-nearest of the image */
+/* Per-pixel stats[0], stats[1] of the last b200pt_render (box tests, triangle tests; raytrace.comp:310,338). */
+int b200pt_read_stats(b200pt_ctx* ctx, float* host_w_h_2);
+/* Headless device buffers (where Vulkan external-memory interop would attach). */
+int b200pt_device_accum_ptr(b200pt_ctx* ctx, void** device_ptr);
+int b200pt_device_image_ptr(b200pt_ctx* ctx, void** device_ptr);
+/* Accumulate into a caller-owned device buffer of W*H float4 (e.g. a torch tensor handed to NCCL);
+ * NULL returns to the context's own buffer. */
+int b200pt_attach_accum(b200pt_ctx* ctx, void* device_ptr);
+
+/* Closest hits of caller-supplied rays (8 floats each: origin.xyz, pad, dir.xyz, pad) through
+ * calculateIntersections (raytrace.comp:276-353); 48-byte records:
+ * {f32 dst; u32 kind (0 miss,1 sphere,2 triangle); u32 objectHitIndex; u32 triHitIndex;
+ *  u32 materialIndex; u32 frontFace; f32 normal[3]; f32 hitPoint[3]}. */
+int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const float* host_rays, uint64_t n,
+                       void* host_hits48);
+
+/* Options: "pipeline" 0 = reference-layout per-pixel kernel, 1 = wavefront (default for
+ * render_frames/trace_batch); "frames_in_flight" (1..64). Unknown keys fail. */
+int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
+int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
+
+/* Counters since the last b200pt_clear / b200pt_reset_counters, 16 x u64:
+ * [0] kernel launches, [1] paths traced, [2] extension rays, [3] shadow/pdf rays, [4] reserved ... */
+int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
+int b200pt_reset_counters(b200pt_ctx* ctx);
+/* Device time of the last render call in milliseconds (CUDA events on the context's stream). */
+int b200pt_last_render_ms(b200pt_ctx* ctx, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PT_H */

@@ -74,6 +74,8 @@ int orc_trace_batch(void* scene, const void* pc208, const float* rays, uint64_t 
     return 0;
 }
 
+void orc_set_math_mode(int mode) { orc::set_math_mode(mode); }
+int orc_math_mode() { return orc::math_mode(); }
 float orc_random(uint32_t* state) { return orc::random(*state); }
 uint32_t orc_starting_seed(uint32_t f) { return starting_seed(f); }
 

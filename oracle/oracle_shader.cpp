@@ -4,6 +4,12 @@
 // Compile with -O2 -ffp-contract=off (no FMA contraction, no fast-math).
 #include "oracle_shader.h"
 
+// Optional "portable" transcendental mode (orc::set_math_mode(1)): sin/cos/pow/tan come from the
+// backend's own double-precision polynomials instead of libm, so that a bit-for-bit image
+// comparison isolates everything else (traversal, RNG stream, BSDF operation order). The default
+// (mode 0) is libm, and the tolerance tests use that. The header is plain C++, no CUDA.
+#include "../ray_tracer_b200/csrc/pt_portable_math.h"
+
 #include <cmath>
 #include <cstring>
 #ifdef _OPENMP
@@ -13,7 +19,16 @@
 namespace orc {
 using namespace om;
 
+static int g_math_mode = 0;
+void set_math_mode(int mode) { g_math_mode = mode; }
+int math_mode() { return g_math_mode; }
+
 namespace {
+
+inline float o_pow(float x, float y) { return g_math_mode ? pt::pt_powf(x, y) : std::pow(x, y); }
+inline float o_sin(float x) { return g_math_mode ? pt::pt_sinf(x) : std::sin(x); }
+inline float o_cos(float x) { return g_math_mode ? pt::pt_cosf(x) : std::cos(x); }
+inline float o_tan(float x) { return g_math_mode ? pt::pt_tanf(x) : std::tan(x); }
 
 const float PI = 3.1415926535897932384f;   // raytrace.comp:6
 const float INV_PI = 0.3183098862f;        // raytrace.comp:7
@@ -69,7 +84,7 @@ namespace {
 float schlick(float cosine, float refraction_index) {
     float r0 = (1.f - refraction_index) / (1.f + refraction_index);
     r0 = r0 * r0;
-    return r0 + (1.f - r0) * std::pow((1.f - cosine), 5.f);
+    return r0 + (1.f - r0) * o_pow((1.f - cosine), 5.f);
 }
 
 // raytrace.comp:195-224
@@ -243,9 +258,9 @@ vec3 getEnvironmentLight(Ctx& cx, const Ray& ray) {
     const ol::EnvironmentData& env = cx.pc.environment;
     vec3 horizon = v3(env.horizonColor), zenith = v3(env.zenithColor), ground = v3(env.groundColor);
     vec3 lightDir = v3(env.lightDir);
-    float skyGradientT = std::pow(smoothstep(0.f, 0.4f, -ray.dir.y), 0.35f);
+    float skyGradientT = o_pow(smoothstep(0.f, 0.4f, -ray.dir.y), 0.35f);
     vec3 skyGradient = mix(horizon, zenith, skyGradientT);
-    float sun = std::pow(gmax(0.f, dot(ray.dir, -lightDir)), env.horizonColor[3]) * env.zenithColor[3];
+    float sun = o_pow(gmax(0.f, dot(ray.dir, -lightDir)), env.horizonColor[3]) * env.zenithColor[3];
 
     float groundToSkyT = smoothstep(-0.01f, 0.f, -ray.dir.y);
     float sunMask = float(groundToSkyT >= 1.f);
@@ -290,8 +305,8 @@ vec3 cosineHemisphereDir(const vec3& rayNormal, uint32_t& state) {
 
     float phi = 2.f * PI * r1;
     float sqrtR2 = std::sqrt(r2);
-    float x = std::cos(phi) * sqrtR2;
-    float y = std::sin(phi) * sqrtR2;
+    float x = o_cos(phi) * sqrtR2;
+    float y = o_sin(phi) * sqrtR2;
     float z = std::sqrt(1.f - r2);
 
     vec3 zAlignedDir = vec3(x, y, z);
@@ -439,7 +454,7 @@ PixelOut shade_pixel(Ctx& cx, uint32_t gx, uint32_t gy, int W, int H) {
     float uvy = float(gy) / float(H);
 
     const ol::CameraInfo& cam = pc.camInfo;
-    float planeHeight = cam.nearPlane * std::tan(radians(cam.fov * 0.5f)) * 2.f;
+    float planeHeight = cam.nearPlane * o_tan(radians(cam.fov * 0.5f)) * 2.f;
     float planeWidth = planeHeight * cam.aspectRatio;
 
     vec3 bottomLeft = vec3(-planeWidth / 2.f, -planeHeight / 2.f, 0.1f);

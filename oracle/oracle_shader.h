@@ -73,6 +73,10 @@ void render_frames(const Scene& sc, const ol::PushConstants& pc, int W, int H, u
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out,
                  Work* work, int threads);
 
+// 0 = libm transcendentals (default), 1 = the backend's portable double-precision polynomials
+void set_math_mode(int mode);
+int math_mode();
+
 // exposed for known-answer tests
 float random(uint32_t& state);
 uint32_t starting_seed(uint32_t frameCount);

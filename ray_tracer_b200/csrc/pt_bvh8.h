@@ -1,0 +1,70 @@
+// Internal acceleration layout: an 8-wide BVH over WORLD-space boxes of every (object instance,
+// triangle) pair, with child boxes quantised to 8 bits per plane relative to the node
+// (compressed-wide-BVH encoding after Ylitie, Karras, Laine 2017): 80-byte nodes read as five
+// 16-byte vectors, 64-byte triangle records read as four. It replaces the reference's
+// "linear loop over objects, one BVH2 per object, 32-byte nodes + 144 bytes of vertices per test"
+// (shaders/raytrace.comp:289-350) — the boxes only decide WHICH triangles are tested; the
+// triangle test itself is the reference's arithmetic in object space (pt_shade.h: tri_test), so
+// accepted hits are bit-identical. Boxes are conservative (padded, rounded outward).
+#pragma once
+#include "pt_shade.h"
+
+namespace pt {
+
+struct Bvh8Node {              // 80 B
+    float px, py, pz;          // quantisation origin (node box minimum)
+    uint8_t ex, ey, ez;        // biased exponents: plane = p + q * 2^(e-127)
+    uint8_t imask;             // bit s set: slot s holds an inner node
+    uint32_t childBase;        // first inner child (children contiguous, ordered by slot)
+    uint32_t primBase;         // first triangle record of this node's leaf children
+    uint8_t meta[8];           // inner: 001|24+slot ; leaf: unary count (1,3,7)<<5 | offset ; empty: 0
+    uint8_t qlox[8], qloy[8], qloz[8];
+    uint8_t qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(Bvh8Node) == 80, "Bvh8Node");
+
+// Triangle record for intersection: edges and face normal are those of triangleIntersection()
+// (raytrace.comp:229-232), evaluated once in object space.
+struct PrimRecord {            // 64 B
+    float p0x, p0y, p0z; uint32_t objectIndex;
+    float e1x, e1y, e1z; uint32_t triIndexFlags;   // bit31 frontOnly, bit30 emissive material, low 30 bits triangle index
+    float e2x, e2y, e2z; uint32_t xformId;
+    float nx, ny, nz;    uint32_t orderKey;        // sphereCount + objectIndex: tie order of the reference's loops
+};
+static_assert(sizeof(PrimRecord) == 64, "PrimRecord");
+#define PT_PRIM_FRONTONLY 0x80000000u
+#define PT_PRIM_EMISSIVE 0x40000000u
+#define PT_PRIM_TRIMASK 0x3fffffffu
+
+// Shading record of the same triangle (vertex normals; raytrace.comp:259)
+struct ShadeRecord {           // 48 B
+    float n0x, n0y, n0z; uint32_t materialIndex;
+    float n1x, n1y, n1z; uint32_t objectIndex;
+    float n2x, n2y, n2z; uint32_t triIndex;
+};
+static_assert(sizeof(ShadeRecord) == 48, "ShadeRecord");
+
+struct Xform { float M[16]; float Minv[16]; };   // per distinct object matrix
+
+struct Bvh8View {
+    const Bvh8Node* nodes;
+    const PrimRecord* prims;
+    uint32_t nNodes, nPrims;
+};
+
+struct WideScene {
+    Bvh8View all;              // every instance triangle
+    Bvh8View emis;             // triangles of objects whose material has emissionStrength != 0
+    const ShadeRecord* shade;  // parallel to all.prims
+    const ShadeRecord* shadeEmis;   // parallel to emis.prims
+    const Xform* xforms;
+    const ptl::Sphere* spheres;
+    const ptl::Material* materials;
+    const uint32_t* objXform;  // object -> xformId
+    uint32_t nXforms, nSpheres, nMaterials, nObjects;
+    uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
+};
+
+#define PT_BVH8_STACK 40
+
+}  // namespace pt

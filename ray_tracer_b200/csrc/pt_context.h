@@ -1,0 +1,71 @@
+// Internal state behind the opaque b200pt_ctx of include/b200pt.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "pt_reftrace.h"
+
+namespace pt {
+
+struct HitRecord48 {          // b200pt_trace_batch output record
+    float dst;
+    uint32_t kind, objectHitIndex, triHitIndex, materialIndex, frontFace;
+    float normal[3];
+    float hitPoint[3];
+};
+static_assert(sizeof(HitRecord48) == 48, "HitRecord48");
+
+struct WavefrontState;        // wavefront.cu
+
+struct DeviceBuffer {
+    void* p = nullptr;
+    size_t bytes = 0;
+};
+
+}  // namespace pt
+
+struct b200pt_ctx {
+    int device = 0;
+    int W = 0, H = 0;
+    cudaStream_t ownStream = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    std::string error;
+
+    // reference-layout scene (device) + host copies kept for re-layout on update_*
+    pt::RefScene ref{};
+    pt::DeviceBuffer dSpheres, dMaterials, dPoints, dTris, dObjects, dNodes, dMinv;
+    std::vector<ptl::Sphere> hSpheres;
+    std::vector<ptl::Material> hMaterials;
+    std::vector<ptl::TrianglePoint> hPoints;
+    std::vector<ptl::Triangle> hTris;
+    std::vector<ptl::RenderObject> hObjects;
+    std::vector<ptl::BVHNode> hNodes;
+    bool sceneLoaded = false;
+
+    // outputs
+    pt::DeviceBuffer dAccumOwn, dImage, dStats;
+    float4* accum = nullptr;      // own buffer or caller-attached
+    struct Texture { pt::DeviceBuffer texels; uint32_t w = 0, h = 0; } textures[64];
+
+    // options
+    int pipeline = 1;
+    int framesInFlight = 4;
+
+    // counters (host side; device-side ray counters are folded in by the wavefront)
+    uint64_t counters[16] = {0};
+    float lastMs = 0.f;
+
+    pt::WavefrontState* wf = nullptr;
+};
+
+namespace pt {
+// megakernel.cu
+cudaError_t launch_ref_dispatch(b200pt_ctx* c, const ptl::PushConstants& pc);
+cudaError_t launch_ref_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
+                              uint32_t row0, uint32_t row1);
+cudaError_t launch_ref_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n,
+                                   HitRecord48* dHits);
+}  // namespace pt

@@ -1,0 +1,248 @@
+// Wavefront form of trace()/main() (shaders/raytrace.comp:483-594): the bounce loop is turned
+// inside out — all paths of a batch of progressive frames advance one bounce per stage launch,
+// survivors are compacted into queues. Per-item stage bodies live here as plain functions so
+// that the CUDA kernels (wavefront.cu) stay thin wrappers; the arithmetic per path is the
+// shader's, in the shader's order (pt_shade.h).
+//
+//   generate : main() :541-566       primary ray + per-pixel RNG seed for every (frame, pixel)
+//   extend   : calculateIntersections :276-353   closest hit (spheres, then the wide BVH)
+//   shade    : trace() :492-535      emission / deferred direct light, BSDF sample, roulette
+//   connect  : diffuseBRDF :441-460  NEE + the two lightSamplePDF queries -> directLight, MIS weight
+//   accumulate : main() :568-581     frames summed per pixel in frame order
+//
+// Result-preserving restructurings: (1) the NEE ray and lightSamplePDF(lightSample)
+// are the same ray (A-Q10) and are traced once; (2) lightSamplePDF only needs "is the closest hit
+// emissive, and its distance": closest hit among EMISSIVE geometry (tiny) + a bounded occlusion
+// query against the rest, instead of two more full closest-hit searches.
+#pragma once
+#include "pt_traverse.h"
+
+namespace pt {
+
+#if !defined(__CUDACC__)
+struct float4 { float x, y, z, w; };
+inline float4 make_float4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
+#endif
+
+struct PathArrays {
+    float4* rayO;      // origin.xyz | misWeight
+    float4* rayD;      // dir.xyz    | rng state (bits)
+    float4* atten;     // attenuation.xyz
+    float4* total;     // totalColor.xyz
+    float4* direct;    // directLight.xyz (x == -1: specular sentinel, raytrace.comp:468,480,500)
+    Hit* hit;          // extend result
+    float4* qO;        // NEE origin.xyz (hit + n*0.01) | cosinePDF(lightSample)
+    float4* qL;        // lightSample.xyz               | realCosinePDF
+    float4* qA;        // albedo*INV_PI*max(0, n.lightSample)
+};
+
+struct WfParams {
+    ptl::PushConstants pc;
+    CameraPlane cp;
+    int W, H;
+    uint32_t row0, rows;            // row band rendered
+    uint32_t firstFrame, stride;    // slot k renders frameCount = firstFrame + k*stride
+    uint32_t nSlots, nPaths;        // nPaths = nSlots * rows * W
+};
+
+PT_HD v3 xyz(const float4& f) { return mk3(f.x, f.y, f.z); }
+PT_HD float4 f4(v3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
+
+// ---- generate -------------------------------------------------------------------------------
+PT_HD void stage_generate(const WfParams& P, const PathArrays& A, uint32_t p) {
+    uint32_t perSlot = P.rows * (uint32_t)P.W;
+    uint32_t k = p / perSlot, rem = p - k * perSlot;
+    uint32_t gy = P.row0 + rem / (uint32_t)P.W, gx = rem % (uint32_t)P.W;
+    uint32_t frame = P.firstFrame + k * P.stride;
+    Ray r = primary_ray(P.pc.cam, P.cp, gx, gy, P.W, P.H);
+    uint32_t state = gy * (uint32_t)P.W + gx + frame_seed(frame);
+    A.rayO[p] = f4(r.o, 1.f);                       // misWeight = 1
+    A.rayD[p] = f4(r.d, as_float(state));
+    A.atten[p] = make_float4(1.f, 1.f, 1.f, 0.f);
+    A.total[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+    A.direct[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// ---- extend ---------------------------------------------------------------------------------
+PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount) {
+    Hit h; h.dst = PT_FAR; h.id = PT_HIT_MISS; h.u = 0.f; h.v = 0.f;
+    for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
+        float dst; bool front;
+        if (sphere_test(sc.spheres[i], ray, dst, front) && dst < h.dst) {
+            h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i;
+        }
+    }
+    bvh8_closest(sc.all, sc.xforms, ray, objectCount, h);
+    return h;
+}
+PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+    Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+    A.hit[p] = wide_closest_hit(sc, r, P.pc.params.sphereCount, P.pc.params.objectCount);
+}
+
+// World-space hit point, shading normal and material of a Hit (raytrace.comp:218-221 for spheres;
+// :247,:259,:318-319 for triangles).
+PT_HD void hit_surface(const WideScene& sc, const Ray& ray, const Hit& h, v3& hp, v3& n, uint32_t& material, bool& front,
+                       uint32_t& objectIndex, uint32_t& primIndex) {
+    front = (h.id & PT_HIT_FRONT) != 0;
+    uint32_t idx = h.id & PT_HIT_IDMASK;
+    if (h.id & PT_HIT_SPHERE) {
+        const ptl::Sphere s = sc.spheres[idx];
+        sphere_surface(s, ray, h.dst, front, hp, n);
+        material = s.materialIndex; objectIndex = 0xffffffffu; primIndex = idx;
+    } else {
+        const ShadeRecord s = sc.shade[idx];
+        const Xform& x = sc.xforms[sc.objXform[s.objectIndex]];
+        Ray orr; orr.d = mul_dir(x.Minv, ray.d); orr.o = mul_point(x.Minv, ray.o);
+        tri_surface(x.M, orr, h.dst, h.u, h.v, front, mk3(s.n0x, s.n0y, s.n0z), mk3(s.n1x, s.n1y, s.n1z),
+                    mk3(s.n2x, s.n2y, s.n2z), hp, n);
+        material = s.materialIndex; objectIndex = s.objectIndex; primIndex = s.triIndex;
+    }
+}
+
+// ---- shade ----------------------------------------------------------------------------------
+#define PT_SHADE_CONTINUE 1u      /* path goes on to bounce j+1 */
+#define PT_SHADE_CONNECT 2u       /* diffuse bounce: NEE/pdf queries pending for this path */
+
+PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p, uint32_t j) {
+    const ptl::RayTracerData& td = P.pc.params;
+    float4 ro = A.rayO[p], rd = A.rayD[p];
+    Ray ray; ray.o = xyz(ro); ray.d = xyz(rd);
+    float misWeight = ro.w;
+    uint32_t state = as_uint(rd.w);
+    v3 total = xyz(A.total[p]), atten = xyz(A.atten[p]), direct = xyz(A.direct[p]);
+    const Hit h = A.hit[p];
+
+    if (h.id == PT_HIT_MISS) {                                   // raytrace.comp:531-534
+        total = total + atten * environment_light(P.pc.env, ray.d);
+        A.total[p] = f4(total, 0.f);
+        return 0u;
+    }
+    v3 hp, n; uint32_t matIdx, objIdx, primIdx; bool front;
+    hit_surface(sc, ray, h, hp, n, matIdx, front, objIdx, primIdx);
+    const ptl::Material mat = sc.materials[matIdx];
+
+    v3 emission = mk3(mat.emissionColor[0], mat.emissionColor[1], mat.emissionColor[2]) * mat.emissionStrength / misWeight;
+    v3 finalLight = direct.x == -1.f ? emission : direct;        // :499-500
+    total = total + finalLight * atten;
+    if (j == 0) total = total + emission;
+    if (isnan3(total) || total.x < 0.f || total.y < 0.f || total.z < 0.f) {   // :505 — the whole path returns 0
+        A.total[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+        return 0u;
+    }
+    A.total[p] = f4(total, 0.f);
+
+    v3 dirOut, radiance;
+    float originSign = 1.f, nextMis = 1.f;
+    uint32_t flags = 0u;
+    if (mat.reflectance != 0.f) {                                // :509-510, specularBRDF :466-469
+        dirOut = reflect(ray.d, n); radiance = splat3(1.f); direct = splat3(-1.f);
+    } else if (mat.ior != -1.f) {                                // :511-512, dielectricBTDF :471-481
+        dirOut = dielectric_dir(ray.d, n, front, mat.ior, state, originSign);
+        radiance = splat3(1.f); direct = splat3(-1.f);
+    } else {                                                     // :513-514, diffuseBRDF :430-464 (sampling half)
+        v3 albedo = mk3(mat.albedo[0], mat.albedo[1], mat.albedo[2]);
+        v3 origin = hp + n * 0.01f;
+        v3 lightSample = light_sample_dir(origin, state);
+        v3 cosineSample = cosine_hemisphere_dir(n, state);
+        float cosinePDF = cosine_hemisphere_pdf(n, lightSample);
+        float realCosinePDF = cosine_hemisphere_pdf(n, cosineSample);
+        radiance = albedo * PT_INV_PI * dot(n, cosineSample) / realCosinePDF;
+        v3 Afac = albedo * PT_INV_PI * gmax(0.f, dot(n, lightSample));
+        A.qO[p] = f4(origin, cosinePDF);
+        A.qL[p] = f4(lightSample, realCosinePDF);
+        A.qA[p] = f4(Afac, 0.f);
+        dirOut = cosineSample;
+        direct = splat3(0.f);                                    // filled in by connect
+        flags |= PT_SHADE_CONNECT;
+    }
+    atten = atten * radiance;
+
+    float rr = gmax(gmax(atten.x, atten.y), atten.z);            // :519-524
+    rr = gmin(rr, 0.95f);
+    rr = j <= 5 ? 1.f : rr;
+    if (rng_next(state) > rr) return 0u;                         // break: pending direct light is dropped
+    if (j >= td.bounceLimit) return 0u;                          // loop ends: nothing computed now is consumed
+    atten = atten * (1.f / rr);
+
+    A.atten[p] = f4(atten, 0.f);
+    A.direct[p] = f4(direct, 0.f);
+    A.rayO[p] = f4(hp + n * originSign * 0.00001f, nextMis);     // :527-529 (misWeight overwritten by connect for diffuse)
+    A.rayD[p] = f4(dirOut, as_float(state));
+    return flags | PT_SHADE_CONTINUE;
+}
+
+// ---- connect --------------------------------------------------------------------------------
+// lightSamplePDF() (raytrace.comp:389-403) for (origin, dir): nonzero only when the closest hit of
+// the ray is emissive. matOut = material of that hit.
+PT_HD float emissive_pdf(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& matOut,
+                         bool& emissiveClosest) {
+    matOut = 0u; emissiveClosest = false;
+    if (!sc.anyEmissive) return 0.f;
+    Ray r; r.o = origin; r.d = dir;
+    Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
+    uint32_t keyE = 0u;
+    for (uint32_t i = 0; i < sphereCount; i++) {
+        const ptl::Sphere s = sc.spheres[i];
+        if (sc.materials[s.materialIndex].emissionStrength == 0.f) continue;
+        float dst; bool front;
+        if (sphere_test(s, r, dst, front) && dst < e.dst) { e.dst = dst; e.id = PT_HIT_SPHERE | i; keyE = i; matOut = s.materialIndex; }
+    }
+    uint32_t before = e.id;
+    bvh8_closest(sc.emis, sc.xforms, r, objectCount, e);
+    if (e.id == PT_HIT_MISS) return 0.f;
+    if (e.id != before) {
+        const ShadeRecord s = sc.shadeEmis[e.id & PT_HIT_IDMASK];
+        keyE = sc.nSpheres + s.objectIndex; matOut = s.materialIndex;
+    }
+    for (uint32_t i = 0; i < sphereCount; i++) {
+        const ptl::Sphere s = sc.spheres[i];
+        if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
+        float dst; bool front;
+        if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return 0.f;
+    }
+    if (bvh8_occluded(sc.all, sc.xforms, r, objectCount, e.dst, keyE)) return 0.f;
+    emissiveClosest = true;
+    return light_pdf_from_dst(e.dst, dir);
+}
+
+PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+    const ptl::RayTracerData& td = P.pc.params;
+    float4 qo = A.qO[p], ql = A.qL[p];
+    v3 origin = xyz(qo), lightSample = xyz(ql), cosineSample = xyz(A.rayD[p]);
+    float cosinePDF = qo.w, realCosinePDF = ql.w;
+    uint32_t lightMat, unused;
+    bool lightIsClosest, unusedB;
+    float realLightPDF = emissive_pdf(sc, origin, lightSample, td.sphereCount, td.objectCount, lightMat, lightIsClosest);   // :443-447
+    float w1 = mis_weight(realLightPDF, cosinePDF);                                                        // :449-450
+    float lightPDF = emissive_pdf(sc, origin, cosineSample, td.sphereCount, td.objectCount, unused, unusedB);       // :453
+    float w2 = mis_weight(realCosinePDF, lightPDF);                                                        // :455-456
+    v3 E = splat3(0.f);           // a non-emissive (or missing) closest hit contributes emission * 0
+    if (lightIsClosest) {
+        const ptl::Material lm = sc.materials[lightMat];
+        E = mk3(lm.emissionColor[0], lm.emissionColor[1], lm.emissionColor[2]) * lm.emissionStrength;
+    }
+    v3 direct = E * (xyz(A.qA[p]) * (realLightPDF == 0.f ? 0.f : w1 / realLightPDF));                       // :459-460
+    A.direct[p] = f4(direct, 0.f);
+    float4 ro = A.rayO[p];
+    ro.w = w2;
+    A.rayO[p] = ro;
+}
+
+// ---- accumulate -----------------------------------------------------------------------------
+// outColor of each frame slot added in frame order (raytrace.comp:568-581: mean over 1 sample,
+// NaN/Inf -> magenta); accum.a counts frames.
+PT_HD void stage_accumulate(const WfParams& P, const PathArrays& A, float4* accum, uint32_t pix) {
+    uint32_t perSlot = P.rows * (uint32_t)P.W;
+    uint32_t gy = P.row0 + pix / (uint32_t)P.W, gx = pix % (uint32_t)P.W;
+    size_t g = (size_t)gy * P.W + gx;
+    float4 a = accum[g];
+    for (uint32_t k = 0; k < P.nSlots; ++k) {
+        v3 c = xyz(A.total[k * perSlot + pix]);
+        if (isnan3(c) || isinf3(c)) c = mk3(1.f, 0.f, 1.f);
+        a.x += c.x; a.y += c.y; a.z += c.z; a.w += 1.f;
+    }
+    accum[g] = a;
+}
+
+}  // namespace pt

@@ -61,6 +61,8 @@ def lib():
         L.orc_default_push_constants.argtypes = [i32, i32, u32, u32, vp]
         L.orc_set_camera_angles.argtypes = [vp, f32, f32, f32]
         L.orc_math_eval.argtypes = [C.c_char_p, vp, vp]
+        L.orc_set_math_mode.argtypes = [i32]
+        L.orc_math_mode.restype = i32
         _lib = L
     return _lib
 
@@ -234,3 +236,17 @@ def random_stream(state, n):
 
 def starting_seed(frame):
     return lib().orc_starting_seed(frame)
+
+
+class math_mode:
+    """Context manager: 1 = the backend's portable double-precision sin/cos/pow/tan, 0 = libm (default)."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = lib().orc_math_mode()
+        lib().orc_set_math_mode(self.mode)
+
+    def __exit__(self, *a):
+        lib().orc_set_math_mode(self.prev)
