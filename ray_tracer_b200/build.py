@@ -1,0 +1,52 @@
+"""Builds ray_tracer_b200/libb200pt.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
+
+-fmad=false: every float operator in the kernels is one IEEE-754 operation, so results are
+reproducible against the CPU oracle (csrc/pt_math.h); box tests use explicit FMA intrinsics.
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libb200pt.so")
+SOURCES = ["api.cu", "megakernel.cu", "wavefront.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
+              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-O2,-fno-fast-math,-ffp-contract=off", "-shared",
+              "-cudart", "static"]
+
+
+def nvcc_path():
+    for p in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if p and os.path.exists(p):
+            return p
+    raise RuntimeError("nvcc not found")
+
+
+def needs_build():
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "b200pt.h"), __file__]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False, extra=()):
+    if not force and not needs_build():
+        return LIB
+    env = dict(os.environ)
+    env.pop("CXX", None)    # the image's $CXX points at a g++ without its spec files
+    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-ccbin", "/usr/bin/g++", "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    if verbose:
+        print(" ".join(cmd))
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stdout + r.stderr)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose=True, extra=["-Xptxas", "-v"] if "--ptxas" in sys.argv else ()))

@@ -10,7 +10,7 @@
 
 #if defined(__CUDACC__)
 #define PT_HD __host__ __device__ __forceinline__
-#define PT_HD_NOINLINE __host__ __device__
+#define PT_HD_NOINLINE __host__ __device__ inline
 #else
 #define PT_HD inline
 #define PT_HD_NOINLINE inline

@@ -1,0 +1,317 @@
+// Wavefront path-tracing pipeline for sm_100a: thin kernels around the stage bodies of
+// pt_wavefront.h, device-side queues with warp-aggregated compaction, no host round trip inside
+// a batch. Compiled with -fmad=false (pt_math.h); box tests use explicit FMAs.
+//
+// One batch = `slots` progressive frames x the row band x W pixels, all in flight at once
+// (frames have independent seeds, raytrace.comp:562-564; samples inside one dispatch do not, A-Q5).
+// Launch sequence per batch:  generate, { extend_j, shade_j, connect_j } for j = 0..bounceLimit,
+// accumulate, fold.  Queue sizes live in device memory (qCount[j], sCount[j]); every kernel is a
+// grid-stride loop over its queue sized to the SM count, so an empty queue costs one idle launch.
+#include <algorithm>
+
+#include "bvh8_build.h"
+#include "pt_wavefront.h"
+#include "wavefront.h"
+
+namespace pt {
+
+struct WavefrontState {
+    // re-laid-out scene
+    DeviceBuffer dNodes, dPrims, dShade, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform;
+    WideScene scene{};
+    uint32_t maxDepth = 0;
+    // path state
+    DeviceBuffer dPaths[9];
+    DeviceBuffer dHit, dQueue[2], dShadowQ, dCounts, dRayCounters;
+    PathArrays arrays{};
+    size_t capacity = 0;
+    uint32_t countSlots = 0;
+    int smCount = 148;
+};
+
+#define WF_THREADS 128
+
+static __device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred) {
+    // warp-aggregated queue append: one atomic per warp; returns this lane's slot (valid when pred)
+    unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0) return 0;
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+}
+
+__global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__ WfParams P, PathArrays A, uint32_t* queue, uint32_t* qCount) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < P.nPaths; p += gridDim.x * blockDim.x) {
+        stage_generate(P, A, p);
+        queue[p] = p;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) qCount[0] = P.nPaths;
+}
+
+__global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                       const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount) {
+    uint32_t n = *qCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        stage_extend(P, sc, A, queue[i]);
+}
+
+__global__ void __launch_bounds__(WF_THREADS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                      const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
+                                                      uint32_t* nextQueue, uint32_t* nextCount, uint32_t* shadowQueue, uint32_t* shadowCount,
+                                                      uint32_t j) {
+    uint32_t n = *qCount;
+    uint32_t nRound = (n + 31u) & ~31u;           // whole warps stay together for the ballots
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
+        uint32_t flags = 0, p = 0;
+        if (i < n) { p = queue[i]; flags = stage_shade(P, sc, A, p, j); }
+        bool go = (flags & PT_SHADE_CONTINUE) != 0;
+        bool sh = go && (flags & PT_SHADE_CONNECT) != 0;
+        uint32_t s0 = warp_push(nextCount, go);
+        if (go) nextQueue[s0] = p;
+        uint32_t s1 = warp_push(shadowCount, sh);
+        if (sh) shadowQueue[s1] = p;
+    }
+}
+
+__global__ void __launch_bounds__(WF_THREADS) k_connect(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount) {
+    uint32_t n = *sCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        stage_connect(P, sc, A, queue[i]);
+}
+
+__global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant__ WfParams P, PathArrays A, float4* accum) {
+    uint32_t n = P.rows * (uint32_t)P.W;
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < n; pix += gridDim.x * blockDim.x)
+        stage_accumulate(P, A, accum, pix);
+}
+
+// ray counters: [0] += extension rays (sum of qCount), [1] += NEE/pdf queries (2 per connect item)
+__global__ void k_fold(const uint32_t* qCount, const uint32_t* sCount, uint32_t nBounce, unsigned long long* rayCounters) {
+    if (blockIdx.x || threadIdx.x) return;
+    unsigned long long e = 0, s = 0;
+    for (uint32_t j = 0; j < nBounce; ++j) { e += qCount[j]; s += sCount[j]; }
+    rayCounters[0] += e;
+    rayCounters[1] += 2ull * s;
+}
+
+__global__ void k_wide_trace_batch(const __grid_constant__ WideScene sc, uint32_t sphereCount, uint32_t objectCount,
+                                   const float4* __restrict__ rays, uint64_t n, HitRecord48* out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 o = rays[2 * i], d = rays[2 * i + 1];
+    Ray r; r.o = mk3(o.x, o.y, o.z); r.d = mk3(d.x, d.y, d.z);
+    Hit h = wide_closest_hit(sc, r, sphereCount, objectCount);
+    HitRecord48 rec;
+    memset(&rec, 0, sizeof(rec));
+    rec.dst = h.dst; rec.objectHitIndex = 0xffffffffu;
+    if (h.id != PT_HIT_MISS) {
+        v3 hp, nn; uint32_t mat, obj, prim; bool front;
+        hit_surface(sc, r, h, hp, nn, mat, front, obj, prim);
+        rec.kind = (h.id & PT_HIT_SPHERE) ? 1u : 2u;
+        rec.objectHitIndex = obj; rec.triHitIndex = prim; rec.materialIndex = mat; rec.frontFace = front ? 1u : 0u;
+        rec.normal[0] = nn.x; rec.normal[1] = nn.y; rec.normal[2] = nn.z;
+        rec.hitPoint[0] = hp.x; rec.hitPoint[1] = hp.y; rec.hitPoint[2] = hp.z;
+    }
+    out[i] = rec;
+}
+
+// Vulkan unorm8 store of the float image: clamp, scale, round to nearest even (f4 of SURVEY.md §8)
+__global__ void k_image_to_rgba8(const float4* __restrict__ img, uchar4* out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 c = img[i];
+    auto q = [](float f) -> unsigned char {
+        if (!(f > 0.f)) return 0;
+        if (f >= 1.f) return 255;
+        return (unsigned char)__float2int_rn(f * 255.f);
+    };
+    out[i] = make_uchar4(q(c.x), q(c.y), q(c.z), 255);
+}
+
+// ---------------------------------------------------------------------------------------------
+static int wf_fail(b200pt_ctx* c, int code, const char* what, cudaError_t e) {
+    c->error = std::string(what) + ": " + (e == cudaSuccess ? "" : cudaGetErrorString(e));
+    return code;
+}
+#define WCU(call)                                                        \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) return wf_fail(c, 2, #call, e_);          \
+    } while (0)
+
+static cudaError_t wf_resize(DeviceBuffer& b, size_t bytes) {
+    if (b.p && bytes <= b.bytes) return cudaSuccess;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.bytes = 0;
+    if (!bytes) return cudaSuccess;
+    cudaError_t e = cudaMalloc(&b.p, bytes);
+    if (e == cudaSuccess) b.bytes = bytes;
+    return e;
+}
+static void wf_free(DeviceBuffer& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
+
+template <class T>
+static cudaError_t wf_upload(b200pt_ctx* c, DeviceBuffer& d, const std::vector<T>& h) {
+    cudaError_t e = wf_resize(d, std::max<size_t>(h.size() * sizeof(T), 16));
+    if (e == cudaSuccess && !h.empty()) e = cudaMemcpyAsync(d.p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream);
+    return e;
+}
+
+int wavefront_build_scene(b200pt_ctx* c) {
+    if (!c->wf) {
+        c->wf = new WavefrontState();
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, c->device) == cudaSuccess) c->wf->smCount = prop.multiProcessorCount;
+    }
+    WavefrontState* w = c->wf;
+    WideSceneHost host;
+    if (const char* err = build_wide_scene(c->hSpheres, c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, host)) {
+        c->error = std::string("scene re-layout: ") + err;
+        return 1;
+    }
+    WCU(wf_upload(c, w->dNodes, host.all.nodes));
+    WCU(wf_upload(c, w->dPrims, host.all.prims));
+    WCU(wf_upload(c, w->dShade, host.all.shade));
+    WCU(wf_upload(c, w->dNodesE, host.emis.nodes));
+    WCU(wf_upload(c, w->dPrimsE, host.emis.prims));
+    WCU(wf_upload(c, w->dShadeE, host.emis.shade));
+    WCU(wf_upload(c, w->dXforms, host.xforms));
+    WCU(wf_upload(c, w->dObjXform, host.objXform));
+    WCU(cudaStreamSynchronize(c->stream));        // `host` is a local
+    WideScene& s = w->scene;
+    s.all = {(const Bvh8Node*)w->dNodes.p, (const PrimRecord*)w->dPrims.p, (uint32_t)host.all.nodes.size(), (uint32_t)host.all.prims.size()};
+    s.emis = {(const Bvh8Node*)w->dNodesE.p, (const PrimRecord*)w->dPrimsE.p, (uint32_t)host.emis.nodes.size(), (uint32_t)host.emis.prims.size()};
+    s.shade = (const ShadeRecord*)w->dShade.p;
+    s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
+    s.xforms = (const Xform*)w->dXforms.p;
+    s.objXform = (const uint32_t*)w->dObjXform.p;
+    s.spheres = c->ref.spheres; s.materials = c->ref.materials;
+    s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
+    s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
+    s.anyEmissive = host.anyEmissive ? 1u : 0u;
+    w->maxDepth = host.all.maxDepth;
+    return 0;
+}
+
+void wavefront_invalidate_frame_state(b200pt_ctx*) {}
+
+void wavefront_destroy(b200pt_ctx* c) {
+    WavefrontState* w = c->wf;
+    if (!w) return;
+    DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform,
+                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dCounts, &w->dRayCounters};
+    for (DeviceBuffer* b : all) wf_free(*b);
+    for (auto& b : w->dPaths) wf_free(b);
+    delete w;
+    c->wf = nullptr;
+}
+
+static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
+    WavefrontState* w = c->wf;
+    if (paths > w->capacity) {
+        for (auto& b : w->dPaths) WCU(wf_resize(b, paths * 16));
+        WCU(wf_resize(w->dHit, paths * sizeof(Hit)));
+        WCU(wf_resize(w->dQueue[0], paths * 4));
+        WCU(wf_resize(w->dQueue[1], paths * 4));
+        WCU(wf_resize(w->dShadowQ, paths * 4));
+        w->capacity = paths;
+        PathArrays& A = w->arrays;
+        A.rayO = (float4*)w->dPaths[0].p; A.rayD = (float4*)w->dPaths[1].p; A.atten = (float4*)w->dPaths[2].p;
+        A.total = (float4*)w->dPaths[3].p; A.direct = (float4*)w->dPaths[4].p; A.qO = (float4*)w->dPaths[5].p;
+        A.qL = (float4*)w->dPaths[6].p; A.qA = (float4*)w->dPaths[7].p; A.hit = (Hit*)w->dHit.p;
+    }
+    uint32_t need = bounces + 3;
+    if (need > w->countSlots) {
+        WCU(wf_resize(w->dCounts, (size_t)need * 2 * 4));
+        w->countSlots = need;
+    }
+    if (!w->dRayCounters.p) {
+        WCU(wf_resize(w->dRayCounters, 16));
+        WCU(cudaMemsetAsync(w->dRayCounters.p, 0, 16, c->stream));
+    }
+    return 0;
+}
+
+int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
+                            uint32_t row0, uint32_t row1) {
+    WavefrontState* w = c->wf;
+    if (!w) { c->error = "wavefront: no scene"; return 3; }
+    if (n == 0 || row1 <= row0) return 0;
+    uint32_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
+    if (samples != 1) {
+        // samples inside one dispatch share a sequential RNG state (A-Q5): served by the per-pixel kernel
+        cudaError_t e = launch_ref_frames(c, pc, first, n, stride, row0, row1);
+        if (e != cudaSuccess) return wf_fail(c, 2, "launch_ref_frames", e);
+        return 0;
+    }
+    uint32_t rows = row1 - row0;
+    size_t perSlot = (size_t)rows * c->W;
+    uint32_t slots = (uint32_t)std::min<uint64_t>((uint64_t)c->framesInFlight, n);
+    // keep a batch below 2^31 paths and ~64M paths (10 GB of path state)
+    while (slots > 1 && perSlot * slots > ((size_t)1 << 26)) slots--;
+    if (int rc = wf_reserve(c, perSlot * slots, pc.params.bounceLimit)) return rc;
+    const int grid = w->smCount * 8;
+    WfParams P;
+    P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
+    uint32_t nB = pc.params.bounceLimit + 1;
+    uint32_t* qCount = (uint32_t*)w->dCounts.p;
+    uint32_t* sCount = qCount + w->countSlots;
+    for (uint32_t done = 0; done < n; done += slots) {
+        P.nSlots = std::min(slots, n - done);
+        P.firstFrame = first + done * stride;
+        P.nPaths = (uint32_t)(perSlot * P.nSlots);
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 2 * 4, c->stream));
+        uint32_t* qa = (uint32_t*)w->dQueue[0].p;
+        uint32_t* qb = (uint32_t*)w->dQueue[1].p;
+        k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount);
+        for (uint32_t j = 0; j < nB; ++j) {
+            k_extend<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j);
+            k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
+                                                        (uint32_t*)w->dShadowQ.p, sCount + j, j);
+            if (j + 1 < nB)
+                k_connect<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j);
+            std::swap(qa, qb);
+            c->counters[0] += (j + 1 < nB) ? 3 : 2;
+        }
+        k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
+        k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
+        c->counters[0] += 3;
+        c->counters[1] += P.nPaths;
+        WCU(cudaGetLastError());
+    }
+    return 0;
+}
+
+int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits) {
+    WavefrontState* w = c->wf;
+    if (!w) { c->error = "wavefront: no scene"; return 3; }
+    if (n == 0) return 0;
+    k_wide_trace_batch<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(w->scene, pc.params.sphereCount, pc.params.objectCount,
+                                                                         (const float4*)dRays, n, dHits);
+    c->counters[0] += 1;
+    c->counters[2] += n;
+    WCU(cudaGetLastError());
+    return 0;
+}
+
+// called with the stream idle: moves the device ray counters into the context's counters
+void wavefront_fold_counters(b200pt_ctx* c) {
+    WavefrontState* w = c->wf;
+    if (!w || !w->dRayCounters.p) return;
+    unsigned long long h[2] = {0, 0};
+    if (cudaMemcpy(h, w->dRayCounters.p, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    c->counters[2] += h[0];
+    c->counters[3] += h[1];
+    cudaMemset(w->dRayCounters.p, 0, 16);
+}
+
+cudaError_t launch_image_to_rgba8(b200pt_ctx* c, const float4* image, uchar4* out, size_t n) {
+    k_image_to_rgba8<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(image, out, n);
+    return cudaGetLastError();
+}
+
+}  // namespace pt

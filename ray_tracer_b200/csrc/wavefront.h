@@ -1,0 +1,14 @@
+// Host-side interface of the wavefront pipeline (wavefront.cu) used by api.cu.
+#pragma once
+#include "pt_context.h"
+
+namespace pt {
+int wavefront_build_scene(b200pt_ctx* c);        // re-layout of the uploaded scene; 0 or a B200PT_ERR_* with c->error set
+void wavefront_destroy(b200pt_ctx* c);
+void wavefront_invalidate_frame_state(b200pt_ctx* c);
+int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
+                            uint32_t row0, uint32_t row1);
+int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits);
+void wavefront_fold_counters(b200pt_ctx* c);
+cudaError_t launch_image_to_rgba8(b200pt_ctx* c, const float4* image, uchar4* out, size_t n);
+}  // namespace pt
