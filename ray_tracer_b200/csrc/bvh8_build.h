@@ -24,6 +24,7 @@ struct WideSceneHost {
     Bvh8Host all, emis;
     std::vector<Xform> xforms;
     std::vector<uint32_t> objXform;
+    std::vector<UpNode> up;
     bool anyEmissive = false;
 };
 
@@ -284,6 +285,19 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
         out.objXform[o] = id;
     }
 
+    // parent links and triangle -> leaf map of the reference BVH2
+    out.up.resize(nodes.size());
+    std::vector<uint32_t> leafOf(tris.size(), 0xffffffffu);
+    for (size_t i = 0; i < nodes.size(); ++i) {
+        UpNode& u = out.up[i];
+        u.minX = nodes[i].minX; u.maxX = nodes[i].maxX; u.minY = nodes[i].minY; u.maxY = nodes[i].maxY;
+        u.minZ = nodes[i].minZ; u.maxZ = nodes[i].maxZ; u.parent = 0xffffffffu; u.pad = 0;
+    }
+    for (size_t i = 0; i < nodes.size(); ++i) {
+        if (nodes[i].triCount) { for (uint32_t t = nodes[i].index; t < nodes[i].index + nodes[i].triCount; ++t) leafOf[t] = (uint32_t)i; }
+        else { out.up[nodes[i].index].parent = (uint32_t)i; out.up[nodes[i].index + 1].parent = (uint32_t)i; }
+    }
+
     std::vector<Box> boxes, boxesE;
     std::vector<Instance> inst, instE;
     std::vector<PrimRecord> prim, primE;
@@ -312,7 +326,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             r.e1x = te.e1.x; r.e1y = te.e1.y; r.e1z = te.e1.z;
             r.triIndexFlags = (t & PT_PRIM_TRIMASK) | (tr.frontOnly ? PT_PRIM_FRONTONLY : 0u) | (em ? PT_PRIM_EMISSIVE : 0u);
             r.e2x = te.e2.x; r.e2y = te.e2.y; r.e2z = te.e2.z; r.xformId = out.objXform[o];
-            r.nx = te.n.x; r.ny = te.n.y; r.nz = te.n.z; r.orderKey = (uint32_t)(spheres.size() + o);
+            r.nx = te.n.x; r.ny = te.n.y; r.nz = te.n.z; r.leafNode = leafOf[t];
             ShadeRecord s;
             s.n0x = a.nx; s.n0y = a.ny; s.n0z = a.nz; s.materialIndex = ob.materialIndex;
             s.n1x = b.nx; s.n1y = b.ny; s.n1z = b.nz; s.objectIndex = (uint32_t)o;

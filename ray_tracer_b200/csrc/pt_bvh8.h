@@ -29,7 +29,7 @@ struct PrimRecord {            // 64 B
     float p0x, p0y, p0z; uint32_t objectIndex;
     float e1x, e1y, e1z; uint32_t triIndexFlags;   // bit31 frontOnly, bit30 emissive material, low 30 bits triangle index
     float e2x, e2y, e2z; uint32_t xformId;
-    float nx, ny, nz;    uint32_t orderKey;        // sphereCount + objectIndex: tie order of the reference's loops
+    float nx, ny, nz;    uint32_t leafNode;        // reference BVH2 leaf holding this triangle (index into UpNode[])
 };
 static_assert(sizeof(PrimRecord) == 64, "PrimRecord");
 #define PT_PRIM_FRONTONLY 0x80000000u
@@ -46,6 +46,19 @@ static_assert(sizeof(ShadeRecord) == 48, "ShadeRecord");
 
 struct Xform { float M[16]; float Minv[16]; };   // per distinct object matrix
 
+// The reference's own BVH2 (src/vk_engine.h:185-189), re-linked child -> parent. The reference
+// only tests a triangle when its slab test (raytrace.comp:263-274) passed for every node between
+// the object's root and the triangle's leaf; a ray that grazes one of those boxes can miss a
+// triangle it geometrically hits. To return the reference's hit and not merely the geometrically
+// closest one, a candidate found through the wide BVH is confirmed by re-running those slab tests
+// leaf-to-root (pt_traverse.h: ref_reachable).
+struct UpNode {                // 32 B
+    float minX, maxX, minY, maxY, minZ, maxZ;
+    uint32_t parent;           // 0xffffffff for an object's root (whose own box the shader never tests)
+    uint32_t pad;
+};
+static_assert(sizeof(UpNode) == 32, "UpNode");
+
 struct Bvh8View {
     const Bvh8Node* nodes;
     const PrimRecord* prims;
@@ -58,6 +71,7 @@ struct WideScene {
     const ShadeRecord* shade;  // parallel to all.prims
     const ShadeRecord* shadeEmis;   // parallel to emis.prims
     const Xform* xforms;
+    const UpNode* up;          // parallel to the reference's bvhNodes
     const ptl::Sphere* spheres;
     const ptl::Material* materials;
     const uint32_t* objXform;  // object -> xformId

@@ -86,16 +86,43 @@ PT_HD uint32_t bvh8_node_hits(const Bvh8Node& n, const BoxRay& br, float tmax) {
     return hits;
 }
 
-struct ObjRayCache { uint32_t xform; Ray r; };
+struct ObjRayCache { uint32_t xform; Ray r; v3 inv; };
 
 PT_HD const Ray& object_ray(ObjRayCache& c, const Xform* xforms, uint32_t xformId, const Ray& world) {
     if (c.xform != xformId) {
         const float* Minv = xforms[xformId].Minv;
         c.r.d = mul_dir(Minv, world.d);       // raytrace.comp:292 (direction not renormalised: t stays world-parametric)
         c.r.o = mul_point(Minv, world.o);     // raytrace.comp:293
+        c.inv = mk3(1.f / c.r.d.x, 1.f / c.r.d.y, 1.f / c.r.d.z);   // raytrace.comp:294
         c.xform = xformId;
     }
     return c.r;
+}
+
+// Would the reference have tested the triangle in BVH2 leaf `leaf`? It does iff boxIntersection()
+// (raytrace.comp:263-274) reports a hit for every node from the leaf up to, not including, the
+// object's root (:324-348; the root's own box is never tested, :301-307). The walk stops early once
+// the object-space hit point is inside a box with a margin far above the slab test's rounding
+// error: every ancestor contains that box, so their tests pass a fortiori. Axes on which the leaf is
+// flat (axis-aligned triangles) are exempt from the margin: there tMin == tMax is the plane distance
+// itself and rounding is monotone in the box coordinate.
+PT_HD bool ref_reachable(const UpNode* __restrict__ up, uint32_t leaf, const ObjRayCache& c, float dst) {
+    UpNode n = up[leaf];
+    if (n.parent == 0xffffffffu) return true;
+    v3 h = c.r.o + c.r.d * dst;
+    float m = 2e-5f * (fmaxf(fmaxf(fabsf(h.x), fabsf(h.y)), fabsf(h.z)) + fmaxf(fmaxf(fabsf(c.r.o.x), fabsf(c.r.o.y)), fabsf(c.r.o.z))) + 1e-30f;
+    v3 dh = h - c.r.o;
+    bool farEnough = fmaxf(fmaxf(fabsf(dh.x), fabsf(dh.y)), fabsf(dh.z)) > m;
+    bool flatX = n.minX == n.maxX, flatY = n.minY == n.maxY, flatZ = n.minZ == n.maxZ;
+    for (;;) {
+        if (box_test_ref(mk3(n.minX, n.minY, n.minZ), mk3(n.maxX, n.maxY, n.maxZ), c.r.o, c.inv) == PT_FAR) return false;
+        bool inX = flatX || (h.x >= n.minX + m && h.x <= n.maxX - m);
+        bool inY = flatY || (h.y >= n.minY + m && h.y <= n.maxY - m);
+        bool inZ = flatZ || (h.z >= n.minZ + m && h.z <= n.maxZ - m);
+        if (inX && inY && inZ && farEnough) return true;
+        n = up[n.parent];
+        if (n.parent == 0xffffffffu) return true;
+    }
 }
 
 PT_HD TriEdges prim_edges(const PrimRecord& p) {
@@ -106,7 +133,10 @@ PT_HD TriEdges prim_edges(const PrimRecord& p) {
 }
 
 // Closest triangle hit strictly closer than hit.dst (the reference's `hitInfo.dst < closestHit.dst`).
-PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const Ray& ray, uint32_t objectCount, Hit& hit) {
+// `key` is the position of the current best hit in the reference's loop order (sphere i -> i, object o
+// -> nSpheres + o; 0xffffffff for none): the reference keeps the FIRST of equal-distance hits.
+PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
+                                 uint32_t objectCount, Hit& hit, uint32_t& key) {
     BoxRay br = make_box_ray(ray);
     ObjRayCache oc; oc.xform = 0xffffffffu;
     uint32_t oct = br.octinv4 & 7u;
@@ -137,9 +167,11 @@ PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const
             if (p.objectIndex >= objectCount) continue;
             const Ray& tr = object_ray(oc, xforms, p.xformId, ray);
             float dst, u, v; bool front;
-            if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) && dst < hit.dst) {
+            if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
+                (dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key)) && ref_reachable(up, p.leafNode, oc, dst)) {
                 hit.dst = dst; hit.u = u; hit.v = v;
                 hit.id = pi | (front ? PT_HIT_FRONT : 0u);
+                key = nSpheres + p.objectIndex;
             }
         }
         if ((gBits & 0xff000000u) == 0) {
@@ -152,7 +184,8 @@ PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const
 // Is there a NON-emissive triangle hit that the reference's closest-hit search would have
 // preferred to an emissive hit at (tE, keyE)? (strictly closer, or equal distance and earlier in
 // the reference's loop order)
-PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const Ray& ray, uint32_t objectCount, float tE, uint32_t keyE) {
+PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
+                                  uint32_t objectCount, float tE, uint32_t keyE) {
     BoxRay br = make_box_ray(ray);
     ObjRayCache oc; oc.xform = 0xffffffffu;
     uint32_t oct = br.octinv4 & 7u;
@@ -183,7 +216,7 @@ PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, cons
             const Ray& tr = object_ray(oc, xforms, p.xformId, ray);
             float dst, u, v; bool front;
             if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
-                (dst < tE || (dst == tE && p.orderKey < keyE)))
+                (dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE)) && ref_reachable(up, p.leafNode, oc, dst))
                 return true;
         }
         if ((gBits & 0xff000000u) == 0) {

@@ -66,13 +66,14 @@ PT_HD void stage_generate(const WfParams& P, const PathArrays& A, uint32_t p) {
 // ---- extend ---------------------------------------------------------------------------------
 PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount) {
     Hit h; h.dst = PT_FAR; h.id = PT_HIT_MISS; h.u = 0.f; h.v = 0.f;
+    uint32_t key = 0xffffffffu;
     for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
         float dst; bool front;
         if (sphere_test(sc.spheres[i], ray, dst, front) && dst < h.dst) {
-            h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i;
+            h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
         }
     }
-    bvh8_closest(sc.all, sc.xforms, ray, objectCount, h);
+    bvh8_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, ray, objectCount, h, key);
     return h;
 }
 PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
@@ -181,7 +182,7 @@ PT_HD float emissive_pdf(const WideScene& sc, v3 origin, v3 dir, uint32_t sphere
     if (!sc.anyEmissive) return 0.f;
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
-    uint32_t keyE = 0u;
+    uint32_t keyE = 0xffffffffu;
     for (uint32_t i = 0; i < sphereCount; i++) {
         const ptl::Sphere s = sc.spheres[i];
         if (sc.materials[s.materialIndex].emissionStrength == 0.f) continue;
@@ -189,19 +190,16 @@ PT_HD float emissive_pdf(const WideScene& sc, v3 origin, v3 dir, uint32_t sphere
         if (sphere_test(s, r, dst, front) && dst < e.dst) { e.dst = dst; e.id = PT_HIT_SPHERE | i; keyE = i; matOut = s.materialIndex; }
     }
     uint32_t before = e.id;
-    bvh8_closest(sc.emis, sc.xforms, r, objectCount, e);
+    bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
     if (e.id == PT_HIT_MISS) return 0.f;
-    if (e.id != before) {
-        const ShadeRecord s = sc.shadeEmis[e.id & PT_HIT_IDMASK];
-        keyE = sc.nSpheres + s.objectIndex; matOut = s.materialIndex;
-    }
+    if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
     for (uint32_t i = 0; i < sphereCount; i++) {
         const ptl::Sphere s = sc.spheres[i];
         if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
         float dst; bool front;
         if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return 0.f;
     }
-    if (bvh8_occluded(sc.all, sc.xforms, r, objectCount, e.dst, keyE)) return 0.f;
+    if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e.dst, keyE)) return 0.f;
     emissiveClosest = true;
     return light_pdf_from_dst(e.dst, dir);
 }

@@ -17,7 +17,7 @@ namespace pt {
 
 struct WavefrontState {
     // re-laid-out scene
-    DeviceBuffer dNodes, dPrims, dShade, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform;
+    DeviceBuffer dNodes, dPrims, dShade, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform, dUp;
     WideScene scene{};
     uint32_t maxDepth = 0;
     // path state
@@ -181,6 +181,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     WCU(wf_upload(c, w->dShadeE, host.emis.shade));
     WCU(wf_upload(c, w->dXforms, host.xforms));
     WCU(wf_upload(c, w->dObjXform, host.objXform));
+    WCU(wf_upload(c, w->dUp, host.up));
     WCU(cudaStreamSynchronize(c->stream));        // `host` is a local
     WideScene& s = w->scene;
     s.all = {(const Bvh8Node*)w->dNodes.p, (const PrimRecord*)w->dPrims.p, (uint32_t)host.all.nodes.size(), (uint32_t)host.all.prims.size()};
@@ -189,6 +190,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
     s.xforms = (const Xform*)w->dXforms.p;
     s.objXform = (const uint32_t*)w->dObjXform.p;
+    s.up = (const UpNode*)w->dUp.p;
     s.spheres = c->ref.spheres; s.materials = c->ref.materials;
     s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
@@ -202,7 +204,7 @@ void wavefront_invalidate_frame_state(b200pt_ctx*) {}
 void wavefront_destroy(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w) return;
-    DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform,
+    DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
                            &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dCounts, &w->dRayCounters};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);

@@ -36,7 +36,7 @@ void* emu_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     v.all = {s->wide.all.nodes.data(), s->wide.all.prims.data(), (uint32_t)s->wide.all.nodes.size(), (uint32_t)s->wide.all.prims.size()};
     v.emis = {s->wide.emis.nodes.data(), s->wide.emis.prims.data(), (uint32_t)s->wide.emis.nodes.size(), (uint32_t)s->wide.emis.prims.size()};
     v.shade = s->wide.all.shade.data(); v.shadeEmis = s->wide.emis.shade.data();
-    v.xforms = s->wide.xforms.data(); v.spheres = s->spheres.data(); v.materials = s->materials.data();
+    v.xforms = s->wide.xforms.data(); v.up = s->wide.up.data(); v.spheres = s->spheres.data(); v.materials = s->materials.data();
     v.objXform = s->wide.objXform.data();
     v.nXforms = (uint32_t)s->wide.xforms.size(); v.nSpheres = nS; v.nMaterials = nM; v.nObjects = nO;
     v.anyEmissive = s->wide.anyEmissive ? 1u : 0u;

@@ -97,3 +97,17 @@ def test_frame_stride_split_equals_whole(cornell_blobs):
     a, _ = sc.render_frames(pc, W, H, 0, 4, stride=2)
     b, _ = sc.render_frames(pc, W, H, 1, 4, stride=2)
     assert np.allclose(a + b, whole, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("frame", [0, 9])
+def test_reference_box_culling_is_reproduced(cornell_blobs, frame):
+    # Regression: at 512x512 frames 0 and 9 contain rays that graze a box of the reference's BVH2 (the light
+    # quad's flat leaf box at the rim of the ceiling hole): the reference's slab test rejects the leaf, so the
+    # reference never tests a triangle the ray geometrically hits. The wide-BVH traversal must return the
+    # reference's answer (pt_traverse.h: ref_reachable), or a handful of bright paths differ.
+    W = H = 512
+    pc = ob.default_push_constants(W, H, 10, 9)
+    with ob.math_mode(1):
+        want, _ = ob.OracleScene(cornell_blobs).render_frames(pc, W, H, frame, 1)
+    got, _ = emu.EmuScene(cornell_blobs).render_frames(pc, W, H, frame, 1, slots=1)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
