@@ -32,7 +32,28 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+HOST_DIR = os.path.join(HERE, "host")
+HOST_LIB = os.path.join(HERE, "libb200pt_host.so")
+HOST_SOURCES = ["scene_builder.cpp", "host_api.cpp"]
+
+
+def build_host(force=False, verbose=False):
+    """Host-side scene builder (plain C++, no CUDA): libb200pt_host.so."""
+    srcs = [os.path.join(HOST_DIR, s) for s in HOST_SOURCES]
+    deps = srcs + [os.path.join(HOST_DIR, "scene_builder.h"), os.path.join(CSRC, "pt_layout.h")]
+    if not force and os.path.exists(HOST_LIB) and all(os.path.getmtime(d) <= os.path.getmtime(HOST_LIB) for d in deps):
+        return HOST_LIB
+    cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-fno-fast-math", "-shared", "-o", HOST_LIB] + srcs
+    if verbose:
+        print(" ".join(cmd))
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return HOST_LIB
+
+
 def build(force=False, verbose=False, extra=()):
+    build_host(force=force, verbose=verbose)
     if not force and not needs_build():
         return LIB
     env = dict(os.environ)
