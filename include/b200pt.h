@@ -119,7 +119,7 @@ int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const fl
                        void* host_hits48);
 
 /* Options: "pipeline" 0 = reference-layout per-pixel kernel, 1 = wavefront (default for
- * render_frames/trace_batch); "frames_in_flight" (1..64). Unknown keys fail. */
+ * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1. Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
 
@@ -127,6 +127,10 @@ int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
  * [0] kernel launches, [1] paths traced, [2] extension rays, [3] shadow/pdf rays, [4] reserved ... */
 int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
 int b200pt_reset_counters(b200pt_ctx* ctx);
+/* With option "profile_stages" = 1 the wavefront records a CUDA event between consecutive launches; this
+ * returns the accumulated device milliseconds and launch counts per stage
+ * (0 generate, 1 extend, 2 shade, 3 connect, 4 accumulate) and optionally resets them. */
+int b200pt_read_stage_times(b200pt_ctx* ctx, double* ms5, uint64_t* launches5, int reset);
 /* Device time of the last render call in milliseconds (CUDA events on the context's stream). */
 int b200pt_last_render_ms(b200pt_ctx* ctx, float* ms);
 

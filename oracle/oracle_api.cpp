@@ -64,6 +64,18 @@ int orc_render_frames(void* scene, const void* pc208, int W, int H, uint32_t fir
     return 0;
 }
 
+// as orc_render_frames; work16 = 8 counters over all rays followed by 8 over extension rays only
+int orc_render_frames2(void* scene, const void* pc208, int W, int H, uint32_t first, uint32_t n, float* accum,
+                       uint64_t* work16, int threads) {
+    ol::PushConstants pc;
+    std::memcpy(&pc, pc208, sizeof(pc));
+    Work w, e;
+    render_frames(*(Scene*)scene, pc, W, H, first, n, accum, &w, threads, &e);
+    work_out(w, work16);
+    work_out(e, work16 ? work16 + 8 : nullptr);
+    return 0;
+}
+
 int orc_trace_batch(void* scene, const void* pc208, const float* rays, uint64_t n, void* hits48, uint64_t* work8,
                     int threads) {
     ol::PushConstants pc;

@@ -57,7 +57,8 @@ struct BxDFResult {     // raytrace.comp:112-118
 struct Ctx {
     const Scene& sc;
     const ol::PushConstants& pc;
-    Work work;
+    Work work;      // all rays
+    Work ext;       // extension rays only (the calls from trace(), raytrace.comp:493): roofline of the extend stage
 };
 
 vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
@@ -178,6 +179,7 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
     closestHit.didHit = false;
     closestHit.dst = 99999999.f;
     const ol::RayTracerData& traceData = cx.pc.rayTraceParams;
+    const Work before = cx.work;
     cx.work.n_ray++;
 
     for (uint32_t i = 0; i < traceData.sphereCount; i++) {
@@ -250,6 +252,11 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
     }
 
     if (closestHit.didHit) cx.work.n_hit++;
+    if (stats) {
+        cx.ext.n_box += cx.work.n_box - before.n_box; cx.ext.n_tri += cx.work.n_tri - before.n_tri;
+        cx.ext.n_obj += cx.work.n_obj - before.n_obj; cx.ext.n_sph += cx.work.n_sph - before.n_sph;
+        cx.ext.n_hit += cx.work.n_hit - before.n_hit; cx.ext.n_ray += 1;
+    }
     return closestHit;
 }
 
@@ -505,7 +512,7 @@ void render_dispatch(const Scene& sc, const ol::PushConstants& pc, int W, int H,
 #endif
 #pragma omp parallel
     {
-        Ctx cx{sc, pc, Work()};
+        Ctx cx{sc, pc, Work(), Work()};
 #pragma omp for schedule(dynamic, 1)
         for (int y = 0; y < H; ++y) {
             for (int x = 0; x < W; ++x) {
@@ -554,8 +561,8 @@ void render_dispatch(const Scene& sc, const ol::PushConstants& pc, int W, int H,
 }
 
 void render_frames(const Scene& sc, const ol::PushConstants& pc_in, int W, int H, uint32_t first, uint32_t n,
-                   float* accum, Work* work, int threads) {
-    Work total;
+                   float* accum, Work* work, int threads, Work* workExt) {
+    Work total, totalExt;
 #ifdef _OPENMP
     if (threads > 0) omp_set_num_threads(threads);
 #endif
@@ -564,7 +571,7 @@ void render_frames(const Scene& sc, const ol::PushConstants& pc_in, int W, int H
         pc.frameCount = f;
 #pragma omp parallel
         {
-            Ctx cx{sc, pc, Work()};
+            Ctx cx{sc, pc, Work(), Work()};
 #pragma omp for schedule(dynamic, 1)
             for (int y = 0; y < H; ++y) {
                 for (int x = 0; x < W; ++x) {
@@ -576,10 +583,11 @@ void render_frames(const Scene& sc, const ol::PushConstants& pc_in, int W, int H
                 }
             }
 #pragma omp critical
-            total.add(cx.work);
+            { total.add(cx.work); totalExt.add(cx.ext); }
         }
     }
     if (work) work->add(total);
+    if (workExt) workExt->add(totalExt);
 }
 
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out, Work* work,
@@ -590,7 +598,7 @@ void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays
 #endif
 #pragma omp parallel
     {
-        Ctx cx{sc, pc, Work()};
+        Ctx cx{sc, pc, Work(), Work()};
 #pragma omp for schedule(dynamic, 256)
         for (long long i = 0; i < (long long)n; ++i) {
             Ray r;

@@ -66,7 +66,7 @@ void render_dispatch(const Scene& sc, const ol::PushConstants& pc, int W, int H,
 // Throughput form: frames first..first+n-1 with frameCount=f; accum.rgb += outColor_f
 // (non-finite outColor contributes magenta, mirroring raytrace.comp:579-581); accum.a += 1.
 void render_frames(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t first, uint32_t n,
-                   float* accum, Work* work, int threads);
+                   float* accum, Work* work, int threads, Work* workExt = nullptr);
 
 // calculateIntersections (raytrace.comp:276-353) on caller-supplied rays (8 floats each:
 // origin.xyz, pad, dir.xyz, pad).

@@ -26,7 +26,8 @@ EXPORTS = (
     "b200pt_update_objects b200pt_upload_texture b200pt_render b200pt_render_frames b200pt_render_frames_rows "
     "b200pt_clear b200pt_read_accum_f32 b200pt_read_image_f32 b200pt_write_image_f32 b200pt_read_rgba8 "
     "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch "
-    "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_last_render_ms").split()
+    "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_read_stage_times "
+    "b200pt_last_render_ms").split()
 
 
 class BackendError(RuntimeError):
@@ -73,6 +74,7 @@ def load_library(path=None):
     L.b200pt_get_option.argtypes = [vp, C.c_char_p, C.POINTER(i64)]
     L.b200pt_read_counters.argtypes = [vp, vp]
     L.b200pt_reset_counters.argtypes = [vp]
+    L.b200pt_read_stage_times.argtypes = [vp, vp, vp, i32]
     L.b200pt_last_render_ms.argtypes = [vp, C.POINTER(C.c_float)]
     if path is None:
         _lib = L
@@ -212,6 +214,15 @@ class ComputePass:
         c = np.zeros(16, np.uint64)
         self._check(self.L.b200pt_read_counters(self.h, _ptr(c)), "b200pt_read_counters")
         return dict(launches=int(c[0]), paths=int(c[1]), extension_rays=int(c[2]), shadow_rays=int(c[3]))
+
+    STAGES = ("generate", "extend", "shade", "connect", "accumulate")
+
+    def stage_times(self, reset=False):
+        """{stage: (device ms, launches)} accumulated while option profile_stages = 1."""
+        ms = np.zeros(5, np.float64)
+        n = np.zeros(5, np.uint64)
+        self._check(self.L.b200pt_read_stage_times(self.h, _ptr(ms), _ptr(n), int(reset)), "b200pt_read_stage_times")
+        return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(self.STAGES)}
 
     def reset_counters(self):
         self._check(self.L.b200pt_reset_counters(self.h), "b200pt_reset_counters")

@@ -379,6 +379,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     std::string k(key);
     if (k == "pipeline") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "pipeline must be 0 or 1"); c->pipeline = (int)v; return 0; }
     if (k == "frames_in_flight") { if (v < 1 || v > 64) return fail(c, B200PT_ERR_ARG, "frames_in_flight must be 1..64"); c->framesInFlight = (int)v; return 0; }
+    if (k == "profile_stages") { c->profileStages = v != 0; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
@@ -386,6 +387,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     std::string k(key);
     if (k == "pipeline") { *v = c->pipeline; return 0; }
     if (k == "frames_in_flight") { *v = c->framesInFlight; return 0; }
+    if (k == "profile_stages") { *v = c->profileStages; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 
@@ -403,6 +405,14 @@ int b200pt_reset_counters(b200pt_ctx* c) {
     CU(c, cudaStreamSynchronize(c->stream));
     wavefront_fold_counters(c);
     std::memset(c->counters, 0, sizeof(c->counters));
+    return 0;
+}
+int b200pt_read_stage_times(b200pt_ctx* c, double* ms5, uint64_t* launches5, int reset) {
+    if (!c || !ms5 || !launches5) return B200PT_ERR_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->stream));
+    wavefront_resolve_stage_times(c);
+    wavefront_stage_times(c, ms5, launches5, reset != 0);
     return 0;
 }
 int b200pt_last_render_ms(b200pt_ctx* c, float* ms) {

@@ -53,6 +53,7 @@ struct b200pt_ctx {
     // options
     int pipeline = 1;
     int framesInFlight = 4;
+    int profileStages = 0;
 
     // counters (host side; device-side ray counters are folded in by the wavefront)
     uint64_t counters[16] = {0};

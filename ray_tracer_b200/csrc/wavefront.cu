@@ -27,7 +27,48 @@ struct WavefrontState {
     size_t capacity = 0;
     uint32_t countSlots = 0;
     int smCount = 148;
+    // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
+    std::vector<cudaEvent_t> events;
+    std::vector<int> eventStage;      // stage of the launch that FOLLOWS event i (-1: batch end)
+    size_t eventsUsed = 0;
+    double stageMs[5] = {0, 0, 0, 0, 0};
+    uint64_t stageLaunches[5] = {0, 0, 0, 0, 0};
 };
+
+enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4 };
+
+static void wf_mark(b200pt_ctx* c, int stage) {
+    WavefrontState* w = c->wf;
+    if (!c->profileStages) return;
+    if (w->eventsUsed == w->events.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        w->events.push_back(e);
+        w->eventStage.push_back(-1);
+    }
+    w->eventStage[w->eventsUsed] = stage;
+    cudaEventRecord(w->events[w->eventsUsed++], c->stream);
+}
+
+// stream must be idle: turns the recorded events into per-stage totals
+void wavefront_resolve_stage_times(b200pt_ctx* c) {
+    WavefrontState* w = c->wf;
+    if (!w) return;
+    for (size_t i = 0; i + 1 < w->eventsUsed; ++i) {
+        int st = w->eventStage[i];
+        if (st < 0) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, w->events[i], w->events[i + 1]) == cudaSuccess) { w->stageMs[st] += ms; w->stageLaunches[st]++; }
+    }
+    w->eventsUsed = 0;
+}
+void wavefront_stage_times(b200pt_ctx* c, double* ms5, uint64_t* launches5, bool reset) {
+    WavefrontState* w = c->wf;
+    for (int i = 0; i < 5; ++i) {
+        ms5[i] = w ? w->stageMs[i] : 0.0; launches5[i] = w ? w->stageLaunches[i] : 0;
+        if (w && reset) { w->stageMs[i] = 0.0; w->stageLaunches[i] = 0; }
+    }
+}
 
 #define WF_THREADS 128
 
@@ -208,6 +249,7 @@ void wavefront_destroy(b200pt_ctx* c) {
                            &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dCounts, &w->dRayCounters};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
+    for (cudaEvent_t e : w->events) cudaEventDestroy(e);
     delete w;
     c->wf = nullptr;
 }
@@ -269,18 +311,25 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 2 * 4, c->stream));
         uint32_t* qa = (uint32_t*)w->dQueue[0].p;
         uint32_t* qb = (uint32_t*)w->dQueue[1].p;
+        if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
+        wf_mark(c, ST_GENERATE);
         k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount);
         for (uint32_t j = 0; j < nB; ++j) {
+            wf_mark(c, ST_EXTEND);
             k_extend<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j);
+            wf_mark(c, ST_SHADE);
             k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
+            if (j + 1 < nB) wf_mark(c, ST_CONNECT);
             if (j + 1 < nB)
                 k_connect<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j);
             std::swap(qa, qb);
             c->counters[0] += (j + 1 < nB) ? 3 : 2;
         }
+        wf_mark(c, ST_ACCUMULATE);
         k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
         k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
+        wf_mark(c, -1);
         c->counters[0] += 3;
         c->counters[1] += P.nPaths;
         WCU(cudaGetLastError());

@@ -41,6 +41,7 @@ def lib():
         L.orc_scene_destroy.argtypes = [vp]
         L.orc_render_dispatch.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, i32]
         L.orc_render_frames.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
+        L.orc_render_frames2.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
         L.orc_trace_batch.argtypes = [vp, vp, vp, u64, vp, vp, i32]
         L.orc_random.restype = f32
         L.orc_random.argtypes = [C.POINTER(u32)]
@@ -121,6 +122,14 @@ class OracleScene:
         work = np.zeros(8, np.uint64)
         lib().orc_render_frames(self.h, _ptr(pcb), W, H, first, n, _ptr(accum), _ptr(work), threads)
         return accum, dict(zip(WORK_FIELDS, work.tolist()))
+
+    def render_frames_work(self, pc, W, H, first, n, threads=0):
+        """render_frames returning (accum, work over all rays, work over extension rays only)."""
+        pcb = self._pc(pc)
+        accum = np.zeros((H, W, 4), np.float32)
+        work = np.zeros(16, np.uint64)
+        lib().orc_render_frames2(self.h, _ptr(pcb), W, H, first, n, _ptr(accum), _ptr(work), threads)
+        return accum, dict(zip(WORK_FIELDS, work[:8].tolist())), dict(zip(WORK_FIELDS, work[8:].tolist()))
 
     def trace_batch(self, pc, rays, threads=0):
         pcb = self._pc(pc)
