@@ -170,8 +170,10 @@ class ComputePass:
         return v.value
 
     # ---- outputs
-    def read_accum(self):
-        a = np.empty((self.height, self.width, 4), np.float32)
+    def read_accum(self, out=None):
+        """W x H float4 accumulator -> host. `out`: caller-owned float32 array of that shape (e.g. pinned memory)."""
+        a = np.empty((self.height, self.width, 4), np.float32) if out is None else out
+        assert a.dtype == np.float32 and a.shape == (self.height, self.width, 4) and a.flags["C_CONTIGUOUS"]
         self._check(self.L.b200pt_read_accum_f32(self.h, _ptr(a)), "b200pt_read_accum_f32")
         return a
 
