@@ -325,6 +325,13 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             r.p0x = te.p0.x; r.p0y = te.p0.y; r.p0z = te.p0.z; r.objectIndex = (uint32_t)o;
             r.e1x = te.e1.x; r.e1y = te.e1.y; r.e1z = te.e1.z;
             r.triIndexFlags = (t & PT_PRIM_TRIMASK) | (tr.frontOnly ? PT_PRIM_FRONTONLY : 0u) | (em ? PT_PRIM_EMISSIVE : 0u);
+            if (leafOf[t] != 0xffffffffu) {
+                const UpNode& lf = out.up[leafOf[t]];
+                if (lf.minX == lf.maxX) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_X;
+                if (lf.minY == lf.maxY) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Y;
+                if (lf.minZ == lf.maxZ) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Z;
+                if (lf.parent == 0xffffffffu) r.triIndexFlags |= PT_PRIM_LEAF_IS_ROOT;
+            }
             r.e2x = te.e2.x; r.e2y = te.e2.y; r.e2z = te.e2.z; r.xformId = out.objXform[o];
             r.nx = te.n.x; r.ny = te.n.y; r.nz = te.n.z; r.leafNode = leafOf[t];
             ShadeRecord s;
@@ -353,7 +360,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     }
     bvh8_build(boxes, inst, prim, shade, out.all);
     bvh8_build(boxesE, instE, primE, shadeE, out.emis);
-    if (out.all.maxDepth + 2 > PT_BVH8_STACK || out.emis.maxDepth + 2 > PT_BVH8_STACK) return "wide BVH deeper than the traversal stack";
+    if (out.all.maxDepth > PT_BVH8_MAX_DEPTH || out.emis.maxDepth > PT_BVH8_MAX_DEPTH) return "wide BVH deeper than the traversal stack";
     return nullptr;
 }
 

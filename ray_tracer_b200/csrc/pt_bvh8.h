@@ -27,14 +27,18 @@ static_assert(sizeof(Bvh8Node) == 80, "Bvh8Node");
 // (raytrace.comp:229-232), evaluated once in object space.
 struct PrimRecord {            // 64 B
     float p0x, p0y, p0z; uint32_t objectIndex;
-    float e1x, e1y, e1z; uint32_t triIndexFlags;   // bit31 frontOnly, bit30 emissive material, low 30 bits triangle index
+    float e1x, e1y, e1z; uint32_t triIndexFlags;   // bit31 frontOnly, bit30 emissive material, bits 29..26 leaf flags, low 26 bits triangle index
     float e2x, e2y, e2z; uint32_t xformId;
     float nx, ny, nz;    uint32_t leafNode;        // reference BVH2 leaf holding this triangle (index into UpNode[])
 };
 static_assert(sizeof(PrimRecord) == 64, "PrimRecord");
 #define PT_PRIM_FRONTONLY 0x80000000u
 #define PT_PRIM_EMISSIVE 0x40000000u
-#define PT_PRIM_TRIMASK 0x3fffffffu
+#define PT_PRIM_LEAF_FLAT_X 0x20000000u    /* the reference BVH2 leaf holding the triangle has minX == maxX */
+#define PT_PRIM_LEAF_FLAT_Y 0x10000000u
+#define PT_PRIM_LEAF_FLAT_Z 0x08000000u
+#define PT_PRIM_LEAF_IS_ROOT 0x04000000u   /* that leaf is the object's root: its box is never tested */
+#define PT_PRIM_TRIMASK 0x03ffffffu
 
 // Shading record of the same triangle (vertex normals; raytrace.comp:259)
 struct ShadeRecord {           // 48 B
@@ -79,6 +83,11 @@ struct WideScene {
     uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
 };
 
-#define PT_BVH8_STACK 40
+// Traversal stack: at most one sibling group per level of the wide tree (<= PT_BVH8_MAX_DEPTH,
+// checked at upload) plus postponed triangle groups, which are only pushed while the stack is
+// below PT_BVH8_POSTPONE_LIMIT entries: LIMIT + 1 + MAX_DEPTH < STACK.
+#define PT_BVH8_STACK 48
+#define PT_BVH8_MAX_DEPTH 30
+#define PT_BVH8_POSTPONE_LIMIT 16
 
 }  // namespace pt

@@ -35,7 +35,6 @@ PT_HD BoxRay make_box_ray(const Ray& r) {
     return b;
 }
 
-PT_HD uint32_t ld_u32(const uint8_t* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
 PT_HD int highest_bit(uint32_t x) {
 #if defined(__CUDA_ARCH__)
     return 31 - __clz(x);
@@ -51,30 +50,56 @@ PT_HD int popcount32(uint32_t x) {
 #endif
 }
 
+// A node held in registers: the 80 bytes as twenty 32-bit words (five 16-byte loads).
+//  w0..2 px,py,pz | w3 ex,ey,ez,imask | w4 childBase | w5 primBase | w6,7 meta[8]
+//  w8,9 qlox | w10,11 qloy | w12,13 qloz | w14,15 qhix | w16,17 qhiy | w18,19 qhiz
+struct NodeWords { uint32_t w[20]; };
+PT_HD NodeWords load_node(const Bvh8Node* nodes, uint32_t idx) {
+    NodeWords n;
+#if defined(__CUDA_ARCH__)
+    const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);
+    uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3), e = __ldg(p + 4);
+    n.w[0] = a.x; n.w[1] = a.y; n.w[2] = a.z; n.w[3] = a.w; n.w[4] = b.x; n.w[5] = b.y; n.w[6] = b.z; n.w[7] = b.w;
+    n.w[8] = c.x; n.w[9] = c.y; n.w[10] = c.z; n.w[11] = c.w; n.w[12] = d.x; n.w[13] = d.y; n.w[14] = d.z; n.w[15] = d.w;
+    n.w[16] = e.x; n.w[17] = e.y; n.w[18] = e.z; n.w[19] = e.w;
+#else
+    memcpy(n.w, nodes + idx, sizeof(Bvh8Node));
+#endif
+    return n;
+}
+// float(byte k of word), exact. Device: the byte is dropped into the mantissa of 2^23 (one PRMT) and
+// 2^23 is subtracted (one FADD) — keeps the 48 conversions per node off the quarter-rate I2F pipe.
+PT_HD float byte_to_float(uint32_t word, int k) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + (uint32_t)k)) - 8388608.f;
+#else
+    return (float)((word >> (8 * k)) & 0xffu);
+#endif
+}
+
 // Slab-test the 8 children of a node; returns hit bits: inner children in bits 24..31 ordered by
 // traversal priority for this ray's octant, leaf triangles in bits 0..23 (offset from primBase).
-PT_HD uint32_t bvh8_node_hits(const Bvh8Node& n, const BoxRay& br, float tmax) {
-    float sx = as_float((uint32_t)n.ex << 23) * br.rd.x;
-    float sy = as_float((uint32_t)n.ey << 23) * br.rd.y;
-    float sz = as_float((uint32_t)n.ez << 23) * br.rd.z;
-    float ox = (n.px - br.o.x) * br.rd.x;
-    float oy = (n.py - br.o.y) * br.rd.y;
-    float oz = (n.pz - br.o.z) * br.rd.z;
-    const uint8_t* nx = br.rd.x < 0.f ? n.qhix : n.qlox;
-    const uint8_t* fx = br.rd.x < 0.f ? n.qlox : n.qhix;
-    const uint8_t* ny = br.rd.y < 0.f ? n.qhiy : n.qloy;
-    const uint8_t* fy = br.rd.y < 0.f ? n.qloy : n.qhiy;
-    const uint8_t* nz = br.rd.z < 0.f ? n.qhiz : n.qloz;
-    const uint8_t* fz = br.rd.z < 0.f ? n.qloz : n.qhiz;
-    uint32_t oct = br.octinv4 & 7u;
+PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) {
+    float sx = as_float((n.w[3] & 0xffu) << 23) * br.rd.x;
+    float sy = as_float(((n.w[3] >> 8) & 0xffu) << 23) * br.rd.y;
+    float sz = as_float(((n.w[3] >> 16) & 0xffu) << 23) * br.rd.z;
+    float ox = (as_float(n.w[0]) - br.o.x) * br.rd.x;
+    float oy = (as_float(n.w[1]) - br.o.y) * br.rd.y;
+    float oz = (as_float(n.w[2]) - br.o.z) * br.rd.z;
+    const bool negx = br.rd.x < 0.f, negy = br.rd.y < 0.f, negz = br.rd.z < 0.f;
+    const uint32_t nx[2] = {negx ? n.w[14] : n.w[8], negx ? n.w[15] : n.w[9]}, fx[2] = {negx ? n.w[8] : n.w[14], negx ? n.w[9] : n.w[15]};
+    const uint32_t ny[2] = {negy ? n.w[16] : n.w[10], negy ? n.w[17] : n.w[11]}, fy[2] = {negy ? n.w[10] : n.w[16], negy ? n.w[11] : n.w[17]};
+    const uint32_t nz[2] = {negz ? n.w[18] : n.w[12], negz ? n.w[19] : n.w[13]}, fz[2] = {negz ? n.w[12] : n.w[18], negz ? n.w[13] : n.w[19]};
+    const uint32_t oct = br.octinv4 & 7u;
     uint32_t hits = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        uint32_t meta = n.meta[i];
+        const int h = i >> 2, k = i & 3;
+        uint32_t meta = (n.w[6 + h] >> (8 * k)) & 0xffu;
         if (meta == 0) continue;
-        float t0x = pt_fma((float)nx[i], sx, ox), t1x = pt_fma((float)fx[i], sx, ox);
-        float t0y = pt_fma((float)ny[i], sy, oy), t1y = pt_fma((float)fy[i], sy, oy);
-        float t0z = pt_fma((float)nz[i], sz, oz), t1z = pt_fma((float)fz[i], sz, oz);
+        float t0x = pt_fma(byte_to_float(nx[h], k), sx, ox), t1x = pt_fma(byte_to_float(fx[h], k), sx, ox);
+        float t0y = pt_fma(byte_to_float(ny[h], k), sy, oy), t1y = pt_fma(byte_to_float(fy[h], k), sy, oy);
+        float t0z = pt_fma(byte_to_float(nz[h], k), sz, oz), t1z = pt_fma(byte_to_float(fz[h], k), sz, oz);
         float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
         float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
         if (tn <= tf) {
@@ -86,36 +111,66 @@ PT_HD uint32_t bvh8_node_hits(const Bvh8Node& n, const BoxRay& br, float tmax) {
     return hits;
 }
 
-struct ObjRayCache { uint32_t xform; Ray r; v3 inv; };
+struct ObjRayCache { uint32_t xform; Ray r; };
 
 PT_HD const Ray& object_ray(ObjRayCache& c, const Xform* xforms, uint32_t xformId, const Ray& world) {
     if (c.xform != xformId) {
         const float* Minv = xforms[xformId].Minv;
         c.r.d = mul_dir(Minv, world.d);       // raytrace.comp:292 (direction not renormalised: t stays world-parametric)
         c.r.o = mul_point(Minv, world.o);     // raytrace.comp:293
-        c.inv = mk3(1.f / c.r.d.x, 1.f / c.r.d.y, 1.f / c.r.d.z);   // raytrace.comp:294
         c.xform = xformId;
     }
     return c.r;
 }
 
+PT_HD PrimRecord load_prim(const PrimRecord* prims, uint32_t i) {
+#if defined(__CUDA_ARCH__)
+    const uint4* q = reinterpret_cast<const uint4*>(prims + i);
+    uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    PrimRecord p;
+    p.p0x = __uint_as_float(a.x); p.p0y = __uint_as_float(a.y); p.p0z = __uint_as_float(a.z); p.objectIndex = a.w;
+    p.e1x = __uint_as_float(b.x); p.e1y = __uint_as_float(b.y); p.e1z = __uint_as_float(b.z); p.triIndexFlags = b.w;
+    p.e2x = __uint_as_float(c.x); p.e2y = __uint_as_float(c.y); p.e2z = __uint_as_float(c.z); p.xformId = c.w;
+    p.nx = __uint_as_float(d.x); p.ny = __uint_as_float(d.y); p.nz = __uint_as_float(d.z); p.leafNode = d.w;
+    return p;
+#else
+    return prims[i];
+#endif
+}
+
 // Would the reference have tested the triangle in BVH2 leaf `leaf`? It does iff boxIntersection()
 // (raytrace.comp:263-274) reports a hit for every node from the leaf up to, not including, the
-// object's root (:324-348; the root's own box is never tested, :301-307). The walk stops early once
-// the object-space hit point is inside a box with a margin far above the slab test's rounding
-// error: every ancestor contains that box, so their tests pass a fortiori. Axes on which the leaf is
-// flat (axis-aligned triangles) are exempt from the margin: there tMin == tMax is the plane distance
-// itself and rounding is monotone in the box coordinate.
-PT_HD bool ref_reachable(const UpNode* __restrict__ up, uint32_t leaf, const ObjRayCache& c, float dst) {
-    UpNode n = up[leaf];
-    if (n.parent == 0xffffffffu) return true;
-    v3 h = c.r.o + c.r.d * dst;
-    float m = 2e-5f * (fmaxf(fmaxf(fabsf(h.x), fabsf(h.y)), fabsf(h.z)) + fmaxf(fmaxf(fabsf(c.r.o.x), fabsf(c.r.o.y)), fabsf(c.r.o.z))) + 1e-30f;
-    v3 dh = h - c.r.o;
-    bool farEnough = fmaxf(fmaxf(fabsf(dh.x), fabsf(dh.y)), fabsf(dh.z)) > m;
-    bool flatX = n.minX == n.maxX, flatY = n.minY == n.maxY, flatZ = n.minZ == n.maxZ;
+// object's root (:324-348; the root's own box is never tested, :301-307). A box that contains the
+// object-space hit point h with a margin m far above the slab test's rounding error passes, and so
+// does every box around it.
+//   quick accept (no memory access): the triangle's own bounding box, rebuilt from the record
+//     (p0, p0+e1, p0+e2), contains h with margin m on every axis on which the LEAF is not flat
+//     (flags precomputed at upload). The leaf box and all its ancestors contain that box.
+//   otherwise: walk leaf -> root re-running the reference's slab test, stopping at the first box
+//     that contains h with the margin. Axes on which the leaf is flat (axis-aligned triangles) are
+//     exempt from the margin: there tMin == tMax is the plane distance itself and rounding is
+//     monotone in the box coordinate.
+PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, const ObjRayCache& c, float dst) {
+    const v3 h = c.r.o + c.r.d * dst;
+    const float m = 2e-5f * (fmaxf(fmaxf(fabsf(h.x), fabsf(h.y)), fabsf(h.z)) + fmaxf(fmaxf(fabsf(c.r.o.x), fabsf(c.r.o.y)), fabsf(c.r.o.z))) + 1e-30f;
+    const v3 dh = h - c.r.o;
+    const bool farEnough = fmaxf(fmaxf(fabsf(dh.x), fabsf(dh.y)), fabsf(dh.z)) > m;
+    const bool flatX = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_X) != 0, flatY = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Y) != 0,
+               flatZ = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Z) != 0;
+    if (p.triIndexFlags & PT_PRIM_LEAF_IS_ROOT) return true;
+    if (farEnough) {
+        const float lx = p.p0x + fminf(fminf(p.e1x, p.e2x), 0.f), hx = p.p0x + fmaxf(fmaxf(p.e1x, p.e2x), 0.f);
+        const float ly = p.p0y + fminf(fminf(p.e1y, p.e2y), 0.f), hy = p.p0y + fmaxf(fmaxf(p.e1y, p.e2y), 0.f);
+        const float lz = p.p0z + fminf(fminf(p.e1z, p.e2z), 0.f), hz = p.p0z + fmaxf(fmaxf(p.e1z, p.e2z), 0.f);
+        const bool inX = flatX || (h.x >= lx + m && h.x <= hx - m);
+        const bool inY = flatY || (h.y >= ly + m && h.y <= hy - m);
+        const bool inZ = flatZ || (h.z >= lz + m && h.z <= hz - m);
+        if (inX && inY && inZ) return true;
+    }
+    const v3 inv = mk3(1.f / c.r.d.x, 1.f / c.r.d.y, 1.f / c.r.d.z);   // raytrace.comp:294
+    UpNode n = up[p.leafNode];
     for (;;) {
-        if (box_test_ref(mk3(n.minX, n.minY, n.minZ), mk3(n.maxX, n.maxY, n.maxZ), c.r.o, c.inv) == PT_FAR) return false;
+        if (box_test_ref(mk3(n.minX, n.minY, n.minZ), mk3(n.maxX, n.maxY, n.maxZ), c.r.o, inv) == PT_FAR) return false;
         bool inX = flatX || (h.x >= n.minX + m && h.x <= n.maxX - m);
         bool inY = flatY || (h.y >= n.minY + m && h.y <= n.maxY - m);
         bool inZ = flatZ || (h.z >= n.minZ + m && h.z <= n.maxZ - m);
@@ -132,97 +187,111 @@ PT_HD TriEdges prim_edges(const PrimRecord& p) {
     return t;
 }
 
-// Closest triangle hit strictly closer than hit.dst (the reference's `hitInfo.dst < closestHit.dst`).
-// `key` is the position of the current best hit in the reference's loop order (sphere i -> i, object o
-// -> nSpheres + o; 0xffffffff for none): the reference keeps the FIRST of equal-distance hits.
-PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, Hit& hit, uint32_t& key) {
-    BoxRay br = make_box_ray(ray);
-    ObjRayCache oc; oc.xform = 0xffffffffu;
-    uint32_t oct = br.octinv4 & 7u;
-    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
-    int sp = 0;
-    uint32_t gBase = 0, gBits = 0x80000000u;          // node group: base index | hit bits(31..24) + imask(7..0)
-    for (;;) {
-        uint32_t tBase = 0, tBits = 0;
-        if (gBits & 0xff000000u) {
-            int bit = highest_bit(gBits);
-            gBits &= ~(1u << bit);
-            uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
-            uint32_t rel = (uint32_t)popcount32(gBits & 0xffu & ~(0xffffffffu << slot));
-            uint32_t nodeIdx = gBase + rel;
-            if (gBits & 0xff000000u) { stackBase[sp] = gBase; stackBits[sp] = gBits; sp++; }
-            const Bvh8Node n = bvh.nodes[nodeIdx];
-            uint32_t h = bvh8_node_hits(n, br, hit.dst);
-            gBase = n.childBase; gBits = (h & 0xff000000u) | n.imask;
-            tBase = n.primBase; tBits = h & 0x00ffffffu;
-        } else {
-            gBits = 0;
-        }
-        while (tBits) {
-            int k = highest_bit(tBits);
-            tBits &= ~(1u << k);
-            uint32_t pi = tBase + (uint32_t)k;
-            const PrimRecord p = bvh.prims[pi];
-            if (p.objectIndex >= objectCount) continue;
-            const Ray& tr = object_ray(oc, xforms, p.xformId, ray);
-            float dst, u, v; bool front;
-            if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
-                (dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key)) && ref_reachable(up, p.leafNode, oc, dst)) {
-                hit.dst = dst; hit.u = u; hit.v = v;
-                hit.id = pi | (front ? PT_HIT_FRONT : 0u);
-                key = nSpheres + p.objectIndex;
-            }
-        }
-        if ((gBits & 0xff000000u) == 0) {
-            if (sp == 0) break;
-            sp--; gBase = stackBase[sp]; gBits = stackBits[sp];
-        }
-    }
+// ---- traversal as per-ray steps ---------------------------------------------------------------
+// The state of one ray's walk through the wide BVH. Work items are "groups": a node group
+// (base = first inner child, bits 31..24 = children still to visit in priority order, bits 7..0 =
+// imask) or a triangle group (base = first record, bits 23..0 = records still to test). The
+// stack holds groups of either kind (a triangle group has no bit above 23). Steps are separate so
+// that a warp can run one KIND of step for all its lanes at a time (wavefront.cu: the persistent
+// kernels vote on which) — and the same functions, looped per ray, are the host emulation.
+struct Trav {
+    Ray ray;            // world space
+    BoxRay br;
+    ObjRayCache oc;
+    uint32_t gBase, gBits;      // current node group
+    uint32_t tBase, tBits;      // current triangle group
+    int sp;
+};
+PT_HD void trav_begin(Trav& t, const Ray& ray) {
+    t.ray = ray; t.br = make_box_ray(ray); t.oc.xform = 0xffffffffu;
+    t.gBase = 0; t.gBits = 0x80000000u;               // the root as the only child of a virtual group
+    t.tBase = 0; t.tBits = 0; t.sp = 0;
+}
+PT_HD bool trav_has_node(const Trav& t) { return (t.gBits & 0xff000000u) != 0; }
+PT_HD bool trav_has_tri(const Trav& t) { return t.tBits != 0; }
+// Nothing in hand: take the next group from the stack. Returns false when the walk is over.
+PT_HD bool trav_pop(Trav& t, const uint32_t* stackBase, const uint32_t* stackBits) {
+    if (t.sp == 0) return false;
+    t.sp--;
+    uint32_t b = stackBase[t.sp], bits = stackBits[t.sp];
+    if (bits & 0xff000000u) { t.gBase = b; t.gBits = bits; }
+    else { t.tBase = b; t.tBits = bits; t.gBits = 0; }
+    return true;
+}
+// Visit the nearest pending child of the current node group (precondition: trav_has_node).
+// A triangle group still in hand is postponed: it goes on top of the stack, so it is the next
+// thing popped once this subtree is done.
+PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, uint32_t* stackBase, uint32_t* stackBits, float tmax) {
+    const uint32_t oct = t.br.octinv4 & 7u;
+    int bit = highest_bit(t.gBits);
+    t.gBits &= ~(1u << bit);
+    uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
+    uint32_t rel = (uint32_t)popcount32(t.gBits & 0xffu & ~(0xffffffffu << slot));
+    uint32_t nodeIdx = t.gBase + rel;
+    if (t.gBits & 0xff000000u) { stackBase[t.sp] = t.gBase; stackBits[t.sp] = t.gBits; t.sp++; }
+    if (t.tBits) { stackBase[t.sp] = t.tBase; stackBits[t.sp] = t.tBits; t.sp++; }
+    const NodeWords n = load_node(bvh.nodes, nodeIdx);
+    uint32_t h = bvh8_node_hits(n, t.br, tmax);
+    t.gBase = n.w[4]; t.gBits = (h & 0xff000000u) | (n.w[3] >> 24);
+    t.tBase = n.w[5]; t.tBits = h & 0x00ffffffu;
 }
 
-// Is there a NON-emissive triangle hit that the reference's closest-hit search would have
-// preferred to an emissive hit at (tE, keyE)? (strictly closer, or equal distance and earlier in
-// the reference's loop order)
+// Test the next triangle of the current group for a closest hit strictly closer than hit.dst (the
+// reference's `hitInfo.dst < closestHit.dst`). `key` is the position of the current best hit in the
+// reference's loop order (sphere i -> i, object o -> nSpheres + o; 0xffffffff for none): the
+// reference keeps the FIRST of equal-distance hits.
+PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
+                                 Trav& t, Hit& hit, uint32_t& key) {
+    int k = highest_bit(t.tBits);
+    t.tBits &= ~(1u << k);
+    uint32_t pi = t.tBase + (uint32_t)k;
+    const PrimRecord p = load_prim(bvh.prims, pi);
+    if (p.objectIndex >= objectCount) return;
+    const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
+    float dst, u, v; bool front;
+    if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
+        (dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key)) && ref_reachable(up, p, t.oc, dst)) {
+        hit.dst = dst; hit.u = u; hit.v = v;
+        hit.id = pi | (front ? PT_HIT_FRONT : 0u);
+        key = nSpheres + p.objectIndex;
+    }
+}
+// Occlusion form: is the next triangle a NON-emissive hit that the reference's closest-hit search
+// would have preferred to an emissive hit at (tE, keyE)? (strictly closer, or equal distance and
+// earlier in the reference's loop order)
+PT_HD bool trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
+                                  Trav& t, float tE, uint32_t keyE) {
+    int k = highest_bit(t.tBits);
+    t.tBits &= ~(1u << k);
+    const PrimRecord p = load_prim(bvh.prims, t.tBase + (uint32_t)k);
+    if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) return false;
+    const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
+    float dst, u, v; bool front;
+    return tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
+           (dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE)) && ref_reachable(up, p, t.oc, dst);
+}
+
+// Per-ray loops over the steps (host emulation, b200pt_trace_batch, the small emissive BVH).
+PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
+                                 uint32_t objectCount, Hit& hit, uint32_t& key) {
+    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    Trav t;
+    trav_begin(t, ray);
+    for (;;) {
+        if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, t, hit, key);
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stackBase, stackBits, hit.dst);
+        else if (!trav_pop(t, stackBase, stackBits)) break;
+    }
+}
 PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
                                   uint32_t objectCount, float tE, uint32_t keyE) {
-    BoxRay br = make_box_ray(ray);
-    ObjRayCache oc; oc.xform = 0xffffffffu;
-    uint32_t oct = br.octinv4 & 7u;
     uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
-    int sp = 0;
-    uint32_t gBase = 0, gBits = 0x80000000u;
+    Trav t;
+    trav_begin(t, ray);
     for (;;) {
-        uint32_t tBase = 0, tBits = 0;
-        if (gBits & 0xff000000u) {
-            int bit = highest_bit(gBits);
-            gBits &= ~(1u << bit);
-            uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
-            uint32_t rel = (uint32_t)popcount32(gBits & 0xffu & ~(0xffffffffu << slot));
-            uint32_t nodeIdx = gBase + rel;
-            if (gBits & 0xff000000u) { stackBase[sp] = gBase; stackBits[sp] = gBits; sp++; }
-            const Bvh8Node n = bvh.nodes[nodeIdx];
-            uint32_t h = bvh8_node_hits(n, br, tE);
-            gBase = n.childBase; gBits = (h & 0xff000000u) | n.imask;
-            tBase = n.primBase; tBits = h & 0x00ffffffu;
-        } else {
-            gBits = 0;
-        }
-        while (tBits) {
-            int k = highest_bit(tBits);
-            tBits &= ~(1u << k);
-            const PrimRecord p = bvh.prims[tBase + (uint32_t)k];
-            if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) continue;
-            const Ray& tr = object_ray(oc, xforms, p.xformId, ray);
-            float dst, u, v; bool front;
-            if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
-                (dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE)) && ref_reachable(up, p.leafNode, oc, dst))
-                return true;
-        }
-        if ((gBits & 0xff000000u) == 0) {
-            if (sp == 0) break;
-            sp--; gBase = stackBase[sp]; gBits = stackBits[sp];
-        }
+        if (trav_has_tri(t)) { if (trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, t, tE, keyE)) return true; }
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stackBase, stackBits, tE);
+        else if (!trav_pop(t, stackBase, stackBits)) break;
     }
     return false;
 }

@@ -27,6 +27,7 @@ struct WavefrontState {
     size_t capacity = 0;
     uint32_t countSlots = 0;
     int smCount = 148;
+    int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
     std::vector<int> eventStage;      // stage of the launch that FOLLOWS event i (-1: batch end)
@@ -92,11 +93,88 @@ __global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__
     if (blockIdx.x == 0 && threadIdx.x == 0) qCount[0] = P.nPaths;
 }
 
+// ---- persistent traversal kernels ------------------------------------------------------------
+// One warp = 32 ray slots. Every iteration the warp votes: lanes whose ray is finished are refilled
+// from the queue (chunks of PT_CHUNK indices per global atomic, handed out by ballot rank) once
+// enough of them are idle; then the whole warp runs ONE kind of step — a triangle test for the lanes
+// that hold a triangle group, or a node visit for the lanes that hold a node group — so that the
+// divergent halves of the classic while-while loop each run with as many lanes as possible.
+// Triangle groups met while the warp is visiting nodes are postponed on the lane's stack
+// (trav_node_step). Grid = exactly the resident blocks of the device: no second wave.
+#define PT_CHUNK 128u
+#define PT_FETCH_MIN_IDLE 8        /* refill once this many lanes are idle (or all are) */
+
+struct WarpFeeder {                // warp-uniform
+    uint32_t next = 0, end = 0;
+    bool exhausted = false;
+};
+// Returns the queue index assigned to this lane (valid when the returned flag is set).
+static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* workCounter, uint32_t n, bool idle, uint32_t& index) {
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned idleMask = __ballot_sync(0xffffffffu, idle);
+    if (f.exhausted || (uint32_t)__popc(idleMask) < PT_FETCH_MIN_IDLE) return false;
+    if (f.next == f.end) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(workCounter, PT_CHUNK);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) { f.exhausted = true; return false; }
+        f.next = base; f.end = min(base + PT_CHUNK, n);
+    }
+    uint32_t give = min((uint32_t)__popc(idleMask), f.end - f.next);
+    uint32_t rank = (uint32_t)__popc(idleMask & ((1u << lane) - 1u));
+    bool got = idle && rank < give;
+    index = f.next + rank;
+    f.next += give;
+    return got;
+}
+
 __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
-                                                       const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount) {
-    uint32_t n = *qCount;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        stage_extend(P, sc, A, queue[i]);
+                                                       const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
+                                                       uint32_t* workCounter) {
+    const uint32_t n = *qCount;
+    const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
+    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    WarpFeeder feed;
+    Trav t;
+    Hit hit;
+    uint32_t key = 0xffffffffu, p = 0;
+    bool busy = false;
+    hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f;
+    t.gBits = 0; t.tBits = 0; t.sp = 0;
+    for (;;) {
+        uint32_t qi;
+        if (feeder_take(feed, workCounter, n, !busy, qi)) {
+            p = queue[qi];
+            Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+            hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f; key = 0xffffffffu;
+            for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
+                float dst; bool front;
+                if (sphere_test(sc.spheres[i], r, dst, front) && dst < hit.dst) {
+                    hit.dst = dst; hit.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
+                }
+            }
+            trav_begin(t, r);
+            busy = true;
+        }
+        // lanes with nothing in hand take the next group from their stack, or finish
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) {
+            A.hit[p] = hit;
+            busy = false;
+        }
+        unsigned busyMask = __ballot_sync(0xffffffffu, busy);
+        if (busyMask == 0u) {
+            if (feed.exhausted) break;
+            continue;
+        }
+        unsigned triMask = __ballot_sync(0xffffffffu, busy && trav_has_tri(t));
+        bool canNode = busy && trav_has_node(t) && (!trav_has_tri(t) || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
+        if (nodeMask == 0u || 4 * __popc(triMask) >= __popc(busyMask)) {
+            if (busy && trav_has_tri(t)) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
+        } else {
+            if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, hit.dst);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(WF_THREADS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
@@ -270,7 +348,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
     }
     uint32_t need = bounces + 3;
     if (need > w->countSlots) {
-        WCU(wf_resize(w->dCounts, (size_t)need * 2 * 4));
+        WCU(wf_resize(w->dCounts, (size_t)need * 4 * 4));      // qCount | sCount | extend work counters | connect work counters
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
@@ -304,11 +382,17 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t nB = pc.params.bounceLimit + 1;
     uint32_t* qCount = (uint32_t*)w->dCounts.p;
     uint32_t* sCount = qCount + w->countSlots;
+    uint32_t* workE = sCount + w->countSlots;
+    if (!w->gridExtend) {
+        int perSm = 0;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend, WF_THREADS, 0));
+        w->gridExtend = std::max(1, perSm) * w->smCount;
+    }
     for (uint32_t done = 0; done < n; done += slots) {
         P.nSlots = std::min(slots, n - done);
         P.firstFrame = first + done * stride;
         P.nPaths = (uint32_t)(perSlot * P.nSlots);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 2 * 4, c->stream));
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 4 * 4, c->stream));
         uint32_t* qa = (uint32_t*)w->dQueue[0].p;
         uint32_t* qb = (uint32_t*)w->dQueue[1].p;
         if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
@@ -316,7 +400,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount);
         for (uint32_t j = 0; j < nB; ++j) {
             wf_mark(c, ST_EXTEND);
-            k_extend<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j);
+            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, workE + j);
             wf_mark(c, ST_SHADE);
             k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
