@@ -319,8 +319,8 @@ def main():
         b_all = algorithmic_bytes(r["work_all"], r["paths"]) + 32.0
         b_ext = algorithmic_bytes(r["work_ext"], r["paths"])
         b_con = b_all - b_ext - 32.0
-        stage_bytes = dict(extend=b_ext, connect=b_con)
-        dom = max(("extend", "connect"), key=lambda s: stages[s][0])
+        stage_bytes = dict(extend=b_ext, occlude=b_con)      # NEE/pdf rays: their traversal is k_occlude
+        dom = max(("extend", "occlude"), key=lambda s: stages[s][0])
         dom_ms, dom_launches = stages[dom]
         peaks = {}
         try:

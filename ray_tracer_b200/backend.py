@@ -217,12 +217,12 @@ class ComputePass:
         self._check(self.L.b200pt_read_counters(self.h, _ptr(c)), "b200pt_read_counters")
         return dict(launches=int(c[0]), paths=int(c[1]), extension_rays=int(c[2]), shadow_rays=int(c[3]))
 
-    STAGES = ("generate", "extend", "shade", "connect", "accumulate")
+    STAGES = ("generate", "extend", "shade", "connect_prep", "accumulate", "occlude", "connect_finish")
 
     def stage_times(self, reset=False):
         """{stage: (device ms, launches)} accumulated while option profile_stages = 1."""
-        ms = np.zeros(5, np.float64)
-        n = np.zeros(5, np.uint64)
+        ms = np.zeros(8, np.float64)
+        n = np.zeros(8, np.uint64)
         self._check(self.L.b200pt_read_stage_times(self.h, _ptr(ms), _ptr(n), int(reset)), "b200pt_read_stage_times")
         return {k: (float(ms[i]), int(n[i])) for i, k in enumerate(self.STAGES)}
 

@@ -407,12 +407,12 @@ int b200pt_reset_counters(b200pt_ctx* c) {
     std::memset(c->counters, 0, sizeof(c->counters));
     return 0;
 }
-int b200pt_read_stage_times(b200pt_ctx* c, double* ms5, uint64_t* launches5, int reset) {
-    if (!c || !ms5 || !launches5) return B200PT_ERR_ARG;
+int b200pt_read_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, int reset) {
+    if (!c || !ms8 || !launches8) return B200PT_ERR_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->stream));
     wavefront_resolve_stage_times(c);
-    wavefront_stage_times(c, ms5, launches5, reset != 0);
+    wavefront_stage_times(c, ms8, launches8, reset != 0);
     return 0;
 }
 int b200pt_last_render_ms(b200pt_ctx* c, float* ms) {

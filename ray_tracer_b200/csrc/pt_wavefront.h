@@ -33,7 +33,8 @@ struct PathArrays {
     Hit* hit;          // extend result
     float4* qO;        // NEE origin.xyz (hit + n*0.01) | cosinePDF(lightSample)
     float4* qL;        // lightSample.xyz               | realCosinePDF
-    float4* qA;        // albedo*INV_PI*max(0, n.lightSample)
+    float4* qA;        // albedo*INV_PI*max(0, n.lightSample) | material of the emissive light-sample hit
+    float4* qE;        // emissive candidate distances and loop-order keys of the two pdf rays (connect)
 };
 
 struct WfParams {
@@ -174,15 +175,23 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 }
 
 // ---- connect --------------------------------------------------------------------------------
-// lightSamplePDF() (raytrace.comp:389-403) for (origin, dir): nonzero only when the closest hit of
-// the ray is emissive. matOut = material of that hit.
-PT_HD float emissive_pdf(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& matOut,
-                         bool& emissiveClosest) {
-    matOut = 0u; emissiveClosest = false;
-    if (!sc.anyEmissive) return 0.f;
+// lightSamplePDF() (raytrace.comp:389-403) for (origin, dir) is nonzero only when the CLOSEST hit of
+// the ray is emissive. It is evaluated in three parts:
+//   prep    : closest hit among EMISSIVE geometry only (spheres + the small emissive BVH), and the
+//             non-emissive spheres that could hide it -> candidate distance tE and loop-order key
+//   occlude : is there a non-emissive triangle the reference would have preferred? (bounded any-hit
+//             walk of the full BVH, the expensive part: its own persistent kernel, wavefront.cu)
+//   finish  : pdfs, MIS weights, direct light (raytrace.comp:447-460)
+// qE[p] = { tE(lightSample), tE(cosineSample), key(lightSample), key(cosineSample) }, tE < 0: no
+// emissive closest hit (none found, or occluded). qA[p].w = material of the light-sample hit.
+#define PT_NO_EMISSIVE (-1.f)
+
+PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
+                               uint32_t& matOut) {
+    matOut = 0u; keyE = 0xffffffffu;
+    if (!sc.anyEmissive) return PT_NO_EMISSIVE;
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
-    uint32_t keyE = 0xffffffffu;
     for (uint32_t i = 0; i < sphereCount; i++) {
         const ptl::Sphere s = sc.spheres[i];
         if (sc.materials[s.materialIndex].emissionStrength == 0.f) continue;
@@ -191,40 +200,73 @@ PT_HD float emissive_pdf(const WideScene& sc, v3 origin, v3 dir, uint32_t sphere
     }
     uint32_t before = e.id;
     bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
-    if (e.id == PT_HIT_MISS) return 0.f;
+    if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
     for (uint32_t i = 0; i < sphereCount; i++) {
         const ptl::Sphere s = sc.spheres[i];
         if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
         float dst; bool front;
-        if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return 0.f;
+        if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
     }
-    if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e.dst, keyE)) return 0.f;
-    emissiveClosest = true;
-    return light_pdf_from_dst(e.dst, dir);
+    return e.dst;
 }
 
-PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+#define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
+#define PT_CONNECT_JOB_COSINE 2u    /* ... for the cosine-sample ray */
+PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
-    float4 qo = A.qO[p], ql = A.qL[p];
-    v3 origin = xyz(qo), lightSample = xyz(ql), cosineSample = xyz(A.rayD[p]);
+    v3 origin = xyz(A.qO[p]), lightSample = xyz(A.qL[p]), cosineSample = xyz(A.rayD[p]);
+    uint32_t keyL, keyC, matL, matC;
+    float tL = emissive_candidate(sc, origin, lightSample, td.sphereCount, td.objectCount, keyL, matL);     // :443-447
+    float tC = emissive_candidate(sc, origin, cosineSample, td.sphereCount, td.objectCount, keyC, matC);    // :453
+    A.qE[p] = make_float4(tL, tC, as_float(keyL), as_float(keyC));
+    float4 qa = A.qA[p];
+    qa.w = as_float(matL);
+    A.qA[p] = qa;
+    return (tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u) | (tC >= 0.f ? PT_CONNECT_JOB_COSINE : 0u);
+}
+// the occlusion query of job `which` (0 light sample, 1 cosine sample) of path p
+PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, uint32_t which, Ray& r, float& tE, uint32_t& keyE) {
+    float4 e = A.qE[p];
+    r.o = xyz(A.qO[p]);
+    r.d = which ? xyz(A.rayD[p]) : xyz(A.qL[p]);
+    tE = which ? e.y : e.x;
+    keyE = as_uint(which ? e.w : e.z);
+}
+PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p, uint32_t which) {
+    float* e = reinterpret_cast<float*>(&A.qE[p]);
+    e[which] = PT_NO_EMISSIVE;
+}
+PT_HD void stage_connect_finish(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+    float4 qo = A.qO[p], ql = A.qL[p], qa = A.qA[p], qe = A.qE[p];
+    v3 lightSample = xyz(ql), cosineSample = xyz(A.rayD[p]);
     float cosinePDF = qo.w, realCosinePDF = ql.w;
-    uint32_t lightMat, unused;
-    bool lightIsClosest, unusedB;
-    float realLightPDF = emissive_pdf(sc, origin, lightSample, td.sphereCount, td.objectCount, lightMat, lightIsClosest);   // :443-447
+    bool lightIsClosest = qe.x >= 0.f;
+    float realLightPDF = lightIsClosest ? light_pdf_from_dst(qe.x, lightSample) : 0.f;                      // :447
     float w1 = mis_weight(realLightPDF, cosinePDF);                                                        // :449-450
-    float lightPDF = emissive_pdf(sc, origin, cosineSample, td.sphereCount, td.objectCount, unused, unusedB);       // :453
+    float lightPDF = qe.y >= 0.f ? light_pdf_from_dst(qe.y, cosineSample) : 0.f;                           // :453
     float w2 = mis_weight(realCosinePDF, lightPDF);                                                        // :455-456
     v3 E = splat3(0.f);           // a non-emissive (or missing) closest hit contributes emission * 0
     if (lightIsClosest) {
-        const ptl::Material lm = sc.materials[lightMat];
+        const ptl::Material lm = sc.materials[as_uint(qa.w)];
         E = mk3(lm.emissionColor[0], lm.emissionColor[1], lm.emissionColor[2]) * lm.emissionStrength;
     }
-    v3 direct = E * (xyz(A.qA[p]) * (realLightPDF == 0.f ? 0.f : w1 / realLightPDF));                       // :459-460
+    v3 direct = E * (xyz(qa) * (realLightPDF == 0.f ? 0.f : w1 / realLightPDF));                            // :459-460
     A.direct[p] = f4(direct, 0.f);
     float4 ro = A.rayO[p];
     ro.w = w2;
     A.rayO[p] = ro;
+}
+// all three parts for one path (host emulation; the kernels run them as separate launches)
+PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+    uint32_t jobs = stage_connect_prep(P, sc, A, p);
+    for (uint32_t which = 0; which < 2; ++which) {
+        if (!(jobs & (1u << which))) continue;
+        Ray r; float tE; uint32_t keyE;
+        connect_job_ray(A, p, which, r, tE, keyE);
+        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p, which);
+    }
+    stage_connect_finish(P, sc, A, p);
 }
 
 // ---- accumulate -----------------------------------------------------------------------------

@@ -15,6 +15,7 @@
 
 namespace pt {
 
+#define PT_N_STAGES 8
 struct WavefrontState {
     // re-laid-out scene
     DeviceBuffer dNodes, dPrims, dShade, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform, dUp;
@@ -22,21 +23,22 @@ struct WavefrontState {
     uint32_t maxDepth = 0;
     // path state
     DeviceBuffer dPaths[9];
-    DeviceBuffer dHit, dQueue[2], dShadowQ, dCounts, dRayCounters;
+    DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters;
     PathArrays arrays{};
     size_t capacity = 0;
     uint32_t countSlots = 0;
     int smCount = 148;
+    int gridOcclude = 0;
     int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
     std::vector<int> eventStage;      // stage of the launch that FOLLOWS event i (-1: batch end)
     size_t eventsUsed = 0;
-    double stageMs[5] = {0, 0, 0, 0, 0};
-    uint64_t stageLaunches[5] = {0, 0, 0, 0, 0};
+    double stageMs[PT_N_STAGES] = {0};
+    uint64_t stageLaunches[PT_N_STAGES] = {0};
 };
 
-enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4 };
+enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4, ST_OCCLUDE = 5, ST_FINISH = 6 };
 
 static void wf_mark(b200pt_ctx* c, int stage) {
     WavefrontState* w = c->wf;
@@ -63,10 +65,10 @@ void wavefront_resolve_stage_times(b200pt_ctx* c) {
     }
     w->eventsUsed = 0;
 }
-void wavefront_stage_times(b200pt_ctx* c, double* ms5, uint64_t* launches5, bool reset) {
+void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool reset) {
     WavefrontState* w = c->wf;
-    for (int i = 0; i < 5; ++i) {
-        ms5[i] = w ? w->stageMs[i] : 0.0; launches5[i] = w ? w->stageLaunches[i] : 0;
+    for (int i = 0; i < PT_N_STAGES; ++i) {
+        ms8[i] = w ? w->stageMs[i] : 0.0; launches8[i] = w ? w->stageLaunches[i] : 0;
         if (w && reset) { w->stageMs[i] = 0.0; w->stageLaunches[i] = 0; }
     }
 }
@@ -195,11 +197,71 @@ __global__ void __launch_bounds__(WF_THREADS) k_shade(const __grid_constant__ Wf
     }
 }
 
-__global__ void __launch_bounds__(WF_THREADS) k_connect(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
-                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount) {
+// connect, part 1: emissive candidates of both pdf rays; emits the occlusion jobs (path | which << 31)
+__global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                             const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
+                                                             uint32_t* jobQueue, uint32_t* jobCount) {
+    uint32_t n = *sCount;
+    uint32_t nRound = (n + 31u) & ~31u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
+        uint32_t jobs = 0, p = 0;
+        if (i < n) { p = queue[i]; jobs = stage_connect_prep(P, sc, A, p); }
+        bool jl = (jobs & PT_CONNECT_JOB_LIGHT) != 0, jc = (jobs & PT_CONNECT_JOB_COSINE) != 0;
+        uint32_t s0 = warp_push(jobCount, jl);
+        if (jl) jobQueue[s0] = p;
+        uint32_t s1 = warp_push(jobCount, jc);
+        if (jc) jobQueue[s1] = p | 0x80000000u;
+    }
+}
+
+// connect, part 2: bounded any-hit walks of the full BVH, same warp scheduling as k_extend
+__global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                        const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
+                                                        uint32_t* workCounter) {
+    const uint32_t n = *jobCount;
+    const uint32_t objectCount = P.pc.params.objectCount;
+    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    WarpFeeder feed;
+    Trav t;
+    float tE = 0.f;
+    uint32_t keyE = 0, job = 0;
+    bool busy = false;
+    t.gBits = 0; t.tBits = 0; t.sp = 0;
+    for (;;) {
+        uint32_t qi;
+        if (feeder_take(feed, workCounter, n, !busy, qi)) {
+            job = jobQueue[qi];
+            Ray r;
+            connect_job_ray(A, job & 0x7fffffffu, job >> 31, r, tE, keyE);
+            trav_begin(t, r);
+            busy = true;
+        }
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) busy = false;   // not occluded
+        unsigned busyMask = __ballot_sync(0xffffffffu, busy);
+        if (busyMask == 0u) {
+            if (feed.exhausted) break;
+            continue;
+        }
+        unsigned triMask = __ballot_sync(0xffffffffu, busy && trav_has_tri(t));
+        bool canNode = busy && trav_has_node(t) && (!trav_has_tri(t) || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
+        if (nodeMask == 0u || 4 * __popc(triMask) >= __popc(busyMask)) {
+            if (busy && trav_has_tri(t) && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
+                connect_job_occluded(A, job & 0x7fffffffu, job >> 31);
+                busy = false;
+            }
+        } else {
+            if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, tE);
+        }
+    }
+}
+
+// connect, part 3: pdfs, MIS weights, direct light
+__global__ void __launch_bounds__(WF_THREADS) k_connect_finish(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                               const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount) {
     uint32_t n = *sCount;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        stage_connect(P, sc, A, queue[i]);
+        stage_connect_finish(P, sc, A, queue[i]);
 }
 
 __global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant__ WfParams P, PathArrays A, float4* accum) {
@@ -324,7 +386,7 @@ void wavefront_destroy(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w) return;
     DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
-                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dCounts, &w->dRayCounters};
+                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
@@ -340,15 +402,16 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
         WCU(wf_resize(w->dQueue[0], paths * 4));
         WCU(wf_resize(w->dQueue[1], paths * 4));
         WCU(wf_resize(w->dShadowQ, paths * 4));
+        WCU(wf_resize(w->dJobQ, paths * 8));
         w->capacity = paths;
         PathArrays& A = w->arrays;
         A.rayO = (float4*)w->dPaths[0].p; A.rayD = (float4*)w->dPaths[1].p; A.atten = (float4*)w->dPaths[2].p;
         A.total = (float4*)w->dPaths[3].p; A.direct = (float4*)w->dPaths[4].p; A.qO = (float4*)w->dPaths[5].p;
-        A.qL = (float4*)w->dPaths[6].p; A.qA = (float4*)w->dPaths[7].p; A.hit = (Hit*)w->dHit.p;
+        A.qL = (float4*)w->dPaths[6].p; A.qA = (float4*)w->dPaths[7].p; A.qE = (float4*)w->dPaths[8].p; A.hit = (Hit*)w->dHit.p;
     }
     uint32_t need = bounces + 3;
     if (need > w->countSlots) {
-        WCU(wf_resize(w->dCounts, (size_t)need * 4 * 4));      // qCount | sCount | extend work counters | connect work counters
+        WCU(wf_resize(w->dCounts, (size_t)need * 5 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
@@ -383,6 +446,13 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* qCount = (uint32_t*)w->dCounts.p;
     uint32_t* sCount = qCount + w->countSlots;
     uint32_t* workE = sCount + w->countSlots;
+    uint32_t* workO = workE + w->countSlots;
+    uint32_t* oCount = workO + w->countSlots;
+    if (!w->gridOcclude) {
+        int perSm = 0;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude, WF_THREADS, 0));
+        w->gridOcclude = std::max(1, perSm) * w->smCount;
+    }
     if (!w->gridExtend) {
         int perSm = 0;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend, WF_THREADS, 0));
@@ -392,7 +462,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         P.nSlots = std::min(slots, n - done);
         P.firstFrame = first + done * stride;
         P.nPaths = (uint32_t)(perSlot * P.nSlots);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 4 * 4, c->stream));
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 5 * 4, c->stream));
         uint32_t* qa = (uint32_t*)w->dQueue[0].p;
         uint32_t* qb = (uint32_t*)w->dQueue[1].p;
         if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
@@ -405,10 +475,16 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
             if (j + 1 < nB) wf_mark(c, ST_CONNECT);
-            if (j + 1 < nB)
-                k_connect<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j);
+            if (j + 1 < nB) {
+                k_connect_prep<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                                                                   (uint32_t*)w->dJobQ.p, oCount + j);
+                wf_mark(c, ST_OCCLUDE);
+                k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
+                wf_mark(c, ST_FINISH);
+                k_connect_finish<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j);
+            }
             std::swap(qa, qb);
-            c->counters[0] += (j + 1 < nB) ? 3 : 2;
+            c->counters[0] += (j + 1 < nB) ? 5 : 2;
         }
         wf_mark(c, ST_ACCUMULATE);
         k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);

@@ -11,6 +11,6 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
 int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits);
 void wavefront_fold_counters(b200pt_ctx* c);
 void wavefront_resolve_stage_times(b200pt_ctx* c);     // stream idle
-void wavefront_stage_times(b200pt_ctx* c, double* ms5, uint64_t* launches5, bool reset);
+void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool reset);
 cudaError_t launch_image_to_rgba8(b200pt_ctx* c, const float4* image, uchar4* out, size_t n);
 }  // namespace pt

@@ -60,9 +60,9 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
     P.cp = camera_plane(P.pc.cam);
     P.W = W; P.H = H; P.row0 = 0; P.rows = (uint32_t)H; P.stride = stride ? stride : 1;
     size_t cap = (size_t)slots * W * H;
-    std::vector<float4> rayO(cap), rayD(cap), atten(cap), total(cap), direct(cap), qO(cap), qL(cap), qA(cap);
+    std::vector<float4> rayO(cap), rayD(cap), atten(cap), total(cap), direct(cap), qO(cap), qL(cap), qA(cap), qE(cap);
     std::vector<Hit> hit(cap);
-    PathArrays A{rayO.data(), rayD.data(), atten.data(), total.data(), direct.data(), hit.data(), qO.data(), qL.data(), qA.data()};
+    PathArrays A{rayO.data(), rayD.data(), atten.data(), total.data(), direct.data(), hit.data(), qO.data(), qL.data(), qA.data(), qE.data()};
     std::vector<uint32_t> q0(cap), q1(cap), qs(cap);
     for (uint32_t done = 0; done < n; done += slots) {
         P.nSlots = std::min(slots, n - done);
