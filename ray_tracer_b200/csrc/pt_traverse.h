@@ -67,45 +67,53 @@ PT_HD NodeWords load_node(const Bvh8Node* nodes, uint32_t idx) {
 #endif
     return n;
 }
-// float(byte k of word), exact. Device: the byte is dropped into the mantissa of 2^23 (one PRMT) and
-// 2^23 is subtracted (one FADD) — keeps the 48 conversions per node off the quarter-rate I2F pipe.
-PT_HD float byte_to_float(uint32_t word, int k) {
+// Byte k of `word` dropped into the mantissa of 1.0f (bits 8..15): 1 + q * 2^-15, exact, one PRMT
+// on the device — no integer->float conversion (quarter-rate pipe) and no subtraction.
+PT_HD float byte_as_unit_float(uint32_t word, int k) {
 #if defined(__CUDA_ARCH__)
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + (uint32_t)k)) - 8388608.f;
+    return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u + ((uint32_t)k << 4)));
 #else
-    return (float)((word >> (8 * k)) & 0xffu);
+    return as_float(0x3F800000u | (((word >> (8 * k)) & 0xffu) << 8));
 #endif
 }
 
 // Slab-test the 8 children of a node; returns hit bits: inner children in bits 24..31 ordered by
 // traversal priority for this ray's octant, leaf triangles in bits 0..23 (offset from primBase).
+// A child plane is at t = (p + q * 2^(e-127) - o) * rd = Q * S + O with Q = 1 + q * 2^-15,
+// S = 2^(e-112) * rd and O = (p - o) * rd - S: one FMA per plane. O carries one extra rounding of
+// at most |S| * 2^-23 (a 1/256 of a quantisation step); near planes are moved down and far planes
+// up by twice that, so the test stays conservative.
 PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) {
-    float sx = as_float((n.w[3] & 0xffu) << 23) * br.rd.x;
-    float sy = as_float(((n.w[3] >> 8) & 0xffu) << 23) * br.rd.y;
-    float sz = as_float(((n.w[3] >> 16) & 0xffu) << 23) * br.rd.z;
-    float ox = (as_float(n.w[0]) - br.o.x) * br.rd.x;
-    float oy = (as_float(n.w[1]) - br.o.y) * br.rd.y;
-    float oz = (as_float(n.w[2]) - br.o.z) * br.rd.z;
+    const float sx = as_float(((n.w[3] & 0xffu) + 15u) << 23) * br.rd.x;
+    const float sy = as_float((((n.w[3] >> 8) & 0xffu) + 15u) << 23) * br.rd.y;
+    const float sz = as_float((((n.w[3] >> 16) & 0xffu) + 15u) << 23) * br.rd.z;
+    const float ox = pt_fma(as_float(n.w[0]) - br.o.x, br.rd.x, -sx);
+    const float oy = pt_fma(as_float(n.w[1]) - br.o.y, br.rd.y, -sy);
+    const float oz = pt_fma(as_float(n.w[2]) - br.o.z, br.rd.z, -sz);
+    const float wx = fabsf(sx) * 2.384185791015625e-07f, wy = fabsf(sy) * 2.384185791015625e-07f, wz = fabsf(sz) * 2.384185791015625e-07f;   // 2^-22
+    const float onx = ox - wx, ofx = ox + wx, ony = oy - wy, ofy = oy + wy, onz = oz - wz, ofz = oz + wz;
     const bool negx = br.rd.x < 0.f, negy = br.rd.y < 0.f, negz = br.rd.z < 0.f;
     const uint32_t nx[2] = {negx ? n.w[14] : n.w[8], negx ? n.w[15] : n.w[9]}, fx[2] = {negx ? n.w[8] : n.w[14], negx ? n.w[9] : n.w[15]};
     const uint32_t ny[2] = {negy ? n.w[16] : n.w[10], negy ? n.w[17] : n.w[11]}, fy[2] = {negy ? n.w[10] : n.w[16], negy ? n.w[11] : n.w[17]};
     const uint32_t nz[2] = {negz ? n.w[18] : n.w[12], negz ? n.w[19] : n.w[13]}, fz[2] = {negz ? n.w[12] : n.w[18], negz ? n.w[13] : n.w[19]};
-    const uint32_t oct = br.octinv4 & 7u;
     uint32_t hits = 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const int h = i >> 2, k = i & 3;
-        uint32_t meta = (n.w[6 + h] >> (8 * k)) & 0xffu;
-        if (meta == 0) continue;
-        float t0x = pt_fma(byte_to_float(nx[h], k), sx, ox), t1x = pt_fma(byte_to_float(fx[h], k), sx, ox);
-        float t0y = pt_fma(byte_to_float(ny[h], k), sy, oy), t1y = pt_fma(byte_to_float(fy[h], k), sy, oy);
-        float t0z = pt_fma(byte_to_float(nz[h], k), sz, oz), t1z = pt_fma(byte_to_float(fz[h], k), sz, oz);
-        float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
-        float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-        if (tn <= tf) {
-            bool inner = (meta & 0x18u) == 0x18u && (meta >> 5) == 1u;
-            uint32_t bit = inner ? ((meta ^ oct) & 0x1fu) : (meta & 0x1fu);
-            hits |= (meta >> 5) << bit;
+    for (int h = 0; h < 2; ++h) {
+        // four children at a time (Ylitie et al. 2017): which are inner nodes, their bit position
+        // (inner: 24 + (slot ^ (7 - octant)), leaf: offset of its first triangle) and unary count
+        const uint32_t meta4 = n.w[6 + h];
+        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
+        const uint32_t bitIndex4 = (meta4 ^ (br.octinv4 & innerMask4)) & 0x1f1f1f1fu;
+        const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float t0x = pt_fma(byte_as_unit_float(nx[h], k), sx, onx), t1x = pt_fma(byte_as_unit_float(fx[h], k), sx, ofx);
+            float t0y = pt_fma(byte_as_unit_float(ny[h], k), sy, ony), t1y = pt_fma(byte_as_unit_float(fy[h], k), sy, ofy);
+            float t0z = pt_fma(byte_as_unit_float(nz[h], k), sz, onz), t1z = pt_fma(byte_as_unit_float(fz[h], k), sz, ofz);
+            float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
+            float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            if (tn <= tf) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);
         }
     }
     return hits;

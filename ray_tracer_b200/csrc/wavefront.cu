@@ -110,11 +110,10 @@ struct WarpFeeder {                // warp-uniform
     uint32_t next = 0, end = 0;
     bool exhausted = false;
 };
-// Returns the queue index assigned to this lane (valid when the returned flag is set).
-static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* workCounter, uint32_t n, bool idle, uint32_t& index) {
+// Hands queue indices to idle lanes (idleMask = ballot of idle lanes, warp-uniform). Returns whether THIS
+// lane got one.
+static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* workCounter, uint32_t n, unsigned idleMask, uint32_t& index) {
     const unsigned lane = threadIdx.x & 31u;
-    unsigned idleMask = __ballot_sync(0xffffffffu, idle);
-    if (f.exhausted || (uint32_t)__popc(idleMask) < PT_FETCH_MIN_IDLE) return false;
     if (f.next == f.end) {
         uint32_t base = 0;
         if (lane == 0) base = atomicAdd(workCounter, PT_CHUNK);
@@ -124,7 +123,7 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     }
     uint32_t give = min((uint32_t)__popc(idleMask), f.end - f.next);
     uint32_t rank = (uint32_t)__popc(idleMask & ((1u << lane) - 1u));
-    bool got = idle && rank < give;
+    bool got = ((idleMask >> lane) & 1u) && rank < give;
     index = f.next + rank;
     f.next += give;
     return got;
@@ -144,35 +143,39 @@ __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ W
     hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
-        uint32_t qi;
-        if (feeder_take(feed, workCounter, n, !busy, qi)) {
-            p = queue[qi];
-            Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-            hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f; key = 0xffffffffu;
-            for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
-                float dst; bool front;
-                if (sphere_test(sc.spheres[i], r, dst, front) && dst < hit.dst) {
-                    hit.dst = dst; hit.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
-                }
-            }
-            trav_begin(t, r);
-            busy = true;
-        }
         // lanes with nothing in hand take the next group from their stack, or finish
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) {
             A.hit[p] = hit;
             busy = false;
         }
-        unsigned busyMask = __ballot_sync(0xffffffffu, busy);
-        if (busyMask == 0u) {
+        unsigned idleMask = __ballot_sync(0xffffffffu, !busy);
+        if (idleMask != 0u && !feed.exhausted && (uint32_t)__popc(idleMask) >= PT_FETCH_MIN_IDLE) {
+            uint32_t qi;
+            if (feeder_take(feed, workCounter, n, idleMask, qi)) {
+                p = queue[qi];
+                Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+                hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f; key = 0xffffffffu;
+                for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
+                    float dst; bool front;
+                    if (sphere_test(sc.spheres[i], r, dst, front) && dst < hit.dst) {
+                        hit.dst = dst; hit.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
+                    }
+                }
+                trav_begin(t, r);
+                busy = true;
+            }
+            idleMask = __ballot_sync(0xffffffffu, !busy);
+        }
+        if (idleMask == 0xffffffffu) {
             if (feed.exhausted) break;
             continue;
         }
-        unsigned triMask = __ballot_sync(0xffffffffu, busy && trav_has_tri(t));
-        bool canNode = busy && trav_has_node(t) && (!trav_has_tri(t) || t.sp < PT_BVH8_POSTPONE_LIMIT);
-        unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
-        if (nodeMask == 0u || 4 * __popc(triMask) >= __popc(busyMask)) {
-            if (busy && trav_has_tri(t)) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
+        const bool hasTri = busy && trav_has_tri(t);
+        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        const unsigned triMask = __ballot_sync(0xffffffffu, hasTri);
+        const unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
+        if (nodeMask == 0u || 4 * __popc(triMask) >= 32 - __popc(idleMask)) {
+            if (hasTri) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
         } else {
             if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, hit.dst);
         }
@@ -228,25 +231,29 @@ __global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ 
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
-        uint32_t qi;
-        if (feeder_take(feed, workCounter, n, !busy, qi)) {
-            job = jobQueue[qi];
-            Ray r;
-            connect_job_ray(A, job & 0x7fffffffu, job >> 31, r, tE, keyE);
-            trav_begin(t, r);
-            busy = true;
-        }
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) busy = false;   // not occluded
-        unsigned busyMask = __ballot_sync(0xffffffffu, busy);
-        if (busyMask == 0u) {
+        unsigned idleMask = __ballot_sync(0xffffffffu, !busy);
+        if (idleMask != 0u && !feed.exhausted && (uint32_t)__popc(idleMask) >= PT_FETCH_MIN_IDLE) {
+            uint32_t qi;
+            if (feeder_take(feed, workCounter, n, idleMask, qi)) {
+                job = jobQueue[qi];
+                Ray r;
+                connect_job_ray(A, job & 0x7fffffffu, job >> 31, r, tE, keyE);
+                trav_begin(t, r);
+                busy = true;
+            }
+            idleMask = __ballot_sync(0xffffffffu, !busy);
+        }
+        if (idleMask == 0xffffffffu) {
             if (feed.exhausted) break;
             continue;
         }
-        unsigned triMask = __ballot_sync(0xffffffffu, busy && trav_has_tri(t));
-        bool canNode = busy && trav_has_node(t) && (!trav_has_tri(t) || t.sp < PT_BVH8_POSTPONE_LIMIT);
-        unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
-        if (nodeMask == 0u || 4 * __popc(triMask) >= __popc(busyMask)) {
-            if (busy && trav_has_tri(t) && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
+        const bool hasTri = busy && trav_has_tri(t);
+        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        const unsigned triMask = __ballot_sync(0xffffffffu, hasTri);
+        const unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
+        if (nodeMask == 0u || 4 * __popc(triMask) >= 32 - __popc(idleMask)) {
+            if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
                 connect_job_occluded(A, job & 0x7fffffffu, job >> 31);
                 busy = false;
             }
