@@ -26,6 +26,7 @@ struct WideSceneHost {
     std::vector<uint32_t> objXform;
     std::vector<UpNode> up;
     bool anyEmissive = false;
+    uint32_t emisSphereMask = 0;
 };
 
 namespace b8 {
@@ -269,7 +270,9 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     using namespace b8;
     out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
     auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
-    for (const auto& s : spheres) if (emissive(s.materialIndex)) out.anyEmissive = true;
+    out.emisSphereMask = 0;
+    for (size_t i = 0; i < spheres.size(); ++i)
+        if (emissive(spheres[i].materialIndex)) { out.anyEmissive = true; if (i < 32) out.emisSphereMask |= 1u << i; }
 
     // distinct object matrices (bit pattern): objects that share one share the transformed ray
     for (size_t o = 0; o < objects.size(); ++o) {

@@ -81,6 +81,7 @@ struct WideScene {
     const uint32_t* objXform;  // object -> xformId
     uint32_t nXforms, nSpheres, nMaterials, nObjects;
     uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
+    uint32_t emisSphereMask;   // bit i: sphere slot i has an emissive material (valid when nSpheres <= 32)
 };
 
 // Traversal stack: at most one sibling group per level of the wide tree (<= PT_BVH8_MAX_DEPTH,

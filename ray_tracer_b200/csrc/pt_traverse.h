@@ -151,9 +151,16 @@ PT_HD PrimRecord load_prim(const PrimRecord* prims, uint32_t i) {
 // object's root (:324-348; the root's own box is never tested, :301-307). A box that contains the
 // object-space hit point h with a margin m far above the slab test's rounding error passes, and so
 // does every box around it.
-//   quick accept (no memory access): the triangle's own bounding box, rebuilt from the record
-//     (p0, p0+e1, p0+e2), contains h with margin m on every axis on which the LEAF is not flat
-//     (flags precomputed at upload). The leaf box and all its ancestors contain that box.
+//   quick accept (no memory access), from the triangle's own bounding box T rebuilt from the record
+//     (p0, p0+e1, p0+e2) — the leaf box and all its ancestors contain T:
+//     (a) h lies inside T with margin m on every axis on which the LEAF is not flat (flags
+//         precomputed at upload): every enclosing box passes a fortiori;
+//     (b) exactly one axis a fails (a): typically a wall triangle lying ON a face of its leaf box.
+//         On the other two axes the slab intervals of every enclosing box contain dst with a
+//         parametric margin m/|d_b|; on axis a the interval end is within (m/16 + rounding)/|d_a| of
+//         dst as long as h_a is within m/16 of T, and t1_a <= t2_a always. With
+//         |d_a| >= max(|d_b|, |d_c|)/4 that slack is below the others' margin, so
+//         tNear <= tFar and tFar > 0 hold for every enclosing box.
 //   otherwise: walk leaf -> root re-running the reference's slab test, stopping at the first box
 //     that contains h with the margin. Axes on which the leaf is flat (axis-aligned triangles) are
 //     exempt from the margin: there tMin == tMax is the plane distance itself and rounding is
@@ -173,7 +180,17 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
         const bool inX = flatX || (h.x >= lx + m && h.x <= hx - m);
         const bool inY = flatY || (h.y >= ly + m && h.y <= hy - m);
         const bool inZ = flatZ || (h.z >= lz + m && h.z <= hz - m);
-        if (inX && inY && inZ) return true;
+        const int nOut = (inX ? 0 : 1) + (inY ? 0 : 1) + (inZ ? 0 : 1);
+        if (nOut == 0) return true;
+        if (nOut == 1) {
+            const float m16 = m * 0.0625f;
+            const float ax = fabsf(c.r.d.x), ay = fabsf(c.r.d.y), az = fabsf(c.r.d.z);
+            bool ok;
+            if (!inX) ok = h.x >= lx - m16 && h.x <= hx + m16 && 4.f * ax >= fmaxf(ay, az);
+            else if (!inY) ok = h.y >= ly - m16 && h.y <= hy + m16 && 4.f * ay >= fmaxf(ax, az);
+            else ok = h.z >= lz - m16 && h.z <= hz + m16 && 4.f * az >= fmaxf(ax, ay);
+            if (ok) return true;
+        }
     }
     const v3 inv = mk3(1.f / c.r.d.x, 1.f / c.r.d.y, 1.f / c.r.d.z);   // raytrace.comp:294
     UpNode n = up[p.leafNode];

@@ -186,27 +186,55 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 // emissive closest hit (none found, or occluded). qA[p].w = material of the light-sample hit.
 #define PT_NO_EMISSIVE (-1.f)
 
+PT_HD int lowest_bit(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+// Sphere slots are split at upload into emissive / non-emissive bit masks (WideScene), so the two
+// loops below touch only the spheres that matter; with more than 32 slots every slot is visited.
 PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
                                uint32_t& matOut) {
     matOut = 0u; keyE = 0xffffffffu;
     if (!sc.anyEmissive) return PT_NO_EMISSIVE;
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
-    for (uint32_t i = 0; i < sphereCount; i++) {
-        const ptl::Sphere s = sc.spheres[i];
-        if (sc.materials[s.materialIndex].emissionStrength == 0.f) continue;
-        float dst; bool front;
-        if (sphere_test(s, r, dst, front) && dst < e.dst) { e.dst = dst; e.id = PT_HIT_SPHERE | i; keyE = i; matOut = s.materialIndex; }
+    const bool masks = sc.nSpheres <= 32u;
+    const uint32_t live = sphereCount >= 32u ? 0xffffffffu : ((1u << sphereCount) - 1u);
+    if (masks) {
+        for (uint32_t mk = sc.emisSphereMask & live; mk; mk &= mk - 1u) {
+            uint32_t i = (uint32_t)lowest_bit(mk);
+            const ptl::Sphere s = sc.spheres[i];
+            float dst; bool front;
+            if (sphere_test(s, r, dst, front) && dst < e.dst) { e.dst = dst; e.id = PT_HIT_SPHERE | i; keyE = i; matOut = s.materialIndex; }
+        }
+    } else {
+        for (uint32_t i = 0; i < sphereCount; i++) {
+            const ptl::Sphere s = sc.spheres[i];
+            if (sc.materials[s.materialIndex].emissionStrength == 0.f) continue;
+            float dst; bool front;
+            if (sphere_test(s, r, dst, front) && dst < e.dst) { e.dst = dst; e.id = PT_HIT_SPHERE | i; keyE = i; matOut = s.materialIndex; }
+        }
     }
     uint32_t before = e.id;
-    bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
+    if (sc.emis.nPrims) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
     if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
-    for (uint32_t i = 0; i < sphereCount; i++) {
-        const ptl::Sphere s = sc.spheres[i];
-        if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
-        float dst; bool front;
-        if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
+    if (masks) {
+        for (uint32_t mk = ~sc.emisSphereMask & live; mk; mk &= mk - 1u) {
+            uint32_t i = (uint32_t)lowest_bit(mk);
+            float dst; bool front;
+            if (sphere_test(sc.spheres[i], r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
+        }
+    } else {
+        for (uint32_t i = 0; i < sphereCount; i++) {
+            const ptl::Sphere s = sc.spheres[i];
+            if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
+            float dst; bool front;
+            if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
+        }
     }
     return e.dst;
 }

@@ -383,6 +383,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
     s.anyEmissive = host.anyEmissive ? 1u : 0u;
+    s.emisSphereMask = host.emisSphereMask;
     w->maxDepth = host.all.maxDepth;
     return 0;
 }
