@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--pipeline", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="480x270x8", help="WxHxframes of the CPU baseline sample")
+    ap.add_argument("--opt", action="append", default=[], help="backend option key=value (b200pt_set_option), repeatable")
     ap.add_argument("--dump", default=None, help="write the final mean image as .npy (rank 0)")
     return ap.parse_args()
 
@@ -228,6 +229,9 @@ def main():
     cp.set_stream(stream.cuda_stream)            # kernels run on torch's current stream: torch events time them
     cp.set_option("pipeline", args.pipeline)
     cp.set_option("frames_in_flight", max(1, min(64, F)))
+    for kv in args.opt:
+        k, v = kv.split("=")
+        cp.set_option(k, int(v))
     t_up = time.perf_counter()
     cp.copy_buffers(blobs)
     cp.sync()

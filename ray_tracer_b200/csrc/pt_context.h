@@ -54,6 +54,9 @@ struct b200pt_ctx {
     int pipeline = 1;
     int framesInFlight = 4;
     int profileStages = 0;
+    int triVote32 = 8;            // see WfParams
+    int fetchMinIdle = 8;
+    int sharePrimary = 1;         // trace the primary ray once per pixel and share the hit between frame slots (A-Q4)
 
     // counters (host side; device-side ray counters are folded in by the wavefront)
     uint64_t counters[16] = {0};

@@ -44,6 +44,9 @@ struct WfParams {
     uint32_t row0, rows;            // row band rendered
     uint32_t firstFrame, stride;    // slot k renders frameCount = firstFrame + k*stride
     uint32_t nSlots, nPaths;        // nPaths = nSlots * rows * W
+    uint32_t triVote32;             // persistent kernels: run a triangle step when >= triVote32/32 of the busy lanes hold triangles
+    uint32_t fetchMinIdle;          // ... refill a warp once this many lanes are idle
+    uint32_t sharePrimary;          // bounce 0: the hit of path p is stored at p % (rows * W) (one primary ray per pixel)
 };
 
 PT_HD v3 xyz(const float4& f) { return mk3(f.x, f.y, f.z); }
@@ -113,7 +116,7 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
     float misWeight = ro.w;
     uint32_t state = as_uint(rd.w);
     v3 total = xyz(A.total[p]), atten = xyz(A.atten[p]), direct = xyz(A.direct[p]);
-    const Hit h = A.hit[p];
+    const Hit h = A.hit[(j == 0 && P.sharePrimary) ? p % (P.rows * (uint32_t)P.W) : p];
 
     if (h.id == PT_HIT_MISS) {                                   // raytrace.comp:531-534
         total = total + atten * environment_light(P.pc.env, ray.d);

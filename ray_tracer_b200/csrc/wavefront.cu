@@ -87,12 +87,13 @@ static __device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pre
     return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
 }
 
-__global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__ WfParams P, PathArrays A, uint32_t* queue, uint32_t* qCount) {
+__global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__ WfParams P, PathArrays A, uint32_t* queue, uint32_t* qCount,
+                                                         uint32_t* primaryCount) {
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < P.nPaths; p += gridDim.x * blockDim.x) {
         stage_generate(P, A, p);
         queue[p] = p;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) qCount[0] = P.nPaths;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { qCount[0] = P.nPaths; *primaryCount = P.rows * (uint32_t)P.W; }
 }
 
 // ---- persistent traversal kernels ------------------------------------------------------------
@@ -129,9 +130,15 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     return got;
 }
 
+// One vote per iteration: a single warp reduction of (busy | holds triangles << 8 | can visit a node << 16)
+// gives the three lane counts the schedule needs.
+static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bool canNode) {
+    return __reduce_add_sync(0xffffffffu, (busy ? 1u : 0u) | (hasTri ? 0x100u : 0u) | (canNode ? 0x10000u : 0u));
+}
+
 __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
-                                                       uint32_t* workCounter) {
+                                                       uint32_t* workCounter, Hit* __restrict__ hitOut) {
     const uint32_t n = *qCount;
     const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
     uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
@@ -145,13 +152,16 @@ __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ W
     for (;;) {
         // lanes with nothing in hand take the next group from their stack, or finish
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) {
-            A.hit[p] = hit;
+            hitOut[p] = hit;
             busy = false;
         }
-        unsigned idleMask = __ballot_sync(0xffffffffu, !busy);
-        if (idleMask != 0u && !feed.exhausted && (uint32_t)__popc(idleMask) >= PT_FETCH_MIN_IDLE) {
+        const bool hasTri = busy && trav_has_tri(t);
+        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        const unsigned votes = warp_votes(busy, hasTri, canNode);
+        const unsigned nBusy = votes & 0xffu, nTri = (votes >> 8) & 0xffu, nNode = votes >> 16;
+        if (!feed.exhausted && 32u - nBusy >= P.fetchMinIdle) {
             uint32_t qi;
-            if (feeder_take(feed, workCounter, n, idleMask, qi)) {
+            if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 p = queue[qi];
                 Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
                 hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f; key = 0xffffffffu;
@@ -164,17 +174,10 @@ __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ W
                 trav_begin(t, r);
                 busy = true;
             }
-            idleMask = __ballot_sync(0xffffffffu, !busy);
-        }
-        if (idleMask == 0xffffffffu) {
-            if (feed.exhausted) break;
             continue;
         }
-        const bool hasTri = busy && trav_has_tri(t);
-        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
-        const unsigned triMask = __ballot_sync(0xffffffffu, hasTri);
-        const unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
-        if (nodeMask == 0u || 4 * __popc(triMask) >= 32 - __popc(idleMask)) {
+        if (nBusy == 0u) break;                    // queue exhausted and every lane done
+        if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
             if (hasTri) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
         } else {
             if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, hit.dst);
@@ -232,27 +235,23 @@ __global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ 
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) busy = false;   // not occluded
-        unsigned idleMask = __ballot_sync(0xffffffffu, !busy);
-        if (idleMask != 0u && !feed.exhausted && (uint32_t)__popc(idleMask) >= PT_FETCH_MIN_IDLE) {
+        const bool hasTri = busy && trav_has_tri(t);
+        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
+        const unsigned votes = warp_votes(busy, hasTri, canNode);
+        const unsigned nBusy = votes & 0xffu, nTri = (votes >> 8) & 0xffu, nNode = votes >> 16;
+        if (!feed.exhausted && 32u - nBusy >= P.fetchMinIdle) {
             uint32_t qi;
-            if (feeder_take(feed, workCounter, n, idleMask, qi)) {
+            if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
                 Ray r;
                 connect_job_ray(A, job & 0x7fffffffu, job >> 31, r, tE, keyE);
                 trav_begin(t, r);
                 busy = true;
             }
-            idleMask = __ballot_sync(0xffffffffu, !busy);
-        }
-        if (idleMask == 0xffffffffu) {
-            if (feed.exhausted) break;
             continue;
         }
-        const bool hasTri = busy && trav_has_tri(t);
-        const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
-        const unsigned triMask = __ballot_sync(0xffffffffu, hasTri);
-        const unsigned nodeMask = __ballot_sync(0xffffffffu, canNode);
-        if (nodeMask == 0u || 4 * __popc(triMask) >= 32 - __popc(idleMask)) {
+        if (nBusy == 0u) break;
+        if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
             if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
                 connect_job_occluded(A, job & 0x7fffffffu, job >> 31);
                 busy = false;
@@ -419,7 +418,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
     }
     uint32_t need = bounces + 3;
     if (need > w->countSlots) {
-        WCU(wf_resize(w->dCounts, (size_t)need * 5 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
+        WCU(wf_resize(w->dCounts, (size_t)need * 6 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
@@ -450,12 +449,14 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     const int grid = w->smCount * 8;
     WfParams P;
     P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
+    P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
     uint32_t nB = pc.params.bounceLimit + 1;
     uint32_t* qCount = (uint32_t*)w->dCounts.p;
     uint32_t* sCount = qCount + w->countSlots;
     uint32_t* workE = sCount + w->countSlots;
     uint32_t* workO = workE + w->countSlots;
     uint32_t* oCount = workO + w->countSlots;
+    uint32_t* primaryCount = oCount + w->countSlots;
     if (!w->gridOcclude) {
         int perSm = 0;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude, WF_THREADS, 0));
@@ -470,15 +471,19 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         P.nSlots = std::min(slots, n - done);
         P.firstFrame = first + done * stride;
         P.nPaths = (uint32_t)(perSlot * P.nSlots);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 5 * 4, c->stream));
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 6 * 4, c->stream));
         uint32_t* qa = (uint32_t*)w->dQueue[0].p;
         uint32_t* qb = (uint32_t*)w->dQueue[1].p;
         if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
         wf_mark(c, ST_GENERATE);
-        k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount);
+        // the primary ray of a pixel is the same in every frame (no jitter: raytrace.comp:541, A-Q4): with several
+        // frame slots in a batch it is traced once (slot 0) and the hit is shared; shade reads hit[p % perSlot] at j = 0
+        P.sharePrimary = (c->sharePrimary && P.nSlots > 1) ? 1u : 0u;
+        k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount, primaryCount);
         for (uint32_t j = 0; j < nB; ++j) {
             wf_mark(c, ST_EXTEND);
-            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, workE + j);
+            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, (j == 0 && P.sharePrimary) ? primaryCount : qCount + j,
+                                                                  workE + j, w->arrays.hit);
             wf_mark(c, ST_SHADE);
             k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
