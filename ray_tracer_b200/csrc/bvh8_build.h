@@ -26,7 +26,7 @@ struct WideSceneHost {
     std::vector<uint32_t> objXform;
     std::vector<UpNode> up;
     bool anyEmissive = false;
-    uint32_t emisSphereMask = 0;
+    uint32_t uniqSphereMask = 0, emisSphereMask = 0, plainSphereMask = 0;
 };
 
 namespace b8 {
@@ -270,9 +270,20 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     using namespace b8;
     out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
     auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
-    out.emisSphereMask = 0;
-    for (size_t i = 0; i < spheres.size(); ++i)
-        if (emissive(spheres[i].materialIndex)) { out.anyEmissive = true; if (i < 32) out.emisSphereMask |= 1u << i; }
+    out.uniqSphereMask = out.emisSphereMask = out.plainSphereMask = 0;
+    for (size_t i = 0; i < spheres.size(); ++i) {
+        bool em = emissive(spheres[i].materialIndex);
+        if (em) out.anyEmissive = true;
+        if (i >= 32) continue;
+        bool firstAll = true, firstClass = true;
+        for (size_t k = 0; k < i; ++k) {
+            if (std::memcmp(&spheres[k], &spheres[i], 16) != 0) continue;      // px, py, pz, radius
+            firstAll = false;
+            if (emissive(spheres[k].materialIndex) == em) firstClass = false;
+        }
+        if (firstAll) out.uniqSphereMask |= 1u << i;
+        if (firstClass) (em ? out.emisSphereMask : out.plainSphereMask) |= 1u << i;
+    }
 
     // distinct object matrices (bit pattern): objects that share one share the transformed ray
     for (size_t o = 0; o < objects.size(); ++o) {

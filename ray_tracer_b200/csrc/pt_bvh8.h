@@ -81,7 +81,12 @@ struct WideScene {
     const uint32_t* objXform;  // object -> xformId
     uint32_t nXforms, nSpheres, nMaterials, nObjects;
     uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
-    uint32_t emisSphereMask;   // bit i: sphere slot i has an emissive material (valid when nSpheres <= 32)
+    // Sphere slot masks (valid when nSpheres <= 32). Slots with bit-identical (position, radius) give identical
+    // test results, and every loop of the reference keeps the FIRST of equal candidates, so only the lowest
+    // slot of each identical class is kept (the ten zero spheres of spheres.resize(10) collapse to one test).
+    uint32_t uniqSphereMask;   // closest-hit loop: first slot of each class
+    uint32_t emisSphereMask;   // first slot of each class among slots with an emissive material
+    uint32_t plainSphereMask;  // ... among slots with a non-emissive material
 };
 
 // Traversal stack: at most one sibling group per level of the wide tree (<= PT_BVH8_MAX_DEPTH,

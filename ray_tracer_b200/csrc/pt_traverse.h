@@ -160,7 +160,12 @@ PT_HD PrimRecord load_prim(const PrimRecord* prims, uint32_t i) {
 //         parametric margin m/|d_b|; on axis a the interval end is within (m/16 + rounding)/|d_a| of
 //         dst as long as h_a is within m/16 of T, and t1_a <= t2_a always. With
 //         |d_a| >= max(|d_b|, |d_c|)/4 that slack is below the others' margin, so
-//         tNear <= tFar and tFar > 0 hold for every enclosing box.
+//         tNear <= tFar and tFar > 0 hold for every enclosing box. When the TRIANGLE itself is flat
+//         on axis a (all three vertices share p0_a, so e1_a == e2_a == 0 exactly) no bound on d_a is
+//         needed: dst = (o_a - p0_a) n_a / -(d_a n_a) and the slab value of the plane p0_a,
+//         (p0_a - o_a) * (1/d_a), start from the same rounded difference and agree to 4e-7 * dst,
+//         rounding is monotone in the box coordinate so t1_a <= that value <= t2_a for every box
+//         around the plane, and the other axes' margins are >= 2e-5 * dst.
 //   otherwise: walk leaf -> root re-running the reference's slab test, stopping at the first box
 //     that contains h with the margin. Axes on which the leaf is flat (axis-aligned triangles) are
 //     exempt from the margin: there tMin == tMax is the plane distance itself and rounding is
@@ -186,9 +191,9 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
             const float m16 = m * 0.0625f;
             const float ax = fabsf(c.r.d.x), ay = fabsf(c.r.d.y), az = fabsf(c.r.d.z);
             bool ok;
-            if (!inX) ok = h.x >= lx - m16 && h.x <= hx + m16 && 4.f * ax >= fmaxf(ay, az);
-            else if (!inY) ok = h.y >= ly - m16 && h.y <= hy + m16 && 4.f * ay >= fmaxf(ax, az);
-            else ok = h.z >= lz - m16 && h.z <= hz + m16 && 4.f * az >= fmaxf(ax, ay);
+            if (!inX) ok = h.x >= lx - m16 && h.x <= hx + m16 && ((lx == hx && ax >= 1e-30f) || 4.f * ax >= fmaxf(ay, az));
+            else if (!inY) ok = h.y >= ly - m16 && h.y <= hy + m16 && ((ly == hy && ay >= 1e-30f) || 4.f * ay >= fmaxf(ax, az));
+            else ok = h.z >= lz - m16 && h.z <= hz + m16 && ((lz == hz && az >= 1e-30f) || 4.f * az >= fmaxf(ax, ay));
             if (ok) return true;
         }
     }

@@ -68,15 +68,37 @@ PT_HD void stage_generate(const WfParams& P, const PathArrays& A, uint32_t p) {
 }
 
 // ---- extend ---------------------------------------------------------------------------------
-PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount) {
-    Hit h; h.dst = PT_FAR; h.id = PT_HIT_MISS; h.u = 0.f; h.v = 0.f;
-    uint32_t key = 0xffffffffu;
-    for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
-        float dst; bool front;
-        if (sphere_test(sc.spheres[i], ray, dst, front) && dst < h.dst) {
-            h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
+PT_HD int lowest_bit(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+    return __ffs((int)x) - 1;
+#else
+    return __builtin_ctz(x);
+#endif
+}
+PT_HD uint32_t live_sphere_mask(uint32_t sphereCount) { return sphereCount >= 32u ? 0xffffffffu : ((1u << sphereCount) - 1u); }
+// raytrace.comp:282-287: closest sphere, first of equal distances (see WideScene for the slot masks)
+PT_HD void spheres_closest(const WideScene& sc, const Ray& ray, uint32_t sphereCount, Hit& h, uint32_t& key) {
+    h.dst = PT_FAR; h.id = PT_HIT_MISS; h.u = 0.f; h.v = 0.f; key = 0xffffffffu;
+    if (sc.nSpheres <= 32u) {
+        for (uint32_t mk = sc.uniqSphereMask & live_sphere_mask(sphereCount); mk; mk &= mk - 1u) {
+            uint32_t i = (uint32_t)lowest_bit(mk);
+            float dst; bool front;
+            if (sphere_test(sc.spheres[i], ray, dst, front) && dst < h.dst) {
+                h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
+            }
+        }
+    } else {
+        for (uint32_t i = 0; i < sphereCount; i++) {
+            float dst; bool front;
+            if (sphere_test(sc.spheres[i], ray, dst, front) && dst < h.dst) {
+                h.dst = dst; h.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
+            }
         }
     }
+}
+PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount) {
+    Hit h; uint32_t key;
+    spheres_closest(sc, ray, sphereCount, h, key);
     bvh8_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, ray, objectCount, h, key);
     return h;
 }
@@ -189,13 +211,6 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 // emissive closest hit (none found, or occluded). qA[p].w = material of the light-sample hit.
 #define PT_NO_EMISSIVE (-1.f)
 
-PT_HD int lowest_bit(uint32_t x) {
-#if defined(__CUDA_ARCH__)
-    return __ffs((int)x) - 1;
-#else
-    return __builtin_ctz(x);
-#endif
-}
 // Sphere slots are split at upload into emissive / non-emissive bit masks (WideScene), so the two
 // loops below touch only the spheres that matter; with more than 32 slots every slot is visited.
 PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
@@ -205,7 +220,7 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
     const bool masks = sc.nSpheres <= 32u;
-    const uint32_t live = sphereCount >= 32u ? 0xffffffffu : ((1u << sphereCount) - 1u);
+    const uint32_t live = live_sphere_mask(sphereCount);
     if (masks) {
         for (uint32_t mk = sc.emisSphereMask & live; mk; mk &= mk - 1u) {
             uint32_t i = (uint32_t)lowest_bit(mk);
@@ -226,7 +241,7 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
     if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
     if (masks) {
-        for (uint32_t mk = ~sc.emisSphereMask & live; mk; mk &= mk - 1u) {
+        for (uint32_t mk = sc.plainSphereMask & live; mk; mk &= mk - 1u) {
             uint32_t i = (uint32_t)lowest_bit(mk);
             float dst; bool front;
             if (sphere_test(sc.spheres[i], r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;

@@ -164,13 +164,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ W
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 p = queue[qi];
                 Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-                hit.dst = PT_FAR; hit.id = PT_HIT_MISS; hit.u = 0.f; hit.v = 0.f; key = 0xffffffffu;
-                for (uint32_t i = 0; i < sphereCount; i++) {      // raytrace.comp:282-287
-                    float dst; bool front;
-                    if (sphere_test(sc.spheres[i], r, dst, front) && dst < hit.dst) {
-                        hit.dst = dst; hit.id = PT_HIT_SPHERE | (front ? PT_HIT_FRONT : 0u) | i; key = i;
-                    }
-                }
+                spheres_closest(sc, r, sphereCount, hit, key);
                 trav_begin(t, r);
                 busy = true;
             }
@@ -382,7 +376,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
     s.anyEmissive = host.anyEmissive ? 1u : 0u;
-    s.emisSphereMask = host.emisSphereMask;
+    s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
     w->maxDepth = host.all.maxDepth;
     return 0;
 }

@@ -40,7 +40,7 @@ void* emu_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     v.objXform = s->wide.objXform.data();
     v.nXforms = (uint32_t)s->wide.xforms.size(); v.nSpheres = nS; v.nMaterials = nM; v.nObjects = nO;
     v.anyEmissive = s->wide.anyEmissive ? 1u : 0u;
-    v.emisSphereMask = s->wide.emisSphereMask;
+    v.uniqSphereMask = s->wide.uniqSphereMask; v.emisSphereMask = s->wide.emisSphereMask; v.plainSphereMask = s->wide.plainSphereMask;
     return s;
 }
 void emu_scene_destroy(void* s) { delete (EmuScene*)s; }
