@@ -52,7 +52,7 @@ def parse_args():
     ap.add_argument("--obj", default=None, help="path of a real sponza.obj (optional; replaces the stand-in)")
     ap.add_argument("--pipeline", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample", default="480x270x8", help="WxHxframes of the CPU baseline sample")
+    ap.add_argument("--cpu-sample", default="960x540x12", help="WxHxframes of the CPU baseline sample")
     ap.add_argument("--opt", action="append", default=[], help="backend option key=value (b200pt_set_option), repeatable")
     ap.add_argument("--dump", default=None, help="write the final mean image as .npy (rank 0)")
     return ap.parse_args()
@@ -246,15 +246,16 @@ def main():
     pcbuf = pc.buffer
     frame_cursor = [0]
 
+    from ray_tracer_b200 import multi_gpu
+
     def step(e2e=False):
         f0 = frame_cursor[0]
         frame_cursor[0] += F * N
-        cp.render_frames(pcbuf, f0 + rank, F, frame_stride=N)      # host push constants -> one batch of F frames
         if N > 1:
-            dist.reduce(stepbuf, dst=0)                            # NCCL sum over NVLink onto rank 0
-            if rank == 0:
-                total.add_(stepbuf)
-            stepbuf.zero_()
+            # rank r renders frames f0 + r, f0 + r + N, ... (F of them); NCCL sum over NVLink onto rank 0's running total
+            multi_gpu.render_frames_split(cp, pcbuf, f0, F * N, stepbuf, total)
+        else:
+            cp.render_frames(pcbuf, f0, F)                         # host push constants -> one batch of F frames
         if e2e and rank == 0:
             if N > 1:
                 pinned.copy_(total, non_blocking=True)
