@@ -105,21 +105,22 @@ def algorithmic_bytes(work, paths):
 
 
 def oracle_sample(blobs, pc, args, sample, threads=0):
-    """Runs the CPU restatement on a bounded sample: same scene and camera at a sub-sampled pixel grid.
+    """Runs the CPU restatement on a bounded sample of the SAME workload: every (W/w)-th pixel in x and (H/h)-th in y
+    of the real W x H image (the full image's rays and seeds), `n` frames; sample = "wxhxn".
     -> dict(mpaths, seconds, paths, work_all, work_ext, cores)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import numpy as np
     import oracle_binding as ob
     w, h, n = (int(x) for x in sample.lower().split("x"))
-    rec = pc.rec.copy()
-    rec["aspectRatio"] = np.float32(w) / np.float32(h)
+    W, H = args.width, args.height
+    sx, sy = max(1, W // w), max(1, H // h)
+    w, h = min(w, (W + sx - 1) // sx), min(h, (H + sy - 1) // sy)
     sc = ob.OracleScene(blobs)
     t0 = time.perf_counter()
-    _, work_all, work_ext = sc.render_frames_work(rec.tobytes(), w, h, 0, n, threads=threads)
+    _, work_all, work_ext = sc.render_window(pc.buffer, W, H, 0, 0, 0, w, h, n=n, sx=sx, sy=sy, threads=threads, want_work=True)
     dt = time.perf_counter() - t0
     paths = w * h * n
     return dict(mpaths=paths / dt / 1e6, seconds=dt, paths=paths, work_all=work_all, work_ext=work_ext,
-                cores=threads or (os.cpu_count() or 1))
+                cores=threads or (os.cpu_count() or 1), lattice="%dx%d pixels (every %d-th column, %d-th row of the %dx%d image) x %d frames" % (w, h, sx, sy, W, H, n))
 
 
 class ClockSampler:
@@ -190,7 +191,7 @@ def run_reference(args, rank, world):
                ms_per_step=secs / args.steps * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
                data="synthetic", config=cfg,
                cpu_baseline=dict(value=v, unit=UNIT, cores=cores, kind="port",
-                                 sample="%s (WxHxframes, same scene+camera, pixel grid sub-sampled) per step, OpenMP all cores" % sample),
+                                 sample="%s per step, OpenMP over rows, all host cores" % r["lattice"]),
                e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
     print(json.dumps(out), flush=True)
 
@@ -318,7 +319,7 @@ def main():
         if N == 1 and not args.no_cpu_baseline:
             r = oracle_sample(blobs, pc, args, args.cpu_sample)
             cpu = dict(value=r["mpaths"], unit=UNIT, cores=r["cores"], kind="port",
-                       sample="%s (WxHxframes; same scene+camera, pixel grid sub-sampled; %.1f s, OpenMP over rows)" % (args.cpu_sample, r["seconds"]))
+                       sample="%s; %.1f s, OpenMP over rows, all host cores" % (r["lattice"], r["seconds"]))
         else:
             r = oracle_sample(blobs, pc, args, "240x135x1")
         b_all = algorithmic_bytes(r["work_all"], r["paths"]) + 32.0
@@ -340,7 +341,16 @@ def main():
             traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
         except (OSError, ValueError):
             pass
-        roofline = dict(bound="hbm", kernel="k_" + dom, achieved=achieved, peak=peak, unit="GB/s",
+        # second candidate bound of SURVEY.md §8(d3): FP32 issue. Flops per path of the extension rays in the
+        # reference's formulation: 24/box test, 64/triangle test, 20/sphere test, 150/object visit.
+        wx = r["work_ext"]
+        flops_ext = (24.0 * wx["n_box"] + 64.0 * wx["n_tri"] + 20.0 * wx["n_sph"] + 150.0 * wx["n_obj"]) / max(r["paths"], 1)
+        ext_ms = stages["extend"][0]
+        fp32 = dict(achieved=flops_ext * paths_rank / (ext_ms * 1e-3) / 1e12 if ext_ms > 0 else None, peak=74.4, unit="TFLOP/s",
+                    kernel="k_extend", peak_source="nominal 148 SM x 128 lanes x 2 x 1.965 GHz (not measured)",
+                    algorithmic_flops_per_path=flops_ext)
+        fp32["frac"] = fp32["achieved"] / fp32["peak"] if fp32["achieved"] else None
+        roofline = dict(bound="hbm", kernel="k_" + dom, fp32_issue=fp32, achieved=achieved, peak=peak, unit="GB/s",
                         frac=(achieved / peak) if achieved else None, traffic=traffic,
                         peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                         algorithmic_bytes_per_path=dict(all_rays=b_all, extension_rays=b_ext, nee_and_pdf_rays=b_con),

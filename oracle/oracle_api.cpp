@@ -76,6 +76,19 @@ int orc_render_frames2(void* scene, const void* pc208, int W, int H, uint32_t fi
     return 0;
 }
 
+// window / pixel lattice of the full W x H image (see render_window); work16 as orc_render_frames2
+int orc_render_window(void* scene, const void* pc208, int W, int H, uint32_t first, uint32_t n, int x0, int y0, int w, int h,
+                      int sx, int sy, float* accum, uint64_t* work16, int threads) {
+    if (w < 0 || h < 0 || sx < 1 || sy < 1 || x0 < 0 || y0 < 0) return 1;
+    ol::PushConstants pc;
+    std::memcpy(&pc, pc208, sizeof(pc));
+    Work wk, e;
+    render_window(*(Scene*)scene, pc, W, H, first, n, x0, y0, w, h, sx, sy, accum, &wk, threads, &e);
+    work_out(wk, work16);
+    work_out(e, work16 ? work16 + 8 : nullptr);
+    return 0;
+}
+
 int orc_trace_batch(void* scene, const void* pc208, const float* rays, uint64_t n, void* hits48, uint64_t* work8,
                     int threads) {
     ol::PushConstants pc;

@@ -590,6 +590,39 @@ void render_frames(const Scene& sc, const ol::PushConstants& pc_in, int W, int H
     if (workExt) workExt->add(totalExt);
 }
 
+// Pixels (x0 + i*sx, y0 + j*sy), i < w, j < h, of the W x H image (seeds and rays are those of the full
+// image: raytrace.comp:541,562-564), frames first .. first+n-1, accumulated into a w x h x 4 buffer. Lets the
+// tests and the timed CPU baseline look at full-resolution configurations through a window or a pixel lattice.
+void render_window(const Scene& sc, const ol::PushConstants& pc_in, int W, int H, uint32_t first, uint32_t n, int x0, int y0,
+                   int w, int h, int sx, int sy, float* accum, Work* work, int threads, Work* workExt) {
+    Work total, totalExt;
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#endif
+    for (uint32_t f = first; f < first + n; ++f) {
+        ol::PushConstants pc = pc_in;
+        pc.frameCount = f;
+#pragma omp parallel
+        {
+            Ctx cx{sc, pc, Work(), Work()};
+#pragma omp for schedule(dynamic, 1)
+            for (int j = 0; j < h; ++j) {
+                for (int i = 0; i < w; ++i) {
+                    size_t p = size_t(j) * w + i;
+                    PixelOut po = shade_pixel(cx, uint32_t(x0 + i * sx), uint32_t(y0 + j * sy), W, H);
+                    vec3 c = po.outColor;
+                    if (isnan3(c) || isinf3(c)) c = vec3(1.f, 0.f, 1.f);
+                    accum[4 * p] += c.x; accum[4 * p + 1] += c.y; accum[4 * p + 2] += c.z; accum[4 * p + 3] += 1.f;
+                }
+            }
+#pragma omp critical
+            { total.add(cx.work); totalExt.add(cx.ext); }
+        }
+    }
+    if (work) work->add(total);
+    if (workExt) workExt->add(totalExt);
+}
+
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out, Work* work,
                  int threads) {
     Work total;

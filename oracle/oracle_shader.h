@@ -65,6 +65,8 @@ void render_dispatch(const Scene& sc, const ol::PushConstants& pc, int W, int H,
 
 // Throughput form: frames first..first+n-1 with frameCount=f; accum.rgb += outColor_f
 // (non-finite outColor contributes magenta, mirroring raytrace.comp:579-581); accum.a += 1.
+void render_window(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t first, uint32_t n, int x0, int y0,
+                   int w, int h, int sx, int sy, float* accum, Work* work = nullptr, int threads = 0, Work* workExt = nullptr);
 void render_frames(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t first, uint32_t n,
                    float* accum, Work* work, int threads, Work* workExt = nullptr);
 

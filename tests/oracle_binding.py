@@ -42,6 +42,7 @@ def lib():
         L.orc_render_dispatch.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, i32]
         L.orc_render_frames.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
         L.orc_render_frames2.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
+        L.orc_render_window.argtypes = [vp, vp, i32, i32, u32, u32, i32, i32, i32, i32, i32, i32, vp, vp, i32]
         L.orc_trace_batch.argtypes = [vp, vp, vp, u64, vp, vp, i32]
         L.orc_random.restype = f32
         L.orc_random.argtypes = [C.POINTER(u32)]
@@ -130,6 +131,17 @@ class OracleScene:
         work = np.zeros(16, np.uint64)
         lib().orc_render_frames2(self.h, _ptr(pcb), W, H, first, n, _ptr(accum), _ptr(work), threads)
         return accum, dict(zip(WORK_FIELDS, work[:8].tolist())), dict(zip(WORK_FIELDS, work[8:].tolist()))
+
+    def render_window(self, pc, W, H, first, x0, y0, w, h, n=1, sx=1, sy=1, threads=0, want_work=False):
+        """Pixels (x0 + i*sx, y0 + j*sy) of the W x H image, frames first..first+n-1 -> (h, w, 4) accumulator."""
+        pcb = self._pc(pc)
+        accum = np.zeros((h, w, 4), np.float32)
+        work = np.zeros(16, np.uint64)
+        rc = lib().orc_render_window(self.h, _ptr(pcb), W, H, first, n, x0, y0, w, h, sx, sy, _ptr(accum), _ptr(work), threads)
+        assert rc == 0
+        if want_work:
+            return accum, dict(zip(WORK_FIELDS, work[:8].tolist())), dict(zip(WORK_FIELDS, work[8:].tolist()))
+        return accum
 
     def trace_batch(self, pc, rays, threads=0):
         pcb = self._pc(pc)

@@ -242,3 +242,13 @@ def test_trace_batch_against_bruteforce(bunny_blobs):
     close = np.isclose(got[finite], best[finite], rtol=1e-3, atol=1e-4)
     assert close.mean() > 0.99, close.mean()      # grazing/edge rays may differ between f32 and f64
     assert (hits["kind"] != 1).all()              # bunny scene has only zero-radius spheres
+
+
+def test_render_window_is_a_view_of_the_full_image(cornell_blobs):
+    # orc_render_window: windows and pixel lattices of the W x H image carry the full image's rays and seeds
+    W, H = 64, 48
+    pc = ob.default_push_constants(W, H, 10, 9)
+    sc = ob.OracleScene(cornell_blobs)
+    full, _ = sc.render_frames(pc, W, H, 2, 2)
+    assert np.array_equal(sc.render_window(pc, W, H, 2, 10, 7, 20, 15, n=2), full[7:22, 10:30])
+    assert np.array_equal(sc.render_window(pc, W, H, 2, 0, 0, 32, 24, n=2, sx=2, sy=2), full[::2, ::2])
