@@ -114,13 +114,15 @@ def oracle_sample(blobs, pc, args, sample, threads=0):
     W, H = args.width, args.height
     sx, sy = max(1, W // w), max(1, H // h)
     w, h = min(w, (W + sx - 1) // sx), min(h, (H + sy - 1) // sy)
+    # torchrun exports OMP_NUM_THREADS=1: ask for the cores this process may run on explicitly
+    threads = threads or len(os.sched_getaffinity(0))
     sc = ob.OracleScene(blobs)
     t0 = time.perf_counter()
     _, work_all, work_ext = sc.render_window(pc.buffer, W, H, 0, 0, 0, w, h, n=n, sx=sx, sy=sy, threads=threads, want_work=True)
     dt = time.perf_counter() - t0
     paths = w * h * n
     return dict(mpaths=paths / dt / 1e6, seconds=dt, paths=paths, work_all=work_all, work_ext=work_ext,
-                cores=threads or (os.cpu_count() or 1), lattice="%dx%d pixels (every %d-th column, %d-th row of the %dx%d image) x %d frames" % (w, h, sx, sy, W, H, n))
+                cores=threads, lattice="%dx%d pixels (every %d-th column, %d-th row of the %dx%d image) x %d frames" % (w, h, sx, sy, W, H, n))
 
 
 class ClockSampler:
