@@ -79,19 +79,30 @@ PT_HD float byte_as_unit_float(uint32_t word, int k) {
 
 // Slab-test the 8 children of a node; returns hit bits: inner children in bits 24..31 ordered by
 // traversal priority for this ray's octant, leaf triangles in bits 0..23 (offset from primBase).
-// A child plane is at t = (p + q * 2^(e-127) - o) * rd = Q * S + O with Q = 1 + q * 2^-15,
-// S = 2^(e-112) * rd and O = (p - o) * rd - S: one FMA per plane. O carries one extra rounding of
-// at most |S| * 2^-23 (a 1/256 of a quantisation step); near planes are moved down and far planes
-// up by twice that, so the test stays conservative.
+// A child plane is at t = (p + q * 2^(e-127) - o) * rd = q * s + o with s = 2^(e-127) * rd, o = (p - o) * rd;
+// in mantissa form = Q * S + O with Q = 1 + q * 2^-15, S = 2^15 * s and O = o - S: one FMA per plane
+// either way. O carries extra rounding of at most |S| * 2^-23 (a 1/256 of a quantisation step); planes
+// evaluated in that form (the entry planes) are moved down by twice that, so the test stays conservative.
+PT_HD float byte_to_float(uint32_t word, int k) {
+#if defined(__CUDA_ARCH__)
+    return __uint2float_rn((word >> (8 * k)) & 0xffu);        // I2F.U8 with a byte selector: one instruction on the XU pipe
+#else
+    return (float)((word >> (8 * k)) & 0xffu);
+#endif
+}
 PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) {
-    const float sx = as_float(((n.w[3] & 0xffu) + 15u) << 23) * br.rd.x;
-    const float sy = as_float((((n.w[3] >> 8) & 0xffu) + 15u) << 23) * br.rd.y;
-    const float sz = as_float((((n.w[3] >> 16) & 0xffu) + 15u) << 23) * br.rd.z;
-    const float ox = pt_fma(as_float(n.w[0]) - br.o.x, br.rd.x, -sx);
-    const float oy = pt_fma(as_float(n.w[1]) - br.o.y, br.rd.y, -sy);
-    const float oz = pt_fma(as_float(n.w[2]) - br.o.z, br.rd.z, -sz);
-    const float wx = fabsf(sx) * 2.384185791015625e-07f, wy = fabsf(sy) * 2.384185791015625e-07f, wz = fabsf(sz) * 2.384185791015625e-07f;   // 2^-22
-    const float onx = ox - wx, ofx = ox + wx, ony = oy - wy, ofy = oy + wy, onz = oz - wz, ofz = oz + wz;
+    // entry planes: mantissa form Q * S + O (PRMT on the ALU pipe + FFMA); exit planes: q * s + o with q converted by
+    // I2F (XU pipe + FFMA) — the ALU pipe is this kernel's busiest unit (ncu: 68 %), the XU pipe is nearly idle.
+    const float sx = as_float((n.w[3] & 0xffu) << 23) * br.rd.x;
+    const float sy = as_float(((n.w[3] >> 8) & 0xffu) << 23) * br.rd.y;
+    const float sz = as_float(((n.w[3] >> 16) & 0xffu) << 23) * br.rd.z;
+    const float Sx = sx * 32768.f, Sy = sy * 32768.f, Sz = sz * 32768.f;
+    const float ofx = (as_float(n.w[0]) - br.o.x) * br.rd.x;
+    const float ofy = (as_float(n.w[1]) - br.o.y) * br.rd.y;
+    const float ofz = (as_float(n.w[2]) - br.o.z) * br.rd.z;
+    const float onx = pt_fma(fabsf(Sx), -2.384185791015625e-07f, ofx - Sx);      // O - |S| * 2^-22
+    const float ony = pt_fma(fabsf(Sy), -2.384185791015625e-07f, ofy - Sy);
+    const float onz = pt_fma(fabsf(Sz), -2.384185791015625e-07f, ofz - Sz);
     const bool negx = br.rd.x < 0.f, negy = br.rd.y < 0.f, negz = br.rd.z < 0.f;
     const uint32_t nx[2] = {negx ? n.w[14] : n.w[8], negx ? n.w[15] : n.w[9]}, fx[2] = {negx ? n.w[8] : n.w[14], negx ? n.w[9] : n.w[15]};
     const uint32_t ny[2] = {negy ? n.w[16] : n.w[10], negy ? n.w[17] : n.w[11]}, fy[2] = {negy ? n.w[10] : n.w[16], negy ? n.w[11] : n.w[17]};
@@ -108,9 +119,9 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
         const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            float t0x = pt_fma(byte_as_unit_float(nx[h], k), sx, onx), t1x = pt_fma(byte_as_unit_float(fx[h], k), sx, ofx);
-            float t0y = pt_fma(byte_as_unit_float(ny[h], k), sy, ony), t1y = pt_fma(byte_as_unit_float(fy[h], k), sy, ofy);
-            float t0z = pt_fma(byte_as_unit_float(nz[h], k), sz, onz), t1z = pt_fma(byte_as_unit_float(fz[h], k), sz, ofz);
+            float t0x = pt_fma(byte_as_unit_float(nx[h], k), Sx, onx), t1x = pt_fma(byte_to_float(fx[h], k), sx, ofx);
+            float t0y = pt_fma(byte_as_unit_float(ny[h], k), Sy, ony), t1y = pt_fma(byte_to_float(fy[h], k), sy, ofy);
+            float t0z = pt_fma(byte_as_unit_float(nz[h], k), Sz, onz), t1z = pt_fma(byte_to_float(fz[h], k), sz, ofz);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (tn <= tf) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);
