@@ -42,7 +42,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("B200PT_LIB") or LIB_PATH      # B200PT_LIB: A/B builds of the same library (profiling)
     if not os.path.exists(p):
         raise BackendError("%s not found: build it with `python -m ray_tracer_b200.build` (nvcc, sm_100a); "
                            "this backend has no CPU fallback" % p)

@@ -52,13 +52,14 @@ def build_host(force=False, verbose=False):
     return HOST_LIB
 
 
-def build(force=False, verbose=False, extra=()):
+def build(force=False, verbose=False, extra=(), out=None):
+    """out: alternative output path (A/B variants with -D flags in `extra`; loaded with B200PT_LIB=<path>)."""
     build_host(force=force, verbose=verbose)
-    if not force and not needs_build():
+    if out is None and not force and not needs_build():
         return LIB
     env = dict(os.environ)
     env.pop("CXX", None)    # the image's $CXX points at a g++ without its spec files
-    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-ccbin", "/usr/bin/g++", "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-ccbin", "/usr/bin/g++", "-o", out or LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     if verbose:
         print(" ".join(cmd))
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
@@ -66,7 +67,7 @@ def build(force=False, verbose=False, extra=()):
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
     if verbose:
         print(r.stdout + r.stderr)
-    return LIB
+    return out or LIB
 
 
 if __name__ == "__main__":

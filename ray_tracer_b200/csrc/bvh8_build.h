@@ -27,6 +27,8 @@ struct WideSceneHost {
     std::vector<UpNode> up;
     bool anyEmissive = false;
     uint32_t uniqSphereMask = 0, emisSphereMask = 0, plainSphereMask = 0;
+    bool emissionFinite = true;
+    float emisLo[3] = {0, 0, 0}, emisHi[3] = {0, 0, 0};
 };
 
 namespace b8 {
@@ -370,6 +372,17 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
             boxes.push_back(bx); inst.push_back({(uint32_t)o, t}); prim.push_back(r); shade.push_back(s);
             if (em) { boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); }
+        }
+    }
+    out.emissionFinite = true;
+    for (const auto& m : materials)
+        for (int k = 0; k < 3; ++k) if (!std::isfinite(m.emissionColor[k] * m.emissionStrength)) out.emissionFinite = false;
+    {
+        b8::Box u; b8::box_reset(u);
+        for (const auto& bx : boxesE) b8::box_grow(u, bx);
+        for (int a = 0; a < 3; ++a) {
+            float mag = std::max(std::fabs(u.lo[a]), std::fabs(u.hi[a]));
+            out.emisLo[a] = u.lo[a] - (1e-4f * mag + 1e-6f); out.emisHi[a] = u.hi[a] + (1e-4f * mag + 1e-6f);
         }
     }
     bvh8_build(boxes, inst, prim, shade, out.all);

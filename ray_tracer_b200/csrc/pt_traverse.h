@@ -90,6 +90,22 @@ PT_HD float byte_to_float(uint32_t word, int k) {
     return (float)((word >> (8 * k)) & 0xffu);
 #endif
 }
+#ifndef PT_NODE_I2F_NEAR
+#define PT_NODE_I2F_NEAR 0        /* how many of the three entry-plane axes also go through I2F (tuning knob) */
+#endif
+#ifndef PT_NODE_IMAD_SELECT
+#define PT_NODE_IMAD_SELECT 0     /* pick near/far words with integer multiply-adds (FMA pipe) instead of SEL (ALU pipe) */
+#endif
+PT_HD uint32_t pick_word(bool neg, uint32_t ifNeg, uint32_t ifPos) {
+#if PT_NODE_IMAD_SELECT && defined(__CUDA_ARCH__)
+    uint32_t d, r, f = neg ? 1u : 0u;
+    asm("mad.lo.u32 %0, %1, 0xffffffff, %2;" : "=r"(d) : "r"(ifPos), "r"(ifNeg));      // ifNeg - ifPos
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(d), "r"(f), "r"(ifPos));
+    return r;
+#else
+    return neg ? ifNeg : ifPos;
+#endif
+}
 PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) {
     // entry planes: mantissa form Q * S + O (PRMT on the ALU pipe + FFMA); exit planes: q * s + o with q converted by
     // I2F (XU pipe + FFMA) — the ALU pipe is this kernel's busiest unit (ncu: 68 %), the XU pipe is nearly idle.
@@ -104,9 +120,9 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
     const float ony = pt_fma(fabsf(Sy), -2.384185791015625e-07f, ofy - Sy);
     const float onz = pt_fma(fabsf(Sz), -2.384185791015625e-07f, ofz - Sz);
     const bool negx = br.rd.x < 0.f, negy = br.rd.y < 0.f, negz = br.rd.z < 0.f;
-    const uint32_t nx[2] = {negx ? n.w[14] : n.w[8], negx ? n.w[15] : n.w[9]}, fx[2] = {negx ? n.w[8] : n.w[14], negx ? n.w[9] : n.w[15]};
-    const uint32_t ny[2] = {negy ? n.w[16] : n.w[10], negy ? n.w[17] : n.w[11]}, fy[2] = {negy ? n.w[10] : n.w[16], negy ? n.w[11] : n.w[17]};
-    const uint32_t nz[2] = {negz ? n.w[18] : n.w[12], negz ? n.w[19] : n.w[13]}, fz[2] = {negz ? n.w[12] : n.w[18], negz ? n.w[13] : n.w[19]};
+    const uint32_t nx[2] = {pick_word(negx, n.w[14], n.w[8]), pick_word(negx, n.w[15], n.w[9])}, fx[2] = {pick_word(negx, n.w[8], n.w[14]), pick_word(negx, n.w[9], n.w[15])};
+    const uint32_t ny[2] = {pick_word(negy, n.w[16], n.w[10]), pick_word(negy, n.w[17], n.w[11])}, fy[2] = {pick_word(negy, n.w[10], n.w[16]), pick_word(negy, n.w[11], n.w[17])};
+    const uint32_t nz[2] = {pick_word(negz, n.w[18], n.w[12]), pick_word(negz, n.w[19], n.w[13])}, fz[2] = {pick_word(negz, n.w[12], n.w[18]), pick_word(negz, n.w[13], n.w[19])};
     uint32_t hits = 0;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -119,9 +135,12 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
         const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            float t0x = pt_fma(byte_as_unit_float(nx[h], k), Sx, onx), t1x = pt_fma(byte_to_float(fx[h], k), sx, ofx);
-            float t0y = pt_fma(byte_as_unit_float(ny[h], k), Sy, ony), t1y = pt_fma(byte_to_float(fy[h], k), sy, ofy);
-            float t0z = pt_fma(byte_as_unit_float(nz[h], k), Sz, onz), t1z = pt_fma(byte_to_float(fz[h], k), sz, ofz);
+            float t0x = PT_NODE_I2F_NEAR > 0 ? pt_fma(byte_to_float(nx[h], k), sx, ofx) : pt_fma(byte_as_unit_float(nx[h], k), Sx, onx);
+            float t0y = PT_NODE_I2F_NEAR > 1 ? pt_fma(byte_to_float(ny[h], k), sy, ofy) : pt_fma(byte_as_unit_float(ny[h], k), Sy, ony);
+            float t0z = PT_NODE_I2F_NEAR > 2 ? pt_fma(byte_to_float(nz[h], k), sz, ofz) : pt_fma(byte_as_unit_float(nz[h], k), Sz, onz);
+            float t1x = pt_fma(byte_to_float(fx[h], k), sx, ofx);
+            float t1y = pt_fma(byte_to_float(fy[h], k), sy, ofy);
+            float t1z = pt_fma(byte_to_float(fz[h], k), sz, ofz);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (tn <= tf) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);

@@ -211,6 +211,18 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 // emissive closest hit (none found, or occluded). qA[p].w = material of the light-sample hit.
 #define PT_NO_EMISSIVE (-1.f)
 
+// Conservative slab test against the bounding box of all emissive triangles (the padded world boxes the small BVH
+// was built from, grown once more by 1e-4 relative at upload: far above this test's rounding). Most BSDF-sampled
+// rays miss it and skip the call into the traversal altogether.
+PT_HD bool ray_meets_box(const Ray& r, const float* lo, const float* hi) {
+    BoxRay b = make_box_ray(r);
+    float t0x = (lo[0] - b.o.x) * b.rd.x, t1x = (hi[0] - b.o.x) * b.rd.x;
+    float t0y = (lo[1] - b.o.y) * b.rd.y, t1y = (hi[1] - b.o.y) * b.rd.y;
+    float t0z = (lo[2] - b.o.z) * b.rd.z, t1z = (hi[2] - b.o.z) * b.rd.z;
+    float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), 0.f));
+    float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    return tn <= tf;
+}
 // Sphere slots are split at upload into emissive / non-emissive bit masks (WideScene), so the two
 // loops below touch only the spheres that matter; with more than 32 slots every slot is visited.
 PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
@@ -237,7 +249,7 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
         }
     }
     uint32_t before = e.id;
-    if (sc.emis.nPrims) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
+    if (sc.emis.nPrims && ray_meets_box(r, sc.emisLo, sc.emisHi)) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
     if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
     if (masks) {
@@ -259,14 +271,26 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 
 #define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
 #define PT_CONNECT_JOB_COSINE 2u    /* ... for the cosine-sample ray */
+// Light-sample ray whose result cannot matter: with Afac = albedo/pi * max(0, n.l) == 0 in all three components
+// (light below the surface's horizon, or a black surface) directLight = E * (Afac * g) is a zero whatever the ray
+// finds, as long as g = w1/pdf and E are finite: g is (pdf == 0 ? 0 : w1/pdf) with w1 <= 1, which is finite unless
+// pdf = dst^2 / (cos * 0.444) is NaN, i.e. cos == 0 — excluded by l.y != 0 (cos = -l.y, raytrace.comp:399) — and
+// E is finite when every material's emission is (WideScene::emissionFinite). The sign of that zero can differ
+// from the traced result; it is only ever added to totalColor, which is never -0 (it starts at +0).
+// About half of the NEE rays of an interior scene are of this kind; they are neither searched nor traced.
+PT_HD bool nee_cannot_contribute(const WideScene& sc, const float4& qa, v3 lightSample) {
+    return sc.emissionFinite && qa.x == 0.f && qa.y == 0.f && qa.z == 0.f && lightSample.y != 0.f;
+}
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
     v3 origin = xyz(A.qO[p]), lightSample = xyz(A.qL[p]), cosineSample = xyz(A.rayD[p]);
-    uint32_t keyL, keyC, matL, matC;
-    float tL = emissive_candidate(sc, origin, lightSample, td.sphereCount, td.objectCount, keyL, matL);     // :443-447
+    float4 qa = A.qA[p];
+    uint32_t keyL = 0xffffffffu, keyC, matL = 0u, matC;
+    float tL = PT_NO_EMISSIVE;
+    if (!nee_cannot_contribute(sc, qa, lightSample))
+        tL = emissive_candidate(sc, origin, lightSample, td.sphereCount, td.objectCount, keyL, matL);        // :443-447
     float tC = emissive_candidate(sc, origin, cosineSample, td.sphereCount, td.objectCount, keyC, matC);    // :453
     A.qE[p] = make_float4(tL, tC, as_float(keyL), as_float(keyC));
-    float4 qa = A.qA[p];
     qa.w = as_float(matL);
     A.qA[p] = qa;
     return (tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u) | (tC >= 0.f ? PT_CONNECT_JOB_COSINE : 0u);

@@ -376,6 +376,8 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
     s.anyEmissive = host.anyEmissive ? 1u : 0u;
+    s.emissionFinite = host.emissionFinite ? 1u : 0u;
+    for (int a = 0; a < 3; ++a) {     s.emisLo[a] = host.emisLo[a];     s.emisHi[a] = host.emisHi[a]; }
     s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
     w->maxDepth = host.all.maxDepth;
     return 0;
