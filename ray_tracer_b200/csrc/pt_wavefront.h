@@ -47,6 +47,7 @@ struct WfParams {
     uint32_t triVote32;             // persistent kernels: run a triangle step when >= triVote32/32 of the busy lanes hold triangles
     uint32_t fetchMinIdle;          // ... refill a warp once this many lanes are idle
     uint32_t sharePrimary;          // bounce 0: the hit of path p is stored at p % (rows * W) (one primary ray per pixel)
+    uint32_t connectAfterExtend;    // connect of bounce j runs after extend of bounce j+1 (A.hit is the NEXT hit)
 };
 
 PT_HD v3 xyz(const float4& f) { return mk3(f.x, f.y, f.z); }
@@ -270,7 +271,6 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 }
 
 #define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
-#define PT_CONNECT_JOB_COSINE 2u    /* ... for the cosine-sample ray */
 // Light-sample ray whose result cannot matter: with Afac = albedo/pi * max(0, n.l) == 0 in all three components
 // (light below the surface's horizon, or a black surface) directLight = E * (Afac * g) is a zero whatever the ray
 // finds, as long as g = w1/pdf and E are finite: g is (pdf == 0 ? 0 : w1/pdf) with w1 <= 1, which is finite unless
@@ -281,41 +281,45 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 PT_HD bool nee_cannot_contribute(const WideScene& sc, const float4& qa, v3 lightSample) {
     return sc.emissionFinite && qa.x == 0.f && qa.y == 0.f && qa.z == 0.f && lightSample.y != 0.f;
 }
+// The second lightSamplePDF call of diffuseBRDF (raytrace.comp:453, the BSDF-sampled direction) only feeds
+// misWeight, and misWeight is only read at the NEXT hit as emission / misWeight, which trace() uses only when
+// directLight.x == -1 (raytrace.comp:499-500; at j == 0 misWeight is still 1). After a diffuse bounce directLight is
+// the NEE result, so that pdf ray is dead unless the NEE result is EXACTLY -1.0f. It is therefore evaluated lazily:
+// stage_connect_finish reports that rare case and connect_mis_weight_exact() then runs both parts of the query.
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
-    v3 origin = xyz(A.qO[p]), lightSample = xyz(A.qL[p]), cosineSample = xyz(A.rayD[p]);
     float4 qa = A.qA[p];
-    uint32_t keyL = 0xffffffffu, keyC, matL = 0u, matC;
+    v3 lightSample = xyz(A.qL[p]);
+    uint32_t keyL = 0xffffffffu, matL = 0u;
     float tL = PT_NO_EMISSIVE;
-    if (!nee_cannot_contribute(sc, qa, lightSample))
-        tL = emissive_candidate(sc, origin, lightSample, td.sphereCount, td.objectCount, keyL, matL);        // :443-447
-    float tC = emissive_candidate(sc, origin, cosineSample, td.sphereCount, td.objectCount, keyC, matC);    // :453
-    A.qE[p] = make_float4(tL, tC, as_float(keyL), as_float(keyC));
+    // connectAfterExtend: bounce j+1 was already extended; directLight of bounce j is dropped when it missed (:531-534)
+    bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
+    if (!dropped && !nee_cannot_contribute(sc, qa, lightSample))
+        tL = emissive_candidate(sc, xyz(A.qO[p]), lightSample, td.sphereCount, td.objectCount, keyL, matL);  // :443-447
+    A.qE[p] = make_float4(tL, 0.f, as_float(keyL), 0.f);
     qa.w = as_float(matL);
     A.qA[p] = qa;
-    return (tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u) | (tC >= 0.f ? PT_CONNECT_JOB_COSINE : 0u);
+    return tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u;
 }
-// the occlusion query of job `which` (0 light sample, 1 cosine sample) of path p
-PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, uint32_t which, Ray& r, float& tE, uint32_t& keyE) {
+// the occlusion query of path p's light-sample ray
+PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, uint32_t& keyE) {
     float4 e = A.qE[p];
     r.o = xyz(A.qO[p]);
-    r.d = which ? xyz(A.rayD[p]) : xyz(A.qL[p]);
-    tE = which ? e.y : e.x;
-    keyE = as_uint(which ? e.w : e.z);
+    r.d = xyz(A.qL[p]);
+    tE = e.x;
+    keyE = as_uint(e.z);
 }
-PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p, uint32_t which) {
-    float* e = reinterpret_cast<float*>(&A.qE[p]);
-    e[which] = PT_NO_EMISSIVE;
+PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p) {
+    reinterpret_cast<float*>(&A.qE[p])[0] = PT_NO_EMISSIVE;
 }
-PT_HD void stage_connect_finish(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+// Returns true when misWeight is live (directLight.x == -1 exactly) and has to be computed.
+PT_HD bool stage_connect_finish(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     float4 qo = A.qO[p], ql = A.qL[p], qa = A.qA[p], qe = A.qE[p];
-    v3 lightSample = xyz(ql), cosineSample = xyz(A.rayD[p]);
-    float cosinePDF = qo.w, realCosinePDF = ql.w;
+    v3 lightSample = xyz(ql);
+    float cosinePDF = qo.w;
     bool lightIsClosest = qe.x >= 0.f;
     float realLightPDF = lightIsClosest ? light_pdf_from_dst(qe.x, lightSample) : 0.f;                      // :447
     float w1 = mis_weight(realLightPDF, cosinePDF);                                                        // :449-450
-    float lightPDF = qe.y >= 0.f ? light_pdf_from_dst(qe.y, cosineSample) : 0.f;                           // :453
-    float w2 = mis_weight(realCosinePDF, lightPDF);                                                        // :455-456
     v3 E = splat3(0.f);           // a non-emissive (or missing) closest hit contributes emission * 0
     if (lightIsClosest) {
         const ptl::Material lm = sc.materials[as_uint(qa.w)];
@@ -323,20 +327,31 @@ PT_HD void stage_connect_finish(const WfParams& P, const WideScene& sc, const Pa
     }
     v3 direct = E * (xyz(qa) * (realLightPDF == 0.f ? 0.f : w1 / realLightPDF));                            // :459-460
     A.direct[p] = f4(direct, 0.f);
+    return direct.x == -1.f;
+}
+PT_HD_NOINLINE void connect_mis_weight_exact(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+    const ptl::RayTracerData& td = P.pc.params;
+    v3 origin = xyz(A.qO[p]), cosineSample = xyz(A.rayD[p]);
+    float realCosinePDF = A.qL[p].w;
+    uint32_t keyC, matC;
+    float tC = emissive_candidate(sc, origin, cosineSample, td.sphereCount, td.objectCount, keyC, matC);    // :453
+    if (tC >= 0.f) {
+        Ray r; r.o = origin; r.d = cosineSample;
+        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, td.objectCount, tC, keyC)) tC = PT_NO_EMISSIVE;
+    }
+    float lightPDF = tC >= 0.f ? light_pdf_from_dst(tC, cosineSample) : 0.f;
     float4 ro = A.rayO[p];
-    ro.w = w2;
+    ro.w = mis_weight(realCosinePDF, lightPDF);                                                            // :455-456
     A.rayO[p] = ro;
 }
-// all three parts for one path (host emulation; the kernels run them as separate launches)
+// all parts for one path (host emulation; the kernels run them as separate launches)
 PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
-    uint32_t jobs = stage_connect_prep(P, sc, A, p);
-    for (uint32_t which = 0; which < 2; ++which) {
-        if (!(jobs & (1u << which))) continue;
+    if (stage_connect_prep(P, sc, A, p)) {
         Ray r; float tE; uint32_t keyE;
-        connect_job_ray(A, p, which, r, tE, keyE);
-        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p, which);
+        connect_job_ray(A, p, r, tE, keyE);
+        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p);
     }
-    stage_connect_finish(P, sc, A, p);
+    if (stage_connect_finish(P, sc, A, p)) connect_mis_weight_exact(P, sc, A, p);
 }
 
 // ---- accumulate -----------------------------------------------------------------------------

@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_shade(const __grid_constant__ Wf
     }
 }
 
-// connect, part 1: emissive candidates of both pdf rays; emits the occlusion jobs (path | which << 31)
+// connect, part 1: emissive candidate of the light-sample ray; emits the occlusion jobs (path indices)
 __global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                              const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
                                                              uint32_t* jobQueue, uint32_t* jobCount) {
@@ -206,11 +206,8 @@ __global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_consta
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
         uint32_t jobs = 0, p = 0;
         if (i < n) { p = queue[i]; jobs = stage_connect_prep(P, sc, A, p); }
-        bool jl = (jobs & PT_CONNECT_JOB_LIGHT) != 0, jc = (jobs & PT_CONNECT_JOB_COSINE) != 0;
-        uint32_t s0 = warp_push(jobCount, jl);
-        if (jl) jobQueue[s0] = p;
-        uint32_t s1 = warp_push(jobCount, jc);
-        if (jc) jobQueue[s1] = p | 0x80000000u;
+        uint32_t s0 = warp_push(jobCount, jobs != 0u);
+        if (jobs) jobQueue[s0] = p;
     }
 }
 
@@ -238,7 +235,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ 
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
                 Ray r;
-                connect_job_ray(A, job & 0x7fffffffu, job >> 31, r, tE, keyE);
+                connect_job_ray(A, job, r, tE, keyE);
                 trav_begin(t, r);
                 busy = true;
             }
@@ -247,7 +244,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ 
         if (nBusy == 0u) break;
         if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
             if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
-                connect_job_occluded(A, job & 0x7fffffffu, job >> 31);
+                connect_job_occluded(A, job);
                 busy = false;
             }
         } else {
@@ -256,12 +253,22 @@ __global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ 
     }
 }
 
-// connect, part 3: pdfs, MIS weights, direct light
+// connect, part 3: pdf, power-heuristic weight, direct light; queues the (practically never occurring) paths whose
+// misWeight is live
 __global__ void __launch_bounds__(WF_THREADS) k_connect_finish(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
-                                                               const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount) {
+                                                               const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
+                                                               uint32_t* misQueue, uint32_t* misCount) {
     uint32_t n = *sCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t p = queue[i];
+        if (stage_connect_finish(P, sc, A, p)) misQueue[atomicAdd(misCount, 1u)] = p;
+    }
+}
+__global__ void __launch_bounds__(WF_THREADS) k_connect_mis(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                            const uint32_t* __restrict__ misQueue, const uint32_t* __restrict__ misCount) {
+    uint32_t n = *misCount;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        stage_connect_finish(P, sc, A, queue[i]);
+        connect_mis_weight_exact(P, sc, A, misQueue[i]);
 }
 
 __global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant__ WfParams P, PathArrays A, float4* accum) {
@@ -414,7 +421,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
     }
     uint32_t need = bounces + 3;
     if (need > w->countSlots) {
-        WCU(wf_resize(w->dCounts, (size_t)need * 6 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
+        WCU(wf_resize(w->dCounts, (size_t)need * 7 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
@@ -453,6 +460,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* workO = workE + w->countSlots;
     uint32_t* oCount = workO + w->countSlots;
     uint32_t* primaryCount = oCount + w->countSlots;
+    uint32_t* mCount = primaryCount + w->countSlots;
     if (!w->gridOcclude) {
         int perSm = 0;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude, WF_THREADS, 0));
@@ -467,7 +475,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         P.nSlots = std::min(slots, n - done);
         P.firstFrame = first + done * stride;
         P.nPaths = (uint32_t)(perSlot * P.nSlots);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 6 * 4, c->stream));
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
         uint32_t* qa = (uint32_t*)w->dQueue[0].p;
         uint32_t* qb = (uint32_t*)w->dQueue[1].p;
         if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
@@ -476,25 +484,32 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         // frame slots in a batch it is traced once (slot 0) and the hit is shared; shade reads hit[p % perSlot] at j = 0
         P.sharePrimary = (c->sharePrimary && P.nSlots > 1) ? 1u : 0u;
         k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount, primaryCount);
+        // Order per bounce: shade(j), extend(j+1), connect(j). Connect comes AFTER the next extension so that NEE rays of
+        // paths whose next ray escapes (their direct light is dropped, raytrace.comp:531-534) are not traced at all.
+        P.connectAfterExtend = 1u;
+        wf_mark(c, ST_EXTEND);
+        k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
         for (uint32_t j = 0; j < nB; ++j) {
-            wf_mark(c, ST_EXTEND);
-            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, (j == 0 && P.sharePrimary) ? primaryCount : qCount + j,
-                                                                  workE + j, w->arrays.hit);
             wf_mark(c, ST_SHADE);
             k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
-            if (j + 1 < nB) wf_mark(c, ST_CONNECT);
             if (j + 1 < nB) {
+                wf_mark(c, ST_EXTEND);
+                k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
+                wf_mark(c, ST_CONNECT);
                 k_connect_prep<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                    (uint32_t*)w->dJobQ.p, oCount + j);
                 wf_mark(c, ST_OCCLUDE);
                 k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
                 wf_mark(c, ST_FINISH);
-                k_connect_finish<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j);
+                k_connect_finish<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                                                                     (uint32_t*)w->dJobQ.p, mCount + j);
+                k_connect_mis<<<w->smCount, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
             }
             std::swap(qa, qb);
-            c->counters[0] += (j + 1 < nB) ? 5 : 2;
+            c->counters[0] += (j + 1 < nB) ? 6 : 1;
         }
+        c->counters[0] += 1;
         wf_mark(c, ST_ACCUMULATE);
         k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
         k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
