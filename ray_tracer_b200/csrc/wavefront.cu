@@ -136,7 +136,10 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
     return __reduce_add_sync(0xffffffffu, (busy ? 1u : 0u) | (hasTri ? 0x100u : 0u) | (canNode ? 0x10000u : 0u));
 }
 
-__global__ void __launch_bounds__(WF_THREADS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+#ifndef PT_EXTEND_MIN_BLOCKS
+#define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
+#endif
+__global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
                                                        uint32_t* workCounter, Hit* __restrict__ hitOut) {
     const uint32_t n = *qCount;
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_consta
 }
 
 // connect, part 2: bounded any-hit walks of the full BVH, same warp scheduling as k_extend
-__global__ void __launch_bounds__(WF_THREADS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+__global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
                                                         uint32_t* workCounter) {
     const uint32_t n = *jobCount;
