@@ -43,6 +43,15 @@ void* orc_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     return s;
 }
 void orc_scene_destroy(void* s) { delete (Scene*)s; }
+// texture extension (see Scene::useTextures)
+int orc_scene_set_texture(void* scene, uint32_t slot, const void* rgba8, uint32_t w, uint32_t h) {
+    if (slot >= 64 || !rgba8 || !w || !h) return 1;
+    Scene::Texture& t = ((Scene*)scene)->textures[slot];
+    t.rgba.assign((const uint8_t*)rgba8, (const uint8_t*)rgba8 + size_t(w) * h * 4);
+    t.w = w; t.h = h;
+    return 0;
+}
+void orc_scene_use_textures(void* scene, int on) { ((Scene*)scene)->useTextures = on != 0; }
 
 int orc_render_dispatch(void* scene, const void* pc208, int W, int H, float* image, uint8_t* rgba8, float* outcol,
                         float* stats, uint64_t* work8, int threads) {

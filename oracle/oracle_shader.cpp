@@ -47,6 +47,7 @@ struct HitInfo {        // raytrace.comp:72-82
     bool didHit = false;
     bool frontFace = false;
     uint32_t kind = 0;            // oracle bookkeeping only: 1 sphere, 2 triangle
+    vec3 albedoTexel{1.f, 1.f, 1.f};   // texture extension: factor on the material's albedo (1 without a map)
 };
 
 struct BxDFResult {     // raytrace.comp:112-118
@@ -334,7 +335,7 @@ float cosineHemispherePDF(const vec3& rayNormal, const vec3& direction) {
 // raytrace.comp:430-464
 BxDFResult diffuseBRDF(Ctx& cx, const vec3& /*incomingDir*/, const HitInfo& prevHit, uint32_t& state) {
     const ol::RayMaterial& hitMaterial = cx.sc.materials[prevHit.materialIndex];
-    vec3 albedo = v3(hitMaterial.albedo);
+    vec3 albedo = v3(hitMaterial.albedo) * prevHit.albedoTexel;      // albedoTexel is 1 unless the texture extension is on
     vec3 origin = prevHit.hitPoint + prevHit.normal * 0.01f;
 
     vec3 lightSample = lightSampleDir(origin, state);
@@ -366,6 +367,42 @@ BxDFResult diffuseBRDF(Ctx& cx, const vec3& /*incomingDir*/, const HitInfo& prev
 
     BxDFResult result = {cosineSample, radiance, directLight, 1.f, misWeight2};
     return result;
+}
+
+// ---- TEXTURE EXTENSION (not in the HEAD shader; semantics of this project) -------------------------------------
+// Texel of TextureBuffer[slot] at uv with the reference's two samplers (src/vk_engine.cpp:525-531: both NEAREST, no
+// mips; sampler 0 REPEAT, sampler 1 CLAMP_TO_EDGE), colour decoded sRGB -> linear (images are R8G8B8A8_SRGB,
+// src/vk_textures.cpp:212): texel index = floor(uv * size), wrapped or clamped. All float operations are single.
+float srgb_to_linear(uint8_t c) {
+    double x = double(c) / 255.0;
+    return float(x <= 0.04045 ? x / 12.92 : std::pow((x + 0.055) / 1.055, 2.4));
+}
+int texel_index(float coord, uint32_t size, uint32_t samplerIndex) {
+    float f = std::floor(coord * float(size));
+    if (!(std::fabs(f) < 1.0e9f)) f = 0.f;          // non-finite or absurd coordinates: texel 0
+    int i = int(f), n = int(size);
+    if (samplerIndex == 0u) { i %= n; if (i < 0) i += n; }
+    else { i = i < 0 ? 0 : (i > n - 1 ? n - 1 : i); }
+    return i;
+}
+bool sample_texture(const Scene& sc, int32_t slot, vec2 uv, uint32_t samplerIndex, vec3& rgb) {
+    if (slot < 0 || slot >= 64 || sc.textures[slot].w == 0) return false;
+    const Scene::Texture& t = sc.textures[slot];
+    int x = texel_index(uv.x, t.w, samplerIndex), y = texel_index(uv.y, t.h, samplerIndex);
+    const uint8_t* px = &t.rgba[(size_t(y) * t.w + x) * 4];
+    rgb = vec3(srgb_to_linear(px[0]), srgb_to_linear(px[1]), srgb_to_linear(px[2]));
+    return true;
+}
+// Applied to a triangle hit before the BSDF is chosen: albedo map multiplies the material's albedo (read_mtl puts
+// map_Kd in albedoIndex, :1109-1117); metalness map (map_Ks, :1119-1125) switches the mirror BSDF on where its red
+// channel is >= 0.5 and off elsewhere. Spheres carry no uv.
+void apply_textures(const Scene& sc, HitInfo& hit, float& reflectance) {
+    if (!sc.useTextures || hit.kind != 2u) return;
+    const ol::RayMaterial& m = sc.materials[hit.materialIndex];
+    uint32_t sampler = sc.objects[hit.objectHitIndex].samplerIndex;
+    vec3 t;
+    if (sample_texture(sc, m.albedoIndex, hit.uv, sampler, t)) hit.albedoTexel = t;
+    if (sample_texture(sc, m.metalnessIndex, hit.uv, sampler, t)) reflectance = t.x >= 0.5f ? 1.f : 0.f;
 }
 
 // raytrace.comp:466-469
@@ -413,7 +450,9 @@ vec3 trace(Ctx& cx, const Ray& ray, uint32_t& state, float* stats) {
 
             // BxDF
             BxDFResult bxdf;
-            if (hitMaterial.reflectance != 0.f) {
+            float reflectance = hitMaterial.reflectance;
+            apply_textures(cx.sc, hit, reflectance);          // no-op unless the texture extension is on
+            if (reflectance != 0.f) {
                 bxdf = specularBRDF(newRay.dir, hit, state);
             } else if (hitMaterial.ior != -1.f) {
                 bxdf = dielectricBTDF(cx, newRay.dir, hit, state);

@@ -41,6 +41,12 @@ struct Scene {
     // (raytrace.comp:292-293) because inverse() is a pure function of the matrix.
     std::vector<om::mat4> M, Minv;
     void finalize();
+    // TEXTURE EXTENSION — NOT in the HEAD shader, which declares TextureBuffer[64] and computes
+    // hit.uv but never samples (raytrace.comp:122,148,249-256). Semantics defined by this project ("parity
+    // unpinned" against the reference): see sample_texture() in oracle_shader.cpp. Off unless useTextures is set.
+    struct Texture { std::vector<uint8_t> rgba; uint32_t w = 0, h = 0; };
+    Texture textures[64];      // TextureBuffer[slot], RGBA8 with sRGB-encoded colour (src/vk_textures.cpp:103-200)
+    bool useTextures = false;
 };
 
 struct HitOut {  // first-hit record for the fixed-ray-batch integer parity test

@@ -9,6 +9,9 @@
 #include <new>
 
 #include "../../include/b200pt.h"
+#include <cmath>
+
+#include "pt_bvh8.h"
 #include "pt_context.h"
 #include "wavefront.h"
 
@@ -130,6 +133,8 @@ int b200pt_create(int device, int width, int height, b200pt_ctx** out) {
     return 0;
 }
 
+static void free_texture(b200pt_ctx::Texture& t);
+
 int b200pt_destroy(b200pt_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
@@ -138,7 +143,8 @@ int b200pt_destroy(b200pt_ctx* c) {
     dev_free(c->dSpheres); dev_free(c->dMaterials); dev_free(c->dPoints); dev_free(c->dTris);
     dev_free(c->dObjects); dev_free(c->dNodes); dev_free(c->dMinv);
     dev_free(c->dAccumOwn); dev_free(c->dImage); dev_free(c->dStats);
-    for (auto& t : c->textures) dev_free(t.texels);
+    for (auto& t : c->textures) free_texture(t);
+    dev_free(c->dTexTable); dev_free(c->dSrgbLut);
     if (c->evStart) cudaEventDestroy(c->evStart);
     if (c->evStop) cudaEventDestroy(c->evStop);
     if (c->ownStream) cudaStreamDestroy(c->ownStream);
@@ -244,16 +250,52 @@ int b200pt_update_objects(b200pt_ctx* c, const void* objects, uint32_t n) {
     return wavefront_build_scene(c);      // world-space boxes move with the transforms
 }
 
+static int upload_texture_table(b200pt_ctx* c) {
+    pt::TexEntry table[B200PT_MAX_TEXTURES];
+    for (int i = 0; i < B200PT_MAX_TEXTURES; ++i) {
+        table[i].object = (unsigned long long)c->textures[i].object; table[i].w = c->textures[i].w; table[i].h = c->textures[i].h;
+    }
+    CU(c, dev_resize(c->dTexTable, sizeof(table)));
+    CU(c, cudaMemcpyAsync(c->dTexTable.p, table, sizeof(table), cudaMemcpyHostToDevice, c->stream));
+    if (!c->dSrgbLut.p) {
+        float lut[256];
+        for (int i = 0; i < 256; ++i) {       // IEC 61966-2-1 decoding, evaluated in double and rounded once
+            double x = double(i) / 255.0;
+            lut[i] = float(x <= 0.04045 ? x / 12.92 : std::pow((x + 0.055) / 1.055, 2.4));
+        }
+        CU(c, dev_resize(c->dSrgbLut, sizeof(lut)));
+        CU(c, cudaMemcpyAsync(c->dSrgbLut.p, lut, sizeof(lut), cudaMemcpyHostToDevice, c->stream));
+    }
+    CU(c, cudaStreamSynchronize(c->stream));
+    wavefront_set_textures(c);
+    return 0;
+}
+static void free_texture(b200pt_ctx::Texture& t) {
+    if (t.object) cudaDestroyTextureObject(t.object);
+    if (t.array) cudaFreeArray(t.array);
+    t.object = 0; t.array = nullptr; t.w = t.h = 0;
+}
+
 int b200pt_upload_texture(b200pt_ctx* c, uint32_t slot, const void* rgba8, uint32_t w, uint32_t h) {
-    if (!c || !rgba8 || slot >= B200PT_MAX_TEXTURES || w == 0 || h == 0 || (uint64_t)w * h > (1ull << 28))
+    if (!c || !rgba8 || slot >= B200PT_MAX_TEXTURES || w == 0 || h == 0 || w > 32768 || h > 32768)
         return fail(c, B200PT_ERR_ARG, "b200pt_upload_texture: bad argument (slot %u, %ux%u)", slot, w, h);
     CU(c, cudaSetDevice(c->device));
-    auto& t = c->textures[slot];
-    CU(c, dev_resize(t.texels, (size_t)w * h * 4));
-    CU(c, cudaMemcpyAsync(t.texels.p, rgba8, (size_t)w * h * 4, cudaMemcpyHostToDevice, c->stream));
     CU(c, cudaStreamSynchronize(c->stream));
+    auto& t = c->textures[slot];
+    free_texture(t);
+    cudaChannelFormatDesc fmt = cudaCreateChannelDesc<uchar4>();
+    CU(c, cudaMallocArray(&t.array, &fmt, w, h));
+    CU(c, cudaMemcpy2DToArray(t.array, 0, 0, rgba8, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice));
+    cudaResourceDesc res;
+    std::memset(&res, 0, sizeof(res));
+    res.resType = cudaResourceTypeArray; res.res.array.array = t.array;
+    cudaTextureDesc td;
+    std::memset(&td, 0, sizeof(td));
+    td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;     // wrap/clamp is applied to the texel index by the kernel
+    td.filterMode = cudaFilterModePoint; td.readMode = cudaReadModeElementType; td.normalizedCoords = 0;
+    CU(c, cudaCreateTextureObject(&t.object, &res, &td, nullptr));
     t.w = w; t.h = h;
-    return 0;
+    return upload_texture_table(c);
 }
 
 static int check_render(b200pt_ctx* c, const void* pc208, ptl::PushConstants& pc) {
@@ -380,6 +422,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "pipeline") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "pipeline must be 0 or 1"); c->pipeline = (int)v; return 0; }
     if (k == "frames_in_flight") { if (v < 1 || v > 64) return fail(c, B200PT_ERR_ARG, "frames_in_flight must be 1..64"); c->framesInFlight = (int)v; return 0; }
     if (k == "profile_stages") { c->profileStages = v != 0; return 0; }
+    if (k == "textures") { c->useTextures = v != 0; return 0; }
     if (k == "trav_tri_vote") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_tri_vote must be 1..32"); c->triVote32 = (int)v; return 0; }
     if (k == "trav_fetch_idle") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_fetch_idle must be 1..32"); c->fetchMinIdle = (int)v; return 0; }
     if (k == "share_primary") { c->sharePrimary = v != 0; return 0; }
@@ -391,6 +434,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "pipeline") { *v = c->pipeline; return 0; }
     if (k == "frames_in_flight") { *v = c->framesInFlight; return 0; }
     if (k == "profile_stages") { *v = c->profileStages; return 0; }
+    if (k == "textures") { *v = c->useTextures; return 0; }
     if (k == "trav_tri_vote") { *v = c->triVote32; return 0; }
     if (k == "trav_fetch_idle") { *v = c->fetchMinIdle; return 0; }
     if (k == "share_primary") { *v = c->sharePrimary; return 0; }

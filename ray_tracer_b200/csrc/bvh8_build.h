@@ -17,6 +17,7 @@ struct Bvh8Host {
     std::vector<Bvh8Node> nodes;
     std::vector<PrimRecord> prims;
     std::vector<ShadeRecord> shade;
+    std::vector<UvRecord> uvs;
     uint32_t maxDepth = 0;
 };
 
@@ -150,7 +151,7 @@ inline float pow2_from_byte(uint8_t b) { uint32_t u = (uint32_t)b << 23; float f
 
 // Encode the subtree rooted at binary node `n2` as wide node `me` (already allocated in out.nodes).
 inline void bvh8_emit(const b8::Builder2& B, const std::vector<b8::Instance>& inst,
-                      const std::vector<PrimRecord>& primOf, const std::vector<ShadeRecord>& shadeOf,
+                      const std::vector<PrimRecord>& primOf, const std::vector<ShadeRecord>& shadeOf, const std::vector<UvRecord>& uvOf,
                       uint32_t n2, uint32_t me, uint32_t depth, Bvh8Host& out) {
     using namespace b8;
     if (depth > out.maxDepth) out.maxDepth = depth;
@@ -244,24 +245,26 @@ inline void bvh8_emit(const b8::Builder2& B, const std::vector<b8::Instance>& in
                 uint32_t id = B.idx[cn.first + k];
                 out.prims.push_back(primOf[id]);
                 out.shade.push_back(shadeOf[id]);
+                out.uvs.push_back(uvOf[id]);
             }
             primOff += cn.count;
         }
     }
     (void)inst;
     out.nodes[me] = node;
-    for (int i = 0; i < nRec; ++i) bvh8_emit(B, inst, primOf, shadeOf, innerNode2[i], innerIdx[i], depth + 1, out);
+    for (int i = 0; i < nRec; ++i) bvh8_emit(B, inst, primOf, shadeOf, uvOf, innerNode2[i], innerIdx[i], depth + 1, out);
 }
 
 inline void bvh8_build(const std::vector<b8::Box>& boxes, const std::vector<b8::Instance>& inst,
-                       const std::vector<PrimRecord>& primOf, const std::vector<ShadeRecord>& shadeOf, Bvh8Host& out) {
-    out.nodes.clear(); out.prims.clear(); out.shade.clear(); out.maxDepth = 0;
+                       const std::vector<PrimRecord>& primOf, const std::vector<ShadeRecord>& shadeOf, const std::vector<UvRecord>& uvOf,
+                       Bvh8Host& out) {
+    out.nodes.clear(); out.prims.clear(); out.shade.clear(); out.uvs.clear(); out.maxDepth = 0;
     out.nodes.resize(1);
     if (boxes.empty()) { std::memset(&out.nodes[0], 0, sizeof(Bvh8Node)); return; }
     b8::Builder2 B(boxes);
     uint32_t root = B.build(0, (uint32_t)boxes.size());
-    out.prims.reserve(boxes.size()); out.shade.reserve(boxes.size());
-    bvh8_emit(B, inst, primOf, shadeOf, root, 0, 1, out);
+    out.prims.reserve(boxes.size()); out.shade.reserve(boxes.size()); out.uvs.reserve(boxes.size());
+    bvh8_emit(B, inst, primOf, shadeOf, uvOf, root, 0, 1, out);
 }
 
 // Reference-layout buffers -> WideSceneHost. Returns nullptr on success or a message.
@@ -318,6 +321,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     std::vector<Instance> inst, instE;
     std::vector<PrimRecord> prim, primE;
     std::vector<ShadeRecord> shade, shadeE;
+    std::vector<UvRecord> uvs, uvsE;
     std::vector<uint32_t> stack, triList;
     for (size_t o = 0; o < objects.size(); ++o) {
         const ptl::RenderObject& ob = objects[o];
@@ -370,8 +374,12 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             for (int ax = 0; ax < 3; ++ax) mag = std::max(mag, std::max(std::fabs(bx.lo[ax]), std::fabs(bx.hi[ax])));
             float pad = 1e-5f * mag + 1e-7f;
             for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
-            boxes.push_back(bx); inst.push_back({(uint32_t)o, t}); prim.push_back(r); shade.push_back(s);
-            if (em) { boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); }
+            UvRecord uvr;
+            uvr.u0 = a.u; uvr.v0 = a.v; uvr.u1 = b.u; uvr.v1 = b.v; uvr.u2 = c.u; uvr.v2 = c.v;
+            uvr.samplerIndex = ob.samplerIndex;
+            uvr.degenerate = ((a.u == b.u && a.v == b.v) || (b.u == c.u && b.v == c.v) || (c.u == a.u && c.v == a.v)) ? 1u : 0u;
+            boxes.push_back(bx); inst.push_back({(uint32_t)o, t}); prim.push_back(r); shade.push_back(s); uvs.push_back(uvr);
+            if (em) { boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); uvsE.push_back(uvr); }
         }
     }
     out.emissionFinite = true;
@@ -385,8 +393,8 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             out.emisLo[a] = u.lo[a] - (1e-4f * mag + 1e-6f); out.emisHi[a] = u.hi[a] + (1e-4f * mag + 1e-6f);
         }
     }
-    bvh8_build(boxes, inst, prim, shade, out.all);
-    bvh8_build(boxesE, instE, primE, shadeE, out.emis);
+    bvh8_build(boxes, inst, prim, shade, uvs, out.all);
+    bvh8_build(boxesE, instE, primE, shadeE, uvsE, out.emis);
     if (out.all.maxDepth > PT_BVH8_MAX_DEPTH || out.emis.maxDepth > PT_BVH8_MAX_DEPTH) return "wide BVH deeper than the traversal stack";
     return nullptr;
 }

@@ -48,6 +48,21 @@ struct ShadeRecord {           // 48 B
 };
 static_assert(sizeof(ShadeRecord) == 48, "ShadeRecord");
 
+// TEXTURE EXTENSION (the HEAD shader never samples — semantics are this project's).
+// Per-triangle texture coordinates (TrianglePoint.position.w / normal.w, raytrace.comp:249-251), parallel to the
+// triangle records; read only for hits on materials that name a texture while option "textures" is on.
+struct UvRecord {              // 32 B
+    float u0, v0, u1, v1, u2, v2;
+    uint32_t samplerIndex;     // RenderObject.samplerIndex: 0 NEAREST/REPEAT, else NEAREST/CLAMP_TO_EDGE
+    uint32_t degenerate;       // two vertices share their uv: the shader substitutes (0.5, 0.5) (raytrace.comp:254-256)
+};
+static_assert(sizeof(UvRecord) == 32, "UvRecord");
+struct TexEntry {              // 16 B: TextureBuffer[slot]
+    unsigned long long object; // cudaTextureObject_t over a cudaArray of uchar4 (point filter, unnormalised coordinates); 0 = empty
+    uint32_t w, h;
+};
+static_assert(sizeof(TexEntry) == 16, "TexEntry");
+
 struct Xform { float M[16]; float Minv[16]; };   // per distinct object matrix
 
 // The reference's own BVH2 (src/vk_engine.h:185-189), re-linked child -> parent. The reference
@@ -74,6 +89,9 @@ struct WideScene {
     Bvh8View emis;             // triangles of objects whose material has emissionStrength != 0
     const ShadeRecord* shade;  // parallel to all.prims
     const ShadeRecord* shadeEmis;   // parallel to emis.prims
+    const UvRecord* uv;        // parallel to all.prims (texture extension)
+    const TexEntry* tex;       // 64 slots
+    const float* srgbLut;      // 256 entries: sRGB-encoded byte -> linear float
     const Xform* xforms;
     const UpNode* up;          // parallel to the reference's bvhNodes
     const ptl::Sphere* spheres;

@@ -48,7 +48,10 @@ struct b200pt_ctx {
     // outputs
     pt::DeviceBuffer dAccumOwn, dImage, dStats;
     float4* accum = nullptr;      // own buffer or caller-attached
-    struct Texture { pt::DeviceBuffer texels; uint32_t w = 0, h = 0; } textures[64];
+    // TextureBuffer[64] (texture extension): texels in a cudaArray behind a point-filtered texture object
+    struct Texture { cudaArray_t array = nullptr; cudaTextureObject_t object = 0; uint32_t w = 0, h = 0; } textures[64];
+    pt::DeviceBuffer dTexTable, dSrgbLut;      // 64 x TexEntry; 256 floats
+    int useTextures = 0;
 
     // options
     int pipeline = 1;

@@ -48,6 +48,7 @@ struct WfParams {
     uint32_t fetchMinIdle;          // ... refill a warp once this many lanes are idle
     uint32_t sharePrimary;          // bounce 0: the hit of path p is stored at p % (rows * W) (one primary ray per pixel)
     uint32_t connectAfterExtend;    // connect of bounce j runs after extend of bounce j+1 (A.hit is the NEXT hit)
+    uint32_t useTextures;           // texture extension on (option "textures"); 0 = the HEAD shader's behaviour
 };
 
 PT_HD v3 xyz(const float4& f) { return mk3(f.x, f.y, f.z); }
@@ -128,6 +129,46 @@ PT_HD void hit_surface(const WideScene& sc, const Ray& ray, const Hit& h, v3& hp
     }
 }
 
+// ---- texture extension ------------------------------------------------------------------------
+// NOT in the HEAD shader (it binds TextureBuffer[64] and computes hit.uv, raytrace.comp:122,148,249-256, but never
+// samples). Semantics of this project (the test checker restates them independently):
+// the reference's samplers are NEAREST without mips, REPEAT (0) or CLAMP_TO_EDGE (1) (src/vk_engine.cpp:525-531),
+// images are RGBA8 sRGB (src/vk_textures.cpp:212): texel = floor(uv * size) wrapped/clamped, bytes decoded to linear
+// through a 256-entry table. The fetch goes through a CUDA texture object (cudaArray: 2-D tiled, texture cache)
+// with point filtering and unnormalised coordinates, so the texel chosen is exactly that index.
+#if defined(__CUDA_ARCH__)
+PT_HD int texel_index(float coord, uint32_t size, uint32_t samplerIndex) {
+    float f = floorf(coord * float(size));
+    if (!(fabsf(f) < 1.0e9f)) f = 0.f;
+    int i = int(f), n = int(size);
+    if (samplerIndex == 0u) { i %= n; if (i < 0) i += n; }
+    else { i = i < 0 ? 0 : (i > n - 1 ? n - 1 : i); }
+    return i;
+}
+__device__ __forceinline__ bool sample_texture(const WideScene& sc, int32_t slot, float tu, float tv, uint32_t samplerIndex, v3& rgb) {
+    if (slot < 0 || slot >= 64) return false;
+    const TexEntry t = sc.tex[slot];
+    if (t.object == 0ull) return false;
+    int x = texel_index(tu, t.w, samplerIndex), y = texel_index(tv, t.h, samplerIndex);
+    uchar4 px = tex2D<uchar4>((cudaTextureObject_t)t.object, float(x) + 0.5f, float(y) + 0.5f);
+    rgb = mk3(sc.srgbLut[px.x], sc.srgbLut[px.y], sc.srgbLut[px.z]);
+    return true;
+}
+// albedo map: factor on the material's albedo; metalness map: mirror BSDF where its red channel >= 0.5
+__device__ __forceinline__ void apply_textures(const WideScene& sc, const ptl::Material& mat, uint32_t primIdx, float u, float v,
+                                               v3& albedoTexel, float& reflectance) {
+    if (mat.albedoIndex < 0 && mat.metalnessIndex < 0) return;
+    const UvRecord r = sc.uv[primIdx];
+    float w = 1.f - u - v;
+    float tu = w * r.u0 + u * r.u1 + v * r.u2;          // hit.uv, raytrace.comp:252
+    float tv = w * r.v0 + u * r.v1 + v * r.v2;
+    if (r.degenerate) { tu = 0.5f; tv = 0.5f; }         // :254-256
+    v3 t;
+    if (sample_texture(sc, mat.albedoIndex, tu, tv, r.samplerIndex, t)) albedoTexel = t;
+    if (sample_texture(sc, mat.metalnessIndex, tu, tv, r.samplerIndex, t)) reflectance = t.x >= 0.5f ? 1.f : 0.f;
+}
+#endif
+
 // ---- shade ----------------------------------------------------------------------------------
 #define PT_SHADE_CONTINUE 1u      /* path goes on to bounce j+1 */
 #define PT_SHADE_CONNECT 2u       /* diffuse bounce: NEE/pdf queries pending for this path */
@@ -163,13 +204,19 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
     v3 dirOut, radiance;
     float originSign = 1.f, nextMis = 1.f;
     uint32_t flags = 0u;
-    if (mat.reflectance != 0.f) {                                // :509-510, specularBRDF :466-469
+    float reflectance = mat.reflectance;
+    v3 albedoTexel = splat3(1.f);
+#if defined(__CUDA_ARCH__)
+    if (P.useTextures && !(h.id & PT_HIT_SPHERE)) apply_textures(sc, mat, h.id & PT_HIT_IDMASK, h.u, h.v, albedoTexel, reflectance);
+#endif
+    if (reflectance != 0.f) {                                    // :509-510, specularBRDF :466-469
         dirOut = reflect(ray.d, n); radiance = splat3(1.f); direct = splat3(-1.f);
     } else if (mat.ior != -1.f) {                                // :511-512, dielectricBTDF :471-481
         dirOut = dielectric_dir(ray.d, n, front, mat.ior, state, originSign);
         radiance = splat3(1.f); direct = splat3(-1.f);
     } else {                                                     // :513-514, diffuseBRDF :430-464 (sampling half)
         v3 albedo = mk3(mat.albedo[0], mat.albedo[1], mat.albedo[2]);
+        if (P.useTextures) albedo = albedo * albedoTexel;
         v3 origin = hp + n * 0.01f;
         v3 lightSample = light_sample_dir(origin, state);
         v3 cosineSample = cosine_hemisphere_dir(n, state);

@@ -18,7 +18,7 @@ namespace pt {
 #define PT_N_STAGES 8
 struct WavefrontState {
     // re-laid-out scene
-    DeviceBuffer dNodes, dPrims, dShade, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform, dUp;
+    DeviceBuffer dNodes, dPrims, dShade, dUv, dNodesE, dPrimsE, dShadeE, dXforms, dObjXform, dUp;
     WideScene scene{};
     uint32_t maxDepth = 0;
     // path state
@@ -367,6 +367,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     WCU(wf_upload(c, w->dNodes, host.all.nodes));
     WCU(wf_upload(c, w->dPrims, host.all.prims));
     WCU(wf_upload(c, w->dShade, host.all.shade));
+    WCU(wf_upload(c, w->dUv, host.all.uvs));
     WCU(wf_upload(c, w->dNodesE, host.emis.nodes));
     WCU(wf_upload(c, w->dPrimsE, host.emis.prims));
     WCU(wf_upload(c, w->dShadeE, host.emis.shade));
@@ -379,6 +380,8 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.emis = {(const Bvh8Node*)w->dNodesE.p, (const PrimRecord*)w->dPrimsE.p, (uint32_t)host.emis.nodes.size(), (uint32_t)host.emis.prims.size()};
     s.shade = (const ShadeRecord*)w->dShade.p;
     s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
+    s.uv = (const UvRecord*)w->dUv.p;
+    s.tex = (const TexEntry*)c->dTexTable.p; s.srgbLut = (const float*)c->dSrgbLut.p;
     s.xforms = (const Xform*)w->dXforms.p;
     s.objXform = (const uint32_t*)w->dObjXform.p;
     s.up = (const UpNode*)w->dUp.p;
@@ -395,10 +398,16 @@ int wavefront_build_scene(b200pt_ctx* c) {
 
 void wavefront_invalidate_frame_state(b200pt_ctx*) {}
 
+void wavefront_set_textures(b200pt_ctx* c) {
+    if (!c->wf) return;
+    c->wf->scene.tex = (const TexEntry*)c->dTexTable.p;
+    c->wf->scene.srgbLut = (const float*)c->dSrgbLut.p;
+}
+
 void wavefront_destroy(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w) return;
-    DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
+    DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dUv, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
                            &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
@@ -455,6 +464,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     const int grid = w->smCount * 8;
     WfParams P;
     P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
+    P.useTextures = (c->useTextures && c->dTexTable.p) ? 1u : 0u;
     P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
     uint32_t nB = pc.params.bounceLimit + 1;
     uint32_t* qCount = (uint32_t*)w->dCounts.p;

@@ -5,6 +5,7 @@
 namespace pt {
 int wavefront_build_scene(b200pt_ctx* c);        // re-layout of the uploaded scene; 0 or a B200PT_ERR_* with c->error set
 void wavefront_destroy(b200pt_ctx* c);
+void wavefront_set_textures(b200pt_ctx* c);      // texture table / sRGB table pointers changed
 void wavefront_invalidate_frame_state(b200pt_ctx* c);
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
                             uint32_t row0, uint32_t row1);

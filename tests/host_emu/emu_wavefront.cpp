@@ -36,6 +36,7 @@ void* emu_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     v.all = {s->wide.all.nodes.data(), s->wide.all.prims.data(), (uint32_t)s->wide.all.nodes.size(), (uint32_t)s->wide.all.prims.size()};
     v.emis = {s->wide.emis.nodes.data(), s->wide.emis.prims.data(), (uint32_t)s->wide.emis.nodes.size(), (uint32_t)s->wide.emis.prims.size()};
     v.shade = s->wide.all.shade.data(); v.shadeEmis = s->wide.emis.shade.data();
+    v.uv = s->wide.all.uvs.data(); v.tex = nullptr; v.srgbLut = nullptr;
     v.xforms = s->wide.xforms.data(); v.up = s->wide.up.data(); v.spheres = s->spheres.data(); v.materials = s->materials.data();
     v.objXform = s->wide.objXform.data();
     v.nXforms = (uint32_t)s->wide.xforms.size(); v.nSpheres = nS; v.nMaterials = nM; v.nObjects = nO;
@@ -61,7 +62,7 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
     WfParams P;
     std::memcpy(&P.pc, pc208, sizeof(P.pc));
     P.cp = camera_plane(P.pc.cam);
-    P.triVote32 = 8; P.fetchMinIdle = 8; P.sharePrimary = 0; P.connectAfterExtend = 0;
+    P.triVote32 = 8; P.fetchMinIdle = 8; P.sharePrimary = 0; P.connectAfterExtend = 0; P.useTextures = 0;
     P.W = W; P.H = H; P.row0 = 0; P.rows = (uint32_t)H; P.stride = stride ? stride : 1;
     size_t cap = (size_t)slots * W * H;
     std::vector<float4> rayO(cap), rayD(cap), atten(cap), total(cap), direct(cap), qO(cap), qL(cap), qA(cap), qE(cap);

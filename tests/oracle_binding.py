@@ -42,6 +42,8 @@ def lib():
         L.orc_render_dispatch.argtypes = [vp, vp, i32, i32, vp, vp, vp, vp, vp, i32]
         L.orc_render_frames.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
         L.orc_render_frames2.argtypes = [vp, vp, i32, i32, u32, u32, vp, vp, i32]
+        L.orc_scene_set_texture.argtypes = [vp, u32, vp, u32, u32]
+        L.orc_scene_use_textures.argtypes = [vp, i32]
         L.orc_render_window.argtypes = [vp, vp, i32, i32, u32, u32, i32, i32, i32, i32, i32, i32, vp, vp, i32]
         L.orc_trace_batch.argtypes = [vp, vp, vp, u64, vp, vp, i32]
         L.orc_random.restype = f32
@@ -131,6 +133,14 @@ class OracleScene:
         work = np.zeros(16, np.uint64)
         lib().orc_render_frames2(self.h, _ptr(pcb), W, H, first, n, _ptr(accum), _ptr(work), threads)
         return accum, dict(zip(WORK_FIELDS, work[:8].tolist())), dict(zip(WORK_FIELDS, work[8:].tolist()))
+
+    def set_texture(self, slot, rgba8):
+        """Texture extension: TextureBuffer[slot] = (h, w, 4) uint8, sRGB-encoded colour."""
+        t = np.ascontiguousarray(rgba8, np.uint8)
+        assert lib().orc_scene_set_texture(self.h, slot, _ptr(t), t.shape[1], t.shape[0]) == 0
+
+    def use_textures(self, on=True):
+        lib().orc_scene_use_textures(self.h, int(on))
 
     def render_window(self, pc, W, H, first, x0, y0, w, h, n=1, sx=1, sy=1, threads=0, want_work=False):
         """Pixels (x0 + i*sx, y0 + j*sy) of the W x H image, frames first..first+n-1 -> (h, w, 4) accumulator."""

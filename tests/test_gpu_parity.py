@@ -256,3 +256,70 @@ def test_full_size_properties_c4(gpu):
     got = one[516:564, 928:992]
     diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
     assert diff.mean() <= 2e-3, diff.mean()
+
+
+def _textured_scene():
+    """Floor + back wall with uv running over [-0.5, 2.5] (exercises REPEAT and CLAMP_TO_EDGE), a wall whose two
+    triangles share uv values (the shader's degenerate rule), the NEE light box; two 8x8 textures."""
+    from ray_tracer_b200 import scene as hs
+    rng = np.random.default_rng(3)
+
+    def quad(p0, du, dv, n, uv0=(-0.5, -0.5), uv1=(2.5, 2.5)):
+        p0, du, dv = (np.asarray(a, np.float32) for a in (p0, du, dv))
+        P = [p0, p0 + du, p0 + du + dv, p0 + dv]
+        UV = [(uv0[0], uv0[1]), (uv1[0], uv0[1]), (uv1[0], uv1[1]), (uv0[0], uv1[1])]
+        out = np.zeros((2, 3, 8), np.float32)
+        for t, idx in enumerate(((0, 1, 2), (0, 2, 3))):
+            for k, i in enumerate(idx):
+                out[t, k, 0:3] = P[i]; out[t, k, 3] = UV[i][0]; out[t, k, 4:7] = n; out[t, k, 7] = UV[i][1]
+        return out
+
+    b = hs.SceneBuilder()
+    b.set_spheres(np.zeros(320, np.uint8))
+    m0 = hs.material(albedo=(0.9, 0.9, 0.9)); m0.view(np.int32)[10] = 0           # albedo map in slot 0
+    m1 = hs.material(albedo=(0.8, 0.7, 0.6)); m1.view(np.int32)[10] = 0; m1.view(np.int32)[11] = 1   # + metalness map slot 1
+    m2 = hs.material(albedo=(0, 0, 0), emission=(1, 1, 1), strength=2.4)
+    m3 = hs.material(albedo=(0.7, 0.2, 0.2)); m3.view(np.int32)[10] = 5           # names an EMPTY slot: no effect
+    for m in (m0, m1, m2, m3):
+        b.add_material(m)
+    b.add_mesh(quad((-2, 0.5, -2), (4, 0, 0), (0, 0, 5), (0, -1, 0)), material=0)                     # floor (y = +0.5 is down)
+    b.add_mesh(quad((-2, 0.5, 2), (4, 0, 0), (0, -3, 0), (0, 0, -1)), material=1)                     # back wall
+    b.add_mesh(quad((-2, 0.5, -2), (0, 0, 5), (0, -3, 0), (1, 0, 0), uv0=(0.3, 0.3), uv1=(0.3, 0.9)), material=0)   # degenerate uv
+    b.add_mesh(quad((2, 0.5, -2), (0, -3, 0), (0, 0, 5), (-1, 0, 0)), material=3)
+    from ray_tracer_b200.scenes import _box, _pack
+    t, n = _box([-1 / 3, -1.52, -1 / 3], [1 / 3, -1.5, 1 / 3])
+    b.add_mesh(_pack(t, n), material=2)
+    blobs = b.blobs()
+    blobs["objects"] = blobs["objects"].copy()
+    blobs["objects"].view(np.uint32).reshape(-1, 20)[1, 19] = 1        # back wall: sampler 1 = CLAMP_TO_EDGE
+    tex0 = rng.integers(0, 256, (8, 8, 4), dtype=np.uint8)
+    tex1 = np.zeros((4, 8, 4), np.uint8); tex1[..., 0] = rng.integers(0, 2, (4, 8)) * 255; tex1[..., 3] = 255
+    return blobs, {0: tex0, 1: tex1}
+
+
+def test_texture_extension(gpu):
+    # SURVEY.md §8 f1: NOT in the HEAD shader; semantics are this project's (DESIGN.md §9) and restated in the oracle
+    W, H = 192, 160
+    blobs, textures = _textured_scene()
+    nobj = blobs["objects"].size // 80
+    pc = ob.default_push_constants(W, H, 10, nobj)
+    sc = ob.OracleScene(blobs)
+    cp = _pass(gpu, blobs, W, H)
+    for slot, t in textures.items():
+        sc.set_texture(slot, t)
+        cp.upload_texture(slot, t)
+    with ob.math_mode(1):
+        plain, _ = sc.render_frames(pc, W, H, 0, 4)
+        sc.use_textures(True)
+        want, _ = sc.render_frames(pc, W, H, 0, 4)
+    assert relrmse(want[..., :3], plain[..., :3]) > 0.05               # the maps do change the image
+    cp.render_frames(pc, 0, 4)                                         # option off: uploaded textures are ignored (HEAD behaviour)
+    got = cp.read_accum()
+    assert (got.view(np.uint32) != plain.view(np.uint32)).any(axis=2).mean() <= 1e-4
+    cp.clear()
+    cp.set_option("textures", 1)
+    cp.render_frames(pc, 0, 4)
+    got = cp.read_accum()
+    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
+    assert diff.mean() <= 1e-4, diff.mean()
+    assert relrmse(got[..., :3], want[..., :3]) <= 1e-5
