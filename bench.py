@@ -340,7 +340,8 @@ def main():
         achieved = stage_bytes[dom] * paths_rank / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(dom)
+            if (args.width, args.height, F, args.obj) == (1920, 1080, 8, None):      # the configuration the capture was taken on
+                traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dom)
         except (OSError, ValueError):
             pass
         # second candidate bound of SURVEY.md §8(d3): FP32 issue. Flops per path of the extension rays in the
