@@ -6,6 +6,7 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -56,6 +57,8 @@ struct Builder2 {
     std::vector<uint32_t> idx;
     std::vector<Node2> nodes;
     static const int NB = 16;
+    int maxLeaf = 3;            // triangles per leaf slot, 1..3 (tuning: B200PT_BVH_LEAF)
+    float travCost = 1.0f;      // cost of one more box level relative to one triangle test (tuning: B200PT_BVH_CT)
 
     explicit Builder2(const std::vector<Box>& b) : boxes(b) {
         size_t n = b.size();
@@ -67,6 +70,8 @@ struct Builder2 {
             cz[i] = 0.5f * (b[i].lo[2] + b[i].hi[2]);
         }
         nodes.reserve(2 * n + 1);
+        if (const char* e = std::getenv("B200PT_BVH_LEAF")) maxLeaf = std::max(1, std::min(3, std::atoi(e)));
+        if (const char* e = std::getenv("B200PT_BVH_CT")) travCost = (float)std::atof(e);
     }
     float cen(uint32_t i, int a) const { return a == 0 ? cx[i] : (a == 1 ? cy[i] : cz[i]); }
 
@@ -109,9 +114,9 @@ struct Builder2 {
             }
         }
         // leaves hold at most 3 triangles (the unary count field of a node slot)
-        if (count <= 3) {
+        if (count <= (uint32_t)maxLeaf) {
             float leafCost = box_half_area(box) * count;
-            float splitCost = bestAxis < 0 ? 1e30f : box_half_area(box) * 1.0f + bestCost;
+            float splitCost = bestAxis < 0 ? 1e30f : box_half_area(box) * travCost + bestCost;
             if (!(splitCost < leafCost)) { nodes[me].first = first; nodes[me].count = count; return me; }
         }
         uint32_t mid;

@@ -90,6 +90,12 @@ PT_HD float byte_to_float(uint32_t word, int k) {
     return (float)((word >> (8 * k)) & 0xffu);
 #endif
 }
+#ifndef PT_DEBUG_COUNT
+#define PT_DEBUG_COUNT(i)      /* host-side instrumentation hook (profiling experiments only) */
+#endif
+#ifndef PT_TRAV_PREFETCH
+#define PT_TRAV_PREFETCH 0
+#endif
 #ifndef PT_NODE_I2F_NEAR
 #define PT_NODE_I2F_NEAR 0        /* how many of the three entry-plane axes also go through I2F (tuning knob) */
 #endif
@@ -290,10 +296,21 @@ PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, uint32_t* stackBase, uin
     uint32_t nodeIdx = t.gBase + rel;
     if (t.gBits & 0xff000000u) { stackBase[t.sp] = t.gBase; stackBits[t.sp] = t.gBits; t.sp++; }
     if (t.tBits) { stackBase[t.sp] = t.tBase; stackBits[t.sp] = t.tBits; t.sp++; }
+    PT_DEBUG_COUNT(0);
     const NodeWords n = load_node(bvh.nodes, nodeIdx);
     uint32_t h = bvh8_node_hits(n, t.br, tmax);
     t.gBase = n.w[4]; t.gBits = (h & 0xff000000u) | (n.w[3] >> 24);
     t.tBase = n.w[5]; t.tBits = h & 0x00ffffffu;
+#if defined(__CUDA_ARCH__) && PT_TRAV_PREFETCH
+    // the records the next steps of this lane will read: first triangle of the new group, nearest child hit
+    if ((PT_TRAV_PREFETCH & 1) && t.tBits) asm volatile("prefetch.global.L1 [%0];" ::"l"(bvh.prims + t.tBase + (uint32_t)highest_bit(t.tBits)));
+    if ((PT_TRAV_PREFETCH & 2) && (t.gBits & 0xff000000u)) {
+        uint32_t slot2 = ((uint32_t)highest_bit(t.gBits) - 24u) ^ oct;
+        const Bvh8Node* nn = bvh.nodes + t.gBase + (uint32_t)popcount32(t.gBits & 0xffu & ~(0xffffffffu << slot2));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(nn));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"((const char*)nn + 64));
+    }
+#endif
 }
 
 // Test the next triangle of the current group for a closest hit strictly closer than hit.dst (the
@@ -305,6 +322,7 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     uint32_t pi = t.tBase + (uint32_t)k;
+    PT_DEBUG_COUNT(1);
     const PrimRecord p = load_prim(bvh.prims, pi);
     if (p.objectIndex >= objectCount) return;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);

@@ -323,3 +323,44 @@ def test_texture_extension(gpu):
     diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
     assert diff.mean() <= 1e-4, diff.mean()
     assert relrmse(got[..., :3], want[..., :3]) <= 1e-5
+
+
+def test_depth16_and_deep_roulette(gpu, bunny_blobs):
+    # C5's bounce limit (16): Russian roulette is live for j > 5 (raytrace.comp:519-524), the queues run 17 bounces
+    W, H = 200, 160
+    nobj = bunny_blobs["objects"].size // 80
+    pc = ob.default_push_constants(W, H, 10, nobj)
+    pc.view(np.uint32)[44] = 16            # bounceLimit
+    pc.view(np.float32)[39] = 1.0          # environment on
+    with ob.math_mode(1):
+        want, _ = ob.OracleScene(bunny_blobs).render_frames(pc, W, H, 0, 3)
+    cp = _pass(gpu, bunny_blobs, W, H)
+    cp.set_option("frames_in_flight", 2)
+    cp.render_frames(pc, 0, 3)
+    got = cp.read_accum()
+    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
+    assert diff.mean() <= 1e-4, diff.mean()
+    # bounceLimit 0: primary hit only (emission at j == 0), no connect, no second extend
+    pc.view(np.uint32)[44] = 0
+    with ob.math_mode(1):
+        want0, _ = ob.OracleScene(bunny_blobs).render_frames(pc, W, H, 0, 2)
+    cp.clear()
+    cp.render_frames(pc, 0, 2)
+    assert np.array_equal(cp.read_accum().view(np.uint32), want0.view(np.uint32))
+
+
+def test_non_finite_emission_disables_nee_shortcut(gpu, cornell_blobs):
+    # the "NEE ray cannot contribute" shortcut needs finite emission (0 * inf = NaN in the reference): with an
+    # infinite emitter every NEE ray is traced again and the image (NaN -> path 0 / magenta rules) still matches
+    W = H = 96
+    mats = cornell_blobs["materials"].copy()
+    mats.view(np.float32).reshape(-1, 16)[3, 7] = np.inf       # light material: emissionStrength
+    blobs = dict(cornell_blobs, materials=mats)
+    pc = ob.default_push_constants(W, H, 10, 9)
+    with ob.math_mode(1):
+        want, _ = ob.OracleScene(blobs).render_frames(pc, W, H, 0, 3)
+    cp = _pass(gpu, blobs, W, H)
+    cp.render_frames(pc, 0, 3)
+    got = cp.read_accum()
+    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
+    assert diff.mean() <= 1e-3, diff.mean()
