@@ -59,8 +59,9 @@ def main():
     tot = [0, 0, 0, 0, 0]
     for i, r in enumerate(data):
         key = table[i][0] if i < len(table) else ("?", 0)
-        vals = [int(float(r[col[c]] or 0)) for c in ("Instructions Executed", "Thread Instructions Executed", "# Samples",
-                                                     "L1 Tag Requests Global", "L2 Theoretical Sectors Local")]
+        vals = [int(float(r[col[c]] or 0)) if c in col else 0      # kernels without local memory have no such column
+                for c in ("Instructions Executed", "Thread Instructions Executed", "# Samples", "L1 Tag Requests Global",
+                          "L2 Theoretical Sectors Local")]
         for k, v in enumerate(vals):
             agg[key][k] += v
             tot[k] += v

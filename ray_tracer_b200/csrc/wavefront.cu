@@ -182,21 +182,54 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
     }
 }
 
-__global__ void __launch_bounds__(WF_THREADS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
-                                                      const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
-                                                      uint32_t* nextQueue, uint32_t* nextCount, uint32_t* shadowQueue, uint32_t* shadowCount,
-                                                      uint32_t j) {
-    uint32_t n = *qCount;
-    uint32_t nRound = (n + 31u) & ~31u;           // whole warps stay together for the ballots
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
+// Block-aggregated queue append: ONE global atomic per block per round instead of one per warp. With 16 M paths per
+// launch the per-warp form issued 0.5 M atomics on each of two addresses and shade's stall samples pointed at them
+// (54 %, profiles/r01/k_shade_v12_by_line.txt); measured gain 0.4 ms of 9.5 per step — the wait was mostly overlapped.
+// Every thread of the block must call it (uniform trip counts).
+#define SHADE_THREADS 256
+template <int NQ>
+static __device__ __forceinline__ void block_push(uint32_t* const (&counters)[NQ], const bool (&pred)[NQ], uint32_t (&slot)[NQ]) {
+    __shared__ uint32_t warpCount[NQ][SHADE_THREADS / 32];
+    __shared__ uint32_t blockBase[NQ];
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    unsigned mask[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        mask[q] = __ballot_sync(0xffffffffu, pred[q]);
+        if (lane == 0) warpCount[q][warp] = (uint32_t)__popc(mask[q]);
+    }
+    __syncthreads();
+    if (threadIdx.x < NQ) {
+        uint32_t total = 0;
+        for (unsigned k = 0; k < blockDim.x / 32; ++k) total += warpCount[threadIdx.x][k];
+        blockBase[threadIdx.x] = total ? atomicAdd(counters[threadIdx.x], total) : 0u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        uint32_t before = 0;
+        for (unsigned k = 0; k < warp; ++k) before += warpCount[q][k];
+        slot[q] = blockBase[q] + before + (uint32_t)__popc(mask[q] & ((1u << lane) - 1u));
+    }
+    __syncthreads();            // warpCount is reused by the next round
+}
+
+__global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+                                                         const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
+                                                         uint32_t* nextQueue, uint32_t* nextCount, uint32_t* shadowQueue, uint32_t* shadowCount,
+                                                         uint32_t j) {
+    const uint32_t n = *qCount;
+    uint32_t* const counters[2] = {nextCount, shadowCount};
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {      // block-uniform trip count
+        const uint32_t i = base + threadIdx.x;
         uint32_t flags = 0, p = 0;
         if (i < n) { p = queue[i]; flags = stage_shade(P, sc, A, p, j); }
-        bool go = (flags & PT_SHADE_CONTINUE) != 0;
-        bool sh = go && (flags & PT_SHADE_CONNECT) != 0;
-        uint32_t s0 = warp_push(nextCount, go);
-        if (go) nextQueue[s0] = p;
-        uint32_t s1 = warp_push(shadowCount, sh);
-        if (sh) shadowQueue[s1] = p;
+        const bool go = (flags & PT_SHADE_CONTINUE) != 0;
+        const bool pred[2] = {go, go && (flags & PT_SHADE_CONNECT) != 0};
+        uint32_t slot[2];
+        block_push<2>(counters, pred, slot);
+        if (pred[0]) nextQueue[slot[0]] = p;
+        if (pred[1]) shadowQueue[slot[1]] = p;
     }
 }
 
@@ -205,7 +238,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_consta
                                                              const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
                                                              uint32_t* jobQueue, uint32_t* jobCount) {
     uint32_t n = *sCount;
-    uint32_t nRound = (n + 31u) & ~31u;
+    uint32_t nRound = (n + 31u) & ~31u;           // whole warps stay together for the ballot
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
         uint32_t jobs = 0, p = 0;
         if (i < n) { p = queue[i]; jobs = stage_connect_prep(P, sc, A, p); }
@@ -462,6 +495,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     while (slots > 1 && perSlot * slots > ((size_t)1 << 26)) slots--;
     if (int rc = wf_reserve(c, perSlot * slots, pc.params.bounceLimit)) return rc;
     const int grid = w->smCount * 8;
+    const int gridShade = w->smCount * 4;         // 256-thread blocks
     WfParams P;
     P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
     P.useTextures = (c->useTextures && c->dTexTable.p) ? 1u : 0u;
@@ -504,7 +538,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
         for (uint32_t j = 0; j < nB; ++j) {
             wf_mark(c, ST_SHADE);
-            k_shade<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
+            k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                         (uint32_t*)w->dShadowQ.p, sCount + j, j);
             if (j + 1 < nB) {
                 wf_mark(c, ST_EXTEND);
