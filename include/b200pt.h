@@ -119,7 +119,11 @@ int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const fl
                        void* host_hits48);
 
 /* Options: "pipeline" 0 = reference-layout per-pixel kernel, 1 = wavefront (default for
- * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1. Unknown keys fail. */
+ * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1;
+ * "textures" 0/1: texture extension (albedo / metalness maps; off = the HEAD shader, which never samples);
+ * "storage_rgba8" 0/1: b200pt_render stores the image at unorm8 precision, as the reference's rgba8 image does;
+ * "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32: scheduling of the wavefront kernels
+ * (results do not depend on them). Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
 

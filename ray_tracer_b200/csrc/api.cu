@@ -423,6 +423,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "frames_in_flight") { if (v < 1 || v > 64) return fail(c, B200PT_ERR_ARG, "frames_in_flight must be 1..64"); c->framesInFlight = (int)v; return 0; }
     if (k == "profile_stages") { c->profileStages = v != 0; return 0; }
     if (k == "textures") { c->useTextures = v != 0; return 0; }
+    if (k == "storage_rgba8") { c->storageRgba8 = v != 0; return 0; }
     if (k == "trav_tri_vote") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_tri_vote must be 1..32"); c->triVote32 = (int)v; return 0; }
     if (k == "trav_fetch_idle") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_fetch_idle must be 1..32"); c->fetchMinIdle = (int)v; return 0; }
     if (k == "share_primary") { c->sharePrimary = v != 0; return 0; }
@@ -435,6 +436,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "frames_in_flight") { *v = c->framesInFlight; return 0; }
     if (k == "profile_stages") { *v = c->profileStages; return 0; }
     if (k == "textures") { *v = c->useTextures; return 0; }
+    if (k == "storage_rgba8") { *v = c->storageRgba8; return 0; }
     if (k == "trav_tri_vote") { *v = c->triVote32; return 0; }
     if (k == "trav_fetch_idle") { *v = c->fetchMinIdle; return 0; }
     if (k == "share_primary") { *v = c->sharePrimary; return 0; }

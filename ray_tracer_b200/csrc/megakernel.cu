@@ -7,7 +7,8 @@
 
 namespace pt {
 
-__global__ void __launch_bounds__(64) k_ref_dispatch(RefScene sc, const __grid_constant__ ptl::PushConstants c_pc, CameraPlane cp, int W, int H, float4* image, float2* stats) {
+__global__ void __launch_bounds__(64) k_ref_dispatch(RefScene sc, const __grid_constant__ ptl::PushConstants c_pc, CameraPlane cp, int W, int H, float4* image, float2* stats,
+                                                     int storeUnorm8) {
     // 8x8 tiles as the reference dispatches them (local_size 8x8, vkCmdDispatch(ceil(W/8), ceil(H/8)));
     // the reference has no bounds guard although it over-covers (A-Q7) — guarded here.
     uint32_t gx = blockIdx.x * 8 + (threadIdx.x & 7);
@@ -17,6 +18,17 @@ __global__ void __launch_bounds__(64) k_ref_dispatch(RefScene sc, const __grid_c
     RefPixel px = ref_pixel(sc, c_pc, cp, gx, gy, W, H);
     float4 old = image[p];
     v3 fin = ref_resolve(c_pc, px, mk3(old.x, old.y, old.z));
+    if (storeUnorm8) {
+        // option "storage_rgba8": the reference's storage image is rgba8 (raytrace.comp:120,593) — what the next dispatch
+        // reads back is the 8-bit value. Vulkan unorm conversion: clamp, scale, round to nearest even; no transfer
+        // function (A-Q3: whether MoltenVK applies sRGB on a storage image is driver-defined — parity unpinned).
+        auto q = [](float f) -> float {
+            if (!(f > 0.f)) return 0.f;
+            if (f >= 1.f) return 1.f;
+            return float(__float2int_rn(f * 255.f)) / 255.f;
+        };
+        fin = mk3(q(fin.x), q(fin.y), q(fin.z));
+    }
     image[p] = make_float4(fin.x, fin.y, fin.z, 1.f);
     stats[p] = make_float2(px.stats0, px.stats1);
 }
@@ -60,7 +72,7 @@ __global__ void k_ref_trace_batch(RefScene sc, const __grid_constant__ ptl::Push
 cudaError_t launch_ref_dispatch(b200pt_ctx* c, const ptl::PushConstants& pc) {
     dim3 grid((c->W + 7) / 8, (c->H + 7) / 8);
     k_ref_dispatch<<<grid, 64, 0, c->stream>>>(c->ref, pc, camera_plane(pc.cam), c->W, c->H, (float4*)c->dImage.p,
-                                               (float2*)c->dStats.p);
+                                               (float2*)c->dStats.p, c->storageRgba8);
     c->counters[0] += 1;
     uint64_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
     c->counters[1] += (uint64_t)c->W * c->H * samples;

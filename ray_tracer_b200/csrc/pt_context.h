@@ -52,6 +52,7 @@ struct b200pt_ctx {
     struct Texture { cudaArray_t array = nullptr; cudaTextureObject_t object = 0; uint32_t w = 0, h = 0; } textures[64];
     pt::DeviceBuffer dTexTable, dSrgbLut;      // 64 x TexEntry; 256 floats
     int useTextures = 0;
+    int storageRgba8 = 0;         // b200pt_render keeps the storage image at 8-bit precision like the reference's rgba8 image
 
     // options
     int pipeline = 1;

@@ -364,3 +364,21 @@ def test_non_finite_emission_disables_nee_shortcut(gpu, cornell_blobs):
     got = cp.read_accum()
     diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
     assert diff.mean() <= 1e-3, diff.mean()
+
+
+def test_storage_rgba8_progressive(gpu, cornell_blobs):
+    # literal 8-bit read-modify-write of the storage image (raytrace.comp:542,576-578,593)
+    W = H = 80
+    sc = ob.OracleScene(cornell_blobs)
+    cp = _pass(gpu, cornell_blobs, W, H)
+    cp.set_option("storage_rgba8", 1)
+    pc = ob.default_push_constants(W, H, 10, 9)
+    pc[160] = 1                            # progressive
+    image = np.zeros((H, W, 4), np.float32)
+    rgba8 = np.zeros((H, W, 4), np.uint8)
+    with ob.math_mode(1):
+        for f in range(6):
+            pc.view(np.uint32)[50] = f
+            sc.render_dispatch(pc, W, H, image=image, rgba8=rgba8)
+            cp.run_compute(pc)
+    assert np.array_equal(cp.read_rgba8()[..., :3], rgba8[..., :3])
