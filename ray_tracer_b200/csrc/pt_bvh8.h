@@ -115,5 +115,6 @@ struct WideScene {
 #define PT_BVH8_STACK 48
 #define PT_BVH8_MAX_DEPTH 30
 #define PT_BVH8_POSTPONE_LIMIT 16
+#define PT_BVH8_SHARED_STACK 20     /* entries per ray kept in shared memory by the persistent kernels */
 
 }  // namespace pt

@@ -273,13 +273,23 @@ PT_HD void trav_begin(Trav& t, const Ray& ray) {
     t.gBase = 0; t.gBits = 0x80000000u;               // the root as the only child of a virtual group
     t.tBase = 0; t.tBits = 0; t.sp = 0;
 }
+// The per-ray stack of groups. PrivateStack: two arrays in thread-private (local) memory. The persistent kernels use
+// a SplitStack (wavefront.cu): the first PT_BVH8_SHARED_STACK entries live in shared memory, [entry][thread] so that a
+// warp's accesses are conflict-free, the rest (rarely reached) in local memory.
+struct PrivateStack {
+    uint32_t base[PT_BVH8_STACK], bits[PT_BVH8_STACK];
+    PT_HD void put(int i, uint32_t b, uint32_t v) { base[i] = b; bits[i] = v; }
+    PT_HD void get(int i, uint32_t& b, uint32_t& v) const { b = base[i]; v = bits[i]; }
+};
 PT_HD bool trav_has_node(const Trav& t) { return (t.gBits & 0xff000000u) != 0; }
 PT_HD bool trav_has_tri(const Trav& t) { return t.tBits != 0; }
 // Nothing in hand: take the next group from the stack. Returns false when the walk is over.
-PT_HD bool trav_pop(Trav& t, const uint32_t* stackBase, const uint32_t* stackBits) {
+template <class Stack>
+PT_HD bool trav_pop(Trav& t, const Stack& stack) {
     if (t.sp == 0) return false;
     t.sp--;
-    uint32_t b = stackBase[t.sp], bits = stackBits[t.sp];
+    uint32_t b, bits;
+    stack.get(t.sp, b, bits);
     if (bits & 0xff000000u) { t.gBase = b; t.gBits = bits; }
     else { t.tBase = b; t.tBits = bits; t.gBits = 0; }
     return true;
@@ -287,15 +297,16 @@ PT_HD bool trav_pop(Trav& t, const uint32_t* stackBase, const uint32_t* stackBit
 // Visit the nearest pending child of the current node group (precondition: trav_has_node).
 // A triangle group still in hand is postponed: it goes on top of the stack, so it is the next
 // thing popped once this subtree is done.
-PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, uint32_t* stackBase, uint32_t* stackBits, float tmax) {
+template <class Stack>
+PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, Stack& stack, float tmax) {
     const uint32_t oct = t.br.octinv4 & 7u;
     int bit = highest_bit(t.gBits);
     t.gBits &= ~(1u << bit);
     uint32_t slot = ((uint32_t)bit - 24u) ^ oct;
     uint32_t rel = (uint32_t)popcount32(t.gBits & 0xffu & ~(0xffffffffu << slot));
     uint32_t nodeIdx = t.gBase + rel;
-    if (t.gBits & 0xff000000u) { stackBase[t.sp] = t.gBase; stackBits[t.sp] = t.gBits; t.sp++; }
-    if (t.tBits) { stackBase[t.sp] = t.tBase; stackBits[t.sp] = t.tBits; t.sp++; }
+    if (t.gBits & 0xff000000u) { stack.put(t.sp, t.gBase, t.gBits); t.sp++; }
+    if (t.tBits) { stack.put(t.sp, t.tBase, t.tBits); t.sp++; }
     PT_DEBUG_COUNT(0);
     const NodeWords n = load_node(bvh.nodes, nodeIdx);
     uint32_t h = bvh8_node_hits(n, t.br, tmax);
@@ -352,24 +363,24 @@ PT_HD bool trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, cons
 // Per-ray loops over the steps (host emulation, b200pt_trace_batch, the small emissive BVH).
 PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
                                  uint32_t objectCount, Hit& hit, uint32_t& key) {
-    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     for (;;) {
         if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, t, hit, key);
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stackBase, stackBits, hit.dst);
-        else if (!trav_pop(t, stackBase, stackBits)) break;
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, hit.dst);
+        else if (!trav_pop(t, stack)) break;
     }
 }
 PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
                                   uint32_t objectCount, float tE, uint32_t keyE) {
-    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     for (;;) {
         if (trav_has_tri(t)) { if (trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, t, tE, keyE)) return true; }
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stackBase, stackBits, tE);
-        else if (!trav_pop(t, stackBase, stackBits)) break;
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, tE);
+        else if (!trav_pop(t, stack)) break;
     }
     return false;
 }

@@ -130,6 +130,30 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     return got;
 }
 
+#ifndef PT_SPLIT_STACK
+#define PT_SPLIT_STACK 0      /* A/B on B200: shared-memory stack 250.2, local-memory stack 252.3 Mpaths/s: local (L1-resident) wins */
+#endif
+#if PT_SPLIT_STACK
+struct SplitStack {
+    uint2* sh;                                            // this thread's column of the block's shared array
+    uint32_t base[PT_BVH8_STACK - PT_BVH8_SHARED_STACK], bits[PT_BVH8_STACK - PT_BVH8_SHARED_STACK];
+    __device__ __forceinline__ void put(int i, uint32_t b, uint32_t v) {
+        if (i < PT_BVH8_SHARED_STACK) sh[i * WF_THREADS] = make_uint2(b, v);
+        else { base[i - PT_BVH8_SHARED_STACK] = b; bits[i - PT_BVH8_SHARED_STACK] = v; }
+    }
+    __device__ __forceinline__ void get(int i, uint32_t& b, uint32_t& v) const {
+        if (i < PT_BVH8_SHARED_STACK) { uint2 e = sh[i * WF_THREADS]; b = e.x; v = e.y; }
+        else { b = base[i - PT_BVH8_SHARED_STACK]; v = bits[i - PT_BVH8_SHARED_STACK]; }
+    }
+};
+#define PT_DECLARE_STACK(name)                                              \
+    __shared__ uint2 name##_shared[PT_BVH8_SHARED_STACK * WF_THREADS];      \
+    SplitStack name;                                                        \
+    name.sh = name##_shared + threadIdx.x
+#else
+#define PT_DECLARE_STACK(name) PrivateStack name
+#endif
+
 // One vote per iteration: a single warp reduction of (busy | holds triangles << 8 | can visit a node << 16)
 // gives the three lane counts the schedule needs.
 static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bool canNode) {
@@ -144,7 +168,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
                                                        uint32_t* workCounter, Hit* __restrict__ hitOut) {
     const uint32_t n = *qCount;
     const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
-    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    PT_DECLARE_STACK(stack);
     WarpFeeder feed;
     Trav t;
     Hit hit;
@@ -154,7 +178,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
         // lanes with nothing in hand take the next group from their stack, or finish
-        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) {
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
             hitOut[p] = hit;
             busy = false;
         }
@@ -177,7 +201,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
             if (hasTri) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
         } else {
-            if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, hit.dst);
+            if (canNode) trav_node_step(sc.all, t, stack, hit.dst);
         }
     }
 }
@@ -253,7 +277,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
                                                         uint32_t* workCounter) {
     const uint32_t n = *jobCount;
     const uint32_t objectCount = P.pc.params.objectCount;
-    uint32_t stackBase[PT_BVH8_STACK], stackBits[PT_BVH8_STACK];
+    PT_DECLARE_STACK(stack);
     WarpFeeder feed;
     Trav t;
     float tE = 0.f;
@@ -261,7 +285,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
-        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stackBase, stackBits)) busy = false;   // not occluded
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) busy = false;   // not occluded
         const bool hasTri = busy && trav_has_tri(t);
         const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
         const unsigned votes = warp_votes(busy, hasTri, canNode);
@@ -284,7 +308,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
                 busy = false;
             }
         } else {
-            if (canNode) trav_node_step(sc.all, t, stackBase, stackBits, tE);
+            if (canNode) trav_node_step(sc.all, t, stack, tE);
         }
     }
 }
