@@ -173,6 +173,21 @@ __device__ __forceinline__ void apply_textures(const WideScene& sc, const ptl::M
 #define PT_SHADE_CONTINUE 1u      /* path goes on to bounce j+1 */
 #define PT_SHADE_CONNECT 2u       /* diffuse bounce: NEE/pdf queries pending for this path */
 
+// Light-sample ray whose result cannot matter: with Afac = albedo/pi * max(0, n.l) == 0 in all three components
+// (light below the surface's horizon, or a black surface) directLight = E * (Afac * g) is a zero whatever the ray
+// finds, as long as g = w1/pdf and E are finite: g is (pdf == 0 ? 0 : w1/pdf) with w1 <= 1, which is finite unless
+// pdf = dst^2 / (cos * 0.444) is NaN, i.e. cos == 0 — excluded by l.y != 0 (cos = -l.y, raytrace.comp:399) — and
+// E is finite when every material's emission is (WideScene::emissionFinite). The sign of that zero can differ
+// from the traced result; it is only ever added to totalColor, which is never -0 (it starts at +0).
+// About half of the NEE rays of an interior scene are of this kind; they are neither searched nor traced.
+PT_HD bool nee_cannot_contribute(const WideScene& sc, const float4& qa, v3 lightSample) {
+    return sc.emissionFinite && qa.x == 0.f && qa.y == 0.f && qa.z == 0.f && lightSample.y != 0.f;
+}
+// The second lightSamplePDF call of diffuseBRDF (raytrace.comp:453, the BSDF-sampled direction) only feeds
+// misWeight, and misWeight is only read at the NEXT hit as emission / misWeight, which trace() uses only when
+// directLight.x == -1 (raytrace.comp:499-500; at j == 0 misWeight is still 1). After a diffuse bounce directLight is
+// the NEE result, so that pdf ray is dead unless the NEE result is EXACTLY -1.0f. It is therefore evaluated lazily:
+// stage_connect_finish reports that rare case and connect_mis_weight_exact() then runs both parts of the query.
 PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p, uint32_t j) {
     const ptl::RayTracerData& td = P.pc.params;
     float4 ro = A.rayO[p], rd = A.rayD[p];
@@ -224,12 +239,17 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
         float realCosinePDF = cosine_hemisphere_pdf(n, cosineSample);
         radiance = albedo * PT_INV_PI * dot(n, cosineSample) / realCosinePDF;
         v3 Afac = albedo * PT_INV_PI * gmax(0.f, dot(n, lightSample));
-        A.qO[p] = f4(origin, cosinePDF);
-        A.qL[p] = f4(lightSample, realCosinePDF);
-        A.qA[p] = f4(Afac, 0.f);
         dirOut = cosineSample;
-        direct = splat3(0.f);                                    // filled in by connect
-        flags |= PT_SHADE_CONNECT;
+        const float4 qa = f4(Afac, 0.f);
+        if (nee_cannot_contribute(sc, qa, lightSample)) {
+            direct = splat3(0.f) * (Afac * 0.f);                 // what connect would store: E = 0 times (Afac * 0); no query
+        } else {
+            A.qO[p] = f4(origin, cosinePDF);
+            A.qL[p] = f4(lightSample, realCosinePDF);
+            A.qA[p] = qa;
+            direct = splat3(0.f);                                // filled in by connect
+            flags |= PT_SHADE_CONNECT;
+        }
     }
     atten = atten * radiance;
 
@@ -318,21 +338,6 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 }
 
 #define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
-// Light-sample ray whose result cannot matter: with Afac = albedo/pi * max(0, n.l) == 0 in all three components
-// (light below the surface's horizon, or a black surface) directLight = E * (Afac * g) is a zero whatever the ray
-// finds, as long as g = w1/pdf and E are finite: g is (pdf == 0 ? 0 : w1/pdf) with w1 <= 1, which is finite unless
-// pdf = dst^2 / (cos * 0.444) is NaN, i.e. cos == 0 — excluded by l.y != 0 (cos = -l.y, raytrace.comp:399) — and
-// E is finite when every material's emission is (WideScene::emissionFinite). The sign of that zero can differ
-// from the traced result; it is only ever added to totalColor, which is never -0 (it starts at +0).
-// About half of the NEE rays of an interior scene are of this kind; they are neither searched nor traced.
-PT_HD bool nee_cannot_contribute(const WideScene& sc, const float4& qa, v3 lightSample) {
-    return sc.emissionFinite && qa.x == 0.f && qa.y == 0.f && qa.z == 0.f && lightSample.y != 0.f;
-}
-// The second lightSamplePDF call of diffuseBRDF (raytrace.comp:453, the BSDF-sampled direction) only feeds
-// misWeight, and misWeight is only read at the NEXT hit as emission / misWeight, which trace() uses only when
-// directLight.x == -1 (raytrace.comp:499-500; at j == 0 misWeight is still 1). After a diffuse bounce directLight is
-// the NEE result, so that pdf ray is dead unless the NEE result is EXACTLY -1.0f. It is therefore evaluated lazily:
-// stage_connect_finish reports that rare case and connect_mis_weight_exact() then runs both parts of the query.
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
     float4 qa = A.qA[p];
@@ -341,7 +346,7 @@ PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const 
     float tL = PT_NO_EMISSIVE;
     // connectAfterExtend: bounce j+1 was already extended; directLight of bounce j is dropped when it missed (:531-534)
     bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
-    if (!dropped && !nee_cannot_contribute(sc, qa, lightSample))
+    if (!dropped)            // (rays that cannot contribute never get here: stage_shade)
         tL = emissive_candidate(sc, xyz(A.qO[p]), lightSample, td.sphereCount, td.objectCount, keyL, matL);  // :443-447
     A.qE[p] = make_float4(tL, 0.f, as_float(keyL), 0.f);
     qa.w = as_float(matL);
