@@ -304,6 +304,33 @@ def main():
         step(e2e=True)
     ms_e2e, _, _ = timed(args.steps, e2e=True)
 
+    # interactive mode (BASELINE.json: "ms/frame @1spp", frames split by image tiles across GPUs): single progressive
+    # frames, each split into row bands over the ranks and gathered on rank 0 (multi_gpu.render_frame_bands)
+    band_img = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
+    cp.attach_accum(band_img.data_ptr())
+    cp.set_option("frames_in_flight", 1)
+    n_inter = max(4, min(32, 4 * args.steps))
+
+    def interactive(k):
+        for f in range(k):
+            if N > 1:
+                multi_gpu.render_frame_bands(cp, pcbuf, 100000 + f, band_img)
+            else:
+                cp.render_frames(pcbuf, 100000 + f, 1)
+
+    interactive(3)
+    fence()
+    i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    i0.record(stream)
+    interactive(n_inter)
+    i1.record(stream)
+    fence()
+    ms_inter = torch.tensor([i0.elapsed_time(i1)], dtype=torch.float64, device=dev)
+    if N > 1:
+        dist.all_reduce(ms_inter, op=dist.ReduceOp.MAX)
+    ms_inter = float(ms_inter.item()) / n_inter
+    cp.attach_accum(stepbuf.data_ptr())
+
     paths_per_step = W * H * F * N
     value = paths_per_step * args.steps / (ms * 1e-3) / 1e6
     e2e_value = paths_per_step * args.steps / (ms_e2e * 1e-3) / 1e6
@@ -373,7 +400,9 @@ def main():
                    e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=208 * N, d2h_bytes_per_step=W * H * 16,
                             ms_per_step=ms_e2e / args.steps),
                    gpu_launches=counters["launches"], roofline=roofline, cpu_baseline=cpu,
-                   ms_per_frame_1spp=ms / args.steps / F)
+                   ms_per_frame_1spp=ms / args.steps / F,
+                   interactive=dict(ms_per_frame=ms_inter, frames=n_inter, split="row bands over %d GPU(s), gathered on rank 0" % N,
+                                    note="one 1-spp progressive frame at a time (latency), vs ms_per_frame_1spp = throughput mode / frames"))
         print(json.dumps(out), flush=True)
     cp.attach_accum(0)
     cp.close()
