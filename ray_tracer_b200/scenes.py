@@ -57,8 +57,9 @@ def _revolve(center, profile_r, profile_y, segments):
     return tris, nrm_of(tris)
 
 
-def _blob(center, radius, rings, segments, bump, seed):
-    """Bumpy sphere (plants, lion heads stand-in)."""
+def _blob(center, radius, rings, segments, bump, seed, outward=False):
+    """Bumpy sphere (plants, lion heads stand-in). The default winding faces inwards (the atrium workload was
+    measured that way and is kept); outward=True winds the triangles so that the outside is the front face."""
     rng = np.random.default_rng(seed)
     th = np.linspace(0, np.pi, rings + 1)[:, None]
     ph = np.linspace(0, 2 * np.pi, segments + 1)[None, :]
@@ -69,6 +70,8 @@ def _blob(center, radius, rings, segments, bump, seed):
     tris = np.concatenate([np.stack([a, b, c], 2).reshape(-1, 3, 3), np.stack([a, c, dd], 2).reshape(-1, 3, 3)])
     area = np.linalg.norm(np.cross(tris[:, 1] - tris[:, 0], tris[:, 2] - tris[:, 0]), axis=1)
     tris = tris[area > 1e-12]                              # pole triangles degenerate
+    if outward:
+        tris = tris[:, ::-1].copy()
     nrm = tris - np.asarray(center)
     nrm /= np.maximum(np.linalg.norm(nrm, axis=-1, keepdims=True), 1e-30)
     return tris, nrm
@@ -181,6 +184,32 @@ def atrium(detail=0.89, with_light=True, seed=1):
     blobs = b.blobs()
     info = dict(triangles=int(sum(counts.values())), objects=len(counts), groups=counts, stand_in_for="sponza.obj")
     return blobs, info
+
+
+def statue_room(triangles=800_000, statue_material=4, seed=7):
+    """C3 stand-in (dragon.obj is not in the reference checkout): a Cornell-style room - white floor/ceiling/back,
+    red and green side walls, the reference's light material on a box at the hard-wired NEE quad - around one
+    high-polygon statue (bumpy blob, ~`triangles` triangles) with the reference's mirror material 4 (gold-metal
+    dragon preset) or dielectric 5. Materials 0..5 are the reference's defaults (src/vk_engine.cpp:689-722)."""
+    b = _scene.SceneBuilder()
+    b.set_spheres(np.zeros(320, np.uint8))
+    b.add_material(_scene.material(albedo=(1, 1, 1)))
+    b.add_material(_scene.material(albedo=(1, 0, 0)))
+    b.add_material(_scene.material(albedo=(0, 1, 0)))
+    b.add_material(_scene.material(albedo=(0, 0, 0), emission=(1, 1, 1), strength=2.4))
+    b.add_material(_scene.material(albedo=(1, 0.84, 0.3), reflectance=1.0))
+    b.add_material(_scene.material(albedo=(1, 1, 1), ior=2.0))
+    lo, hi = np.array([-1.5, -1.52, -4.0]), np.array([1.5, 0.5, 1.5])          # closed: the default camera is inside
+    white = [_box(lo, hi, skip=("x0", "x1"))]
+    b.add_mesh(_pack(*[np.concatenate(x) for x in zip(*white)]), material=0)
+    b.add_mesh(_pack(*_grid([lo[0], hi[1], lo[2]], [0, 0, hi[2] - lo[2]], [0, lo[1] - hi[1], 0], 1, 1)), material=1)
+    b.add_mesh(_pack(*_grid([hi[0], hi[1], hi[2]], [0, 0, lo[2] - hi[2]], [0, lo[1] - hi[1], 0], 1, 1)), material=2)
+    b.add_mesh(_pack(*_box([-1 / 3, -1.5, -1 / 3], [1 / 3, -1.48, 1 / 3])), material=3)
+    n = max(8, int(round((triangles / 2) ** 0.5)))
+    st, sn = _blob([0.0, -0.25, 0.2], 0.62, n, n, 0.22, seed=seed, outward=True)
+    b.add_mesh(_pack(st, sn), material=statue_material)
+    info = dict(triangles=int(len(st)) + 8 + 2 + 2 + 12, objects=5, stand_in_for="dragon.obj")
+    return b.blobs(), info
 
 
 def soup(n, seed=0x5EED, edge=0.01):

@@ -258,6 +258,56 @@ def test_full_size_properties_c4(gpu):
     assert diff.mean() <= 2e-3, diff.mean()
 
 
+def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, tie_budget):
+    """Accumulated `frames` frames of the full image on the GPU against the oracle on one window of it."""
+    cp.clear()
+    cp.render_frames(pc, 0, frames)
+    acc = cp.read_accum()
+    assert np.array_equal(acc[..., 3], np.full((H, W), frames, np.float32)) and np.isfinite(acc).all()
+    with ob.math_mode(1):
+        want = ob.OracleScene(blobs).render_window(pc, W, H, 0, x0, y0, w, h, n=frames)
+    got = acc[y0:y0 + h, x0:x0 + w]
+    if frames == 1:
+        diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
+        assert diff.mean() <= tie_budget, diff.mean()
+    else:                                                   # frame sums: equal up to fp32 summation of equal terms
+        assert relrmse(got[..., :3], want[..., :3]) <= 1e-3
+        close = np.isclose(got, want, rtol=1e-5, atol=1e-6).all(axis=2)
+        assert (~close).mean() <= tie_budget, (~close).mean()
+    return acc
+
+
+def test_full_size_c2_bunny(gpu, bunny_blobs):
+    # BASELINE.json configs[1] at its full size: dielectric bunny in the Cornell shell, 1024 x 1024, 64 frames
+    W = H = 1024
+    pc = ob.default_push_constants(W, H, 10, bunny_blobs["objects"].size // 80)
+    cp = _pass(gpu, bunny_blobs, W, H)
+    acc = _window_check(cp, bunny_blobs, pc, W, H, 64, 480, 470, 40, 40, 5e-3)
+    assert acc[..., :3].mean() / 64 > 0.01
+    c = cp.counters()
+    assert c["paths"] == 64 * W * H
+
+
+def test_full_size_c3_c5_statue_stand_in(gpu):
+    # configs[2] (dragon, mirror material, 1920 x 1080) and the dragon half of configs[4] (3840 x 2160, depth 16) on the
+    # labelled stand-in scene: ~800 k triangles in one object + Cornell-style room
+    from ray_tracer_b200 import PushConstants, scenes
+    blobs, info = scenes.statue_room(800_000)
+    assert info["triangles"] == blobs["triangles"].size // 48
+    W, H = 1920, 1080
+    pc = PushConstants(W, H, 10, info["objects"])
+    cp = _pass(gpu, blobs, W, H)
+    _window_check(cp, blobs, pc.buffer, W, H, 1, 930, 500, 64, 48, 5e-3)       # the statue's silhouette
+    _window_check(cp, blobs, pc.buffer, W, H, 4, 700, 800, 48, 32, 5e-3)       # floor in front of it, 4 frames
+    W, H = 3840, 2160
+    blobs5, info5 = scenes.statue_room(800_000, statue_material=5)             # dielectric: longest paths
+    pc = PushConstants(W, H, 10, info5["objects"])
+    pc["bounceLimit"] = 16
+    cp = _pass(gpu, blobs5, W, H)
+    cp.set_option("frames_in_flight", 2)
+    _window_check(cp, blobs5, pc.buffer, W, H, 1, 1900, 1000, 64, 40, 5e-3)
+
+
 def _textured_scene():
     """Floor + back wall with uv running over [-0.5, 2.5] (exercises REPEAT and CLAMP_TO_EDGE), a wall whose two
     triangles share uv values (the shader's degenerate rule), the NEE light box; two 8x8 textures."""
