@@ -29,6 +29,7 @@ struct WavefrontState {
     uint32_t countSlots = 0;
     int smCount = 148;
     int gridOcclude = 0;
+    int gridShade = 0, gridPrep = 0, gridFinish = 0;
     int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
@@ -210,7 +211,9 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
 // launch the per-warp form issued 0.5 M atomics on each of two addresses and shade's stall samples pointed at them
 // (54 %, profiles/r01/k_shade_v12_by_line.txt); measured gain 0.4 ms of 9.5 per step — the wait was mostly overlapped.
 // Every thread of the block must call it (uniform trip counts).
-#define SHADE_THREADS 256
+#ifndef SHADE_THREADS
+#define SHADE_THREADS 128       // 128 x 8 blocks at 64 registers: 6.3 ms per step; 256 x 3 at 75 registers: 7.0 ms
+#endif
 template <int NQ>
 static __device__ __forceinline__ void block_push(uint32_t* const (&counters)[NQ], const bool (&pred)[NQ], uint32_t (&slot)[NQ]) {
     __shared__ uint32_t warpCount[NQ][SHADE_THREADS / 32];
@@ -238,7 +241,10 @@ static __device__ __forceinline__ void block_push(uint32_t* const (&counters)[NQ
     __syncthreads();            // warpCount is reused by the next round
 }
 
-__global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+#ifndef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(SHADE_THREADS, PT_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                          const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
                                                          uint32_t* nextQueue, uint32_t* nextCount, uint32_t* shadowQueue, uint32_t* shadowCount,
                                                          uint32_t j) {
@@ -258,7 +264,10 @@ __global__ void __launch_bounds__(SHADE_THREADS) k_shade(const __grid_constant__
 }
 
 // connect, part 1: emissive candidate of the light-sample ray; emits the occlusion jobs (path indices)
-__global__ void __launch_bounds__(WF_THREADS) k_connect_prep(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+#ifndef PT_PREP_MIN_BLOCKS
+#define PT_PREP_MIN_BLOCKS 8        // 64 registers: 2.98 ms per step; unconstrained (80 registers, 6 blocks) 3.12; 10 blocks 3.26
+#endif
+__global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                              const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
                                                              uint32_t* jobQueue, uint32_t* jobCount) {
     uint32_t n = *sCount;
@@ -518,8 +527,20 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     // keep a batch below 2^31 paths and ~64M paths (10 GB of path state)
     while (slots > 1 && perSlot * slots > ((size_t)1 << 26)) slots--;
     if (int rc = wf_reserve(c, perSlot * slots, pc.params.bounceLimit)) return rc;
+    // grid-stride kernels: exactly one wave of resident blocks. The former fixed grids (4 or 8 blocks per SM) were 1.33
+    // waves for k_shade and k_connect_prep: the last third ran at a fraction of the occupancy (shade 9.05 -> 7.0 ms,
+    // prep 3.8 -> 3.1 ms per step; 2, 4 or 8 whole waves measured the same or slightly slower).
+    if (!w->gridShade) {
+        int perSm = 0;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_shade, SHADE_THREADS, 0));
+        w->gridShade = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_prep, WF_THREADS, 0));
+        w->gridPrep = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_finish, WF_THREADS, 0));
+        w->gridFinish = std::max(1, perSm) * w->smCount;
+    }
     const int grid = w->smCount * 8;
-    const int gridShade = w->smCount * 4;         // 256-thread blocks
+    const int gridShade = w->gridShade;
     WfParams P;
     P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
     P.useTextures = (c->useTextures && c->dTexTable.p) ? 1u : 0u;
@@ -568,12 +589,12 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                 wf_mark(c, ST_EXTEND);
                 k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
                 wf_mark(c, ST_CONNECT);
-                k_connect_prep<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                k_connect_prep<<<w->gridPrep, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                    (uint32_t*)w->dJobQ.p, oCount + j);
                 wf_mark(c, ST_OCCLUDE);
                 k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
                 wf_mark(c, ST_FINISH);
-                k_connect_finish<<<grid, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                k_connect_finish<<<w->gridFinish, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                      (uint32_t*)w->dJobQ.p, mCount + j);
                 k_connect_mis<<<w->smCount, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
             }
