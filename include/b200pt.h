@@ -118,6 +118,21 @@ int b200pt_attach_accum(b200pt_ctx* ctx, void* device_ptr);
 int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const float* host_rays, uint64_t n,
                        void* host_hits48);
 
+/* GPU build of one object's BVH2 — replaces VulkanEngine::build_bvh(size, triIndex) with update_bvh_bounds,
+ * subdivide_bvh and find_bvh_split_plane (src/vk_engine.cpp:1169-1337): 20-bin SAH, back-swapping partition,
+ * depth-first node numbering. Bit-identical to the reference's sequential build for finite coordinates: same node
+ * bounds, same node order, same final triangle order.
+ *   tri_points      the engine's triPoints (32-byte TrianglePoint), n_points entries
+ *   triangles       the engine's triangles (48-byte Triangle); [first_tri, first_tri + count) is this object's
+ *                   range and is REORDERED IN PLACE as the reference's partition does
+ *   root_index      bvhNodes.size() before the call (= RenderObject.bvhIndex); children indices are absolute
+ *   nodes_out       room for 2 * count - 1 32-byte BVHNodes; *n_nodes_out receives the number written, which the
+ *                   caller appends to bvhNodes
+ *   device_ms       optional: device time of the build without the host<->device copies
+ * No context is needed (the scene is not uploaded yet). Errors: b200pt_global_error(). */
+int b200pt_build_bvh(int device, const void* tri_points, uint32_t n_points, void* triangles, uint32_t first_tri,
+                     uint32_t count, uint32_t root_index, void* nodes_out, uint32_t* n_nodes_out, double* device_ms);
+
 /* Options: "pipeline" 0 = reference-layout per-pixel kernel, 1 = wavefront (default for
  * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1;
  * "textures" 0/1: texture extension (albedo / metalness maps; off = the HEAD shader, which never samples);

@@ -70,6 +70,7 @@ def load_library(path=None):
     L.b200pt_device_accum_ptr.argtypes = [vp, C.POINTER(vp)]
     L.b200pt_device_image_ptr.argtypes = [vp, C.POINTER(vp)]
     L.b200pt_trace_batch.argtypes = [vp, vp, vp, u64, vp]
+    L.b200pt_build_bvh.argtypes = [i32, vp, u32, vp, u32, u32, u32, vp, C.POINTER(u32), C.POINTER(C.c_double)]
     L.b200pt_set_option.argtypes = [vp, C.c_char_p, i64]
     L.b200pt_get_option.argtypes = [vp, C.c_char_p, C.POINTER(i64)]
     L.b200pt_read_counters.argtypes = [vp, vp]
@@ -233,3 +234,19 @@ class ComputePass:
         ms = C.c_float()
         self._check(self.L.b200pt_last_render_ms(self.h, C.byref(ms)), "b200pt_last_render_ms")
         return ms.value
+
+
+def build_bvh(tri_points, triangles, first_tri, count, root_index, device=0):
+    """b200pt_build_bvh on numpy blobs: reorders `triangles` (uint8 view of 48-byte records) in place and returns
+    (nodes uint8 blob, device milliseconds). The GPU restatement of VulkanEngine::build_bvh (src/vk_engine.cpp:1169)."""
+    L = load_library()
+    pts = np.ascontiguousarray(tri_points).view(np.uint8).reshape(-1)
+    tri = triangles.view(np.uint8).reshape(-1)
+    assert tri.flags["C_CONTIGUOUS"] and tri.flags["WRITEABLE"] and pts.size % 32 == 0 and tri.size % 48 == 0
+    nodes = np.zeros((2 * count - 1) * 32, np.uint8)
+    made, ms = C.c_uint32(0), C.c_double(0.0)
+    rc = L.b200pt_build_bvh(device, pts.ctypes.data, pts.size // 32, tri.ctypes.data, first_tri, count, root_index,
+                            nodes.ctypes.data, C.byref(made), C.byref(ms))
+    if rc:
+        raise BackendError("b200pt_build_bvh: " + L.b200pt_global_error().decode())
+    return nodes[: made.value * 32].copy(), ms.value

@@ -18,6 +18,7 @@
 using namespace pt;
 
 static thread_local std::string g_error;
+namespace pt { void set_global_error(const char* what) { g_error = what; } }     // bvh2_build.cu
 
 static int fail(b200pt_ctx* c, int code, const char* fmt, ...) {
     char buf[512];

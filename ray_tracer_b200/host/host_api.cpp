@@ -18,6 +18,13 @@ static Placement mk(const float* pos, const float* rot, const float* scl, uint32
 extern "C" {
 
 void* b200host_builder_create() { return new SceneBuilder(); }
+// fn: address of b200pt_build_bvh (or any function with that signature); NULL restores the host build
+void b200host_set_bvh_builder(void* b, void* fn, int device, uint32_t minTriangles) {
+    ((SceneBuilder*)b)->set_bvh_builder((SceneBuilder::BvhBuildFn)fn, device, minTriangles);
+}
+void b200host_bvh_builder_stats(void* b, double* deviceMs, uint32_t* builds) {
+    *deviceMs = ((SceneBuilder*)b)->bvhDeviceMs; *builds = ((SceneBuilder*)b)->bvhPluggedBuilds;
+}
 void b200host_builder_destroy(void* b) { delete (SceneBuilder*)b; }
 
 // 0 ok, 1 file not found (the reference silently skips it), 2 malformed input

@@ -375,6 +375,17 @@ float SceneBuilder::best_split(const ptl::BVHNode& node, int& axis, float& pos) 
 
 void SceneBuilder::build_bvh(uint32_t firstTri, uint32_t count) {   // build_bvh :1169-1194 + subdivide_bvh :1212-1277
     if (count == 0) throw std::runtime_error("object without triangles");
+    if (bvhFn_ && count >= bvhMinTris_) {                   // plugged-in builder (b200pt_build_bvh): same bytes
+        uint32_t root = (uint32_t)nodes.size(), made = 0;
+        double ms = 0.0;
+        std::vector<ptl::BVHNode> out((size_t)count * 2 - 1);
+        if (bvhFn_(bvhDevice_, points.data(), (uint32_t)points.size(), triangles.data(), firstTri, count, root, out.data(), &made, &ms))
+            throw std::runtime_error("plugged-in BVH builder failed");
+        nodes.insert(nodes.end(), out.begin(), out.begin() + made);
+        nodesUsed_ = (uint32_t)nodes.size();
+        bvhDeviceMs += ms; bvhPluggedBuilds++;
+        return;                                             // centroids_ keep their original order: only used by build_bvh of this range
+    }
     nodesUsed_++;
     uint32_t root = (uint32_t)nodes.size();
     ptl::BVHNode zero;

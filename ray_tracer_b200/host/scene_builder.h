@@ -44,12 +44,24 @@ class SceneBuilder {
     void default_scene(const std::string& assetDir);
     static void object_matrix(const Placement& p, float out16[16]);   // translate*rotX*rotY*rotZ*scale (:807-811)
 
+    // Optional replacement for build_bvh: the signature of b200pt_build_bvh (include/b200pt.h), so the CUDA library's
+    // entry point can be plugged in without this library linking against it. Objects with fewer triangles than
+    // `minTriangles` keep the host build. Both produce the same bytes.
+    typedef int (*BvhBuildFn)(int device, const void* triPoints, uint32_t nPoints, void* triangles, uint32_t firstTri, uint32_t count,
+                              uint32_t rootIndex, void* nodesOut, uint32_t* nNodesOut, double* deviceMs);
+    void set_bvh_builder(BvhBuildFn fn, int device, uint32_t minTriangles) { bvhFn_ = fn; bvhDevice_ = device; bvhMinTris_ = minTriangles; }
+    double bvhDeviceMs = 0.0;                // accumulated device time of plugged-in builds
+    uint32_t bvhPluggedBuilds = 0;
+
    private:
     struct C3 { float x, y, z; };
     std::vector<C3> centroids_;
     std::map<std::string, uint32_t> loadedObjects_;
     std::map<std::string, uint32_t> loadedMaterials_;
     uint32_t nodesUsed_ = 0;
+    BvhBuildFn bvhFn_ = nullptr;
+    int bvhDevice_ = 0;
+    uint32_t bvhMinTris_ = 0;
 
     uint32_t push_face(const ptl::TrianglePoint* v, bool frontOnly);
     void finish_object(size_t firstTri, const Placement& where, uint32_t material, bool smooth, uint32_t sampler);

@@ -35,6 +35,8 @@ def _host():
         L.b200host_copy.argtypes = [vp, i32, vp]
         L.b200host_texture_path.argtypes = [vp, u32, C.c_char_p, i32]
         L.b200host_object_matrix.argtypes = [vp, vp, vp, vp]
+        L.b200host_set_bvh_builder.argtypes = [vp, vp, i32, u32]
+        L.b200host_bvh_builder_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
         _lib = L
     return _lib
 
@@ -75,6 +77,18 @@ class SceneBuilder:
         if getattr(self, "h", None):
             _host().b200host_builder_destroy(self.h)
             self.h = None
+
+    def use_gpu_bvh(self, device=0, min_triangles=4096):
+        """Objects with at least `min_triangles` triangles get their BVH2 from b200pt_build_bvh (CUDA, bit-identical to
+        the host build). Needs libb200pt.so and a GPU; fails loudly otherwise."""
+        from . import backend
+        fn = C.cast(backend.load_library().b200pt_build_bvh, C.c_void_p)
+        _host().b200host_set_bvh_builder(self.h, fn, device, min_triangles)
+
+    def gpu_bvh_stats(self):
+        ms, n = C.c_double(0.0), C.c_uint32(0)
+        _host().b200host_bvh_builder_stats(self.h, C.byref(ms), C.byref(n))
+        return dict(device_ms=ms.value, builds=n.value)
 
     def read_obj(self, path, position=(0, 0, 0), rotation=(0, 0, 0), scale=(1, 1, 1), sampler_index=0, front_only=False,
                  material=0):
