@@ -27,7 +27,7 @@ EXPORTS = (
     "b200pt_clear b200pt_read_accum_f32 b200pt_read_image_f32 b200pt_write_image_f32 b200pt_read_rgba8 "
     "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch "
     "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_read_stage_times "
-    "b200pt_last_render_ms").split()
+    "b200pt_last_render_ms b200pt_build_bvh").split()
 
 
 class BackendError(RuntimeError):

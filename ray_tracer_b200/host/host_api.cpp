@@ -1,5 +1,6 @@
 // C entry points of the host-side scene builder (libb200pt_host.so), for the Python bench/tests and
 // for any C caller that wants reference-layout buffers from OBJ/MTL files or procedural meshes.
+#include <cstdio>
 #include <cstring>
 #include <string>
 
@@ -81,6 +82,88 @@ int b200host_texture_path(void* b, uint32_t slot, char* dst, int cap) {
 }
 void b200host_object_matrix(const float* pos, const float* rot, const float* scl, float* out16) {
     SceneBuilder::object_matrix(mk(pos, rot, scl, 0, 0), out16);
+}
+
+// ---- on-disk scene cache: the six storage buffers of prepare_storage_buffers() (src/vk_engine.cpp:680-758)
+// exactly as they are uploaded, so a large OBJ is parsed and its BVH built once. Layout, little endian:
+//   0   char[8]  "B2PTSCN1"
+//   8   u32      version (1), u32 reserved
+//   16  u64[6]   record counts: spheres, materials, triPoints, triangles, objects, bvhNodes
+//   64  u32[6]   record sizes: 32, 64, 32, 48, 80, 32
+//   88  u64      FNV-1a 64 of the payload
+//   96  ... 128  zero
+//   128 payload: the six arrays in that order, each padded to a multiple of 64 bytes
+static const uint32_t kRecord[6] = {32, 64, 32, 48, 80, 32};
+static uint64_t fnv1a(uint64_t h, const unsigned char* p, size_t n) {
+    for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 1099511628211ull; }
+    return h;
+}
+static size_t pad64(size_t n) { return (n + 63) & ~(size_t)63; }
+
+// 0 ok, 1 cannot open/write
+int b200host_scene_write(const char* path, const void* const* blobs6, const uint64_t* counts6) {
+    unsigned char head[128] = {0};
+    std::memcpy(head, "B2PTSCN1", 8);
+    uint32_t version = 1;
+    std::memcpy(head + 8, &version, 4);
+    std::memcpy(head + 16, counts6, 48);
+    std::memcpy(head + 64, kRecord, 24);
+    uint64_t h = 14695981039346656037ull;
+    for (int i = 0; i < 6; ++i) h = fnv1a(h, (const unsigned char*)blobs6[i], (size_t)counts6[i] * kRecord[i]);
+    std::memcpy(head + 88, &h, 8);
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return 1;
+    bool ok = std::fwrite(head, 1, 128, f) == 128;
+    static const unsigned char zeros[64] = {0};
+    for (int i = 0; i < 6 && ok; ++i) {
+        size_t n = (size_t)counts6[i] * kRecord[i];
+        ok = (n == 0 || std::fwrite(blobs6[i], 1, n, f) == n) && std::fwrite(zeros, 1, pad64(n) - n, f) == pad64(n) - n;
+    }
+    ok = std::fclose(f) == 0 && ok;
+    return ok ? 0 : 1;
+}
+// Reads the header: 0 ok, 1 cannot open, 2 not a scene file / unsupported version / record sizes differ, 3 truncated
+int b200host_scene_probe(const char* path, uint64_t* counts6) {
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return 1;
+    unsigned char head[128];
+    size_t got = std::fread(head, 1, 128, f);
+    int rc = 0;
+    uint32_t version = 0;
+    if (got != 128 || std::memcmp(head, "B2PTSCN1", 8) != 0) rc = 2;
+    else {
+        std::memcpy(&version, head + 8, 4);
+        if (version != 1 || std::memcmp(head + 64, kRecord, 24) != 0) rc = 2;
+    }
+    if (!rc) {
+        std::memcpy(counts6, head + 16, 48);
+        size_t need = 128;
+        for (int i = 0; i < 6; ++i) need += pad64((size_t)counts6[i] * kRecord[i]);
+        std::fseek(f, 0, SEEK_END);
+        if ((size_t)std::ftell(f) < need) rc = 3;
+    }
+    std::fclose(f);
+    return rc;
+}
+// Fills six caller-allocated arrays (sizes from b200host_scene_probe): 0 ok, 1 cannot open, 3 truncated, 4 checksum mismatch
+int b200host_scene_read(const char* path, void* const* blobs6) {
+    uint64_t counts[6];
+    if (int rc = b200host_scene_probe(path, counts)) return rc;
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return 1;
+    unsigned char head[128];
+    int rc = std::fread(head, 1, 128, f) == 128 ? 0 : 3;
+    uint64_t h = 14695981039346656037ull, want = 0;
+    std::memcpy(&want, head + 88, 8);
+    for (int i = 0; i < 6 && !rc; ++i) {
+        size_t n = (size_t)counts[i] * kRecord[i];
+        if (n && std::fread(blobs6[i], 1, n, f) != n) rc = 3;
+        else if (std::fseek(f, (long)(pad64(n) - n), SEEK_CUR) != 0) rc = 3;
+        else h = fnv1a(h, (const unsigned char*)blobs6[i], n);
+    }
+    std::fclose(f);
+    if (!rc && h != want) rc = 4;
+    return rc;
 }
 
 }  // extern "C"

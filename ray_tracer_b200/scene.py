@@ -35,6 +35,9 @@ def _host():
         L.b200host_copy.argtypes = [vp, i32, vp]
         L.b200host_texture_path.argtypes = [vp, u32, C.c_char_p, i32]
         L.b200host_object_matrix.argtypes = [vp, vp, vp, vp]
+        L.b200host_scene_write.argtypes = [C.c_char_p, vp, vp]
+        L.b200host_scene_probe.argtypes = [C.c_char_p, vp]
+        L.b200host_scene_read.argtypes = [C.c_char_p, vp]
         L.b200host_set_bvh_builder.argtypes = [vp, vp, i32, u32]
         L.b200host_bvh_builder_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
         _lib = L
@@ -151,3 +154,46 @@ class SceneBuilder:
             _host().b200host_texture_path(self.h, i, buf, 4096)
             out.append(buf.value.decode())
         return out
+
+
+class SceneFileError(RuntimeError):
+    pass
+
+
+def save_scene(path, blobs):
+    """Writes the six reference-layout buffers to one file (host/host_api.cpp: layout and checksum)."""
+    arrs = [np.ascontiguousarray(blobs[k]).view(np.uint8).reshape(-1) for k in BLOB_NAMES]
+    for a, sz, k in zip(arrs, BLOB_ITEMSIZE, BLOB_NAMES):
+        if a.size % sz:
+            raise SceneFileError("%s: %d bytes is not a multiple of %d" % (k, a.size, sz))
+    ptrs = (C.c_void_p * 6)(*[a.ctypes.data for a in arrs])
+    counts = (C.c_uint64 * 6)(*[a.size // sz for a, sz in zip(arrs, BLOB_ITEMSIZE)])
+    if _host().b200host_scene_write(str(path).encode(), ptrs, counts):
+        raise SceneFileError("cannot write " + str(path))
+
+
+def load_scene(path):
+    """Reads a file written by save_scene -> blobs dict; raises SceneFileError on a foreign, truncated or corrupt file."""
+    why = {1: "cannot open", 2: "not a scene file of this version", 3: "truncated", 4: "checksum mismatch"}
+    counts = (C.c_uint64 * 6)()
+    rc = _host().b200host_scene_probe(str(path).encode(), counts)
+    if rc:
+        raise SceneFileError("%s: %s" % (path, why[rc]))
+    arrs = [np.zeros(int(c) * sz, np.uint8) for c, sz in zip(counts, BLOB_ITEMSIZE)]
+    ptrs = (C.c_void_p * 6)(*[a.ctypes.data for a in arrs])
+    rc = _host().b200host_scene_read(str(path).encode(), ptrs)
+    if rc:
+        raise SceneFileError("%s: %s" % (path, why[rc]))
+    return dict(zip(BLOB_NAMES, arrs))
+
+
+def cached_scene(path, make):
+    """blobs from `path` if it holds a valid scene file, else make() -> blobs, written to `path` for the next run."""
+    if os.path.exists(path):
+        try:
+            return load_scene(path)
+        except SceneFileError:
+            pass
+    blobs = make()
+    save_scene(path, blobs)
+    return blobs

@@ -121,3 +121,43 @@ def test_missing_file_and_object_matrix(scene_mod):
     b = scene_mod.SceneBuilder()
     assert b.read_obj("/nonexistent/file.obj") is False      # the reference returns silently (src/vk_engine.cpp:834)
     assert b.counts()[4] == 0
+
+
+def test_scene_file_round_trip_and_damage(tmp_path, cornell_blobs):
+    # on-disk scene cache: the six storage buffers byte for byte, checked on the way back in
+    from ray_tracer_b200 import scene
+    p = tmp_path / "cornell.b2pt"
+    scene.save_scene(p, cornell_blobs)
+    back = scene.load_scene(p)
+    assert set(back) == set(scene.BLOB_NAMES)
+    for k in scene.BLOB_NAMES:
+        assert np.array_equal(back[k], cornell_blobs[k]), k
+    raw = bytearray(p.read_bytes())
+    assert raw[:8] == b"B2PTSCN1" and len(raw) % 64 == 0
+    # empty arrays are legal (a scene with spheres only)
+    empty = {k: np.zeros(0, np.uint8) for k in scene.BLOB_NAMES}
+    empty["spheres"] = cornell_blobs["spheres"]
+    scene.save_scene(tmp_path / "e.b2pt", empty)
+    assert scene.load_scene(tmp_path / "e.b2pt")["triangles"].size == 0
+    # damage: flipped payload byte, truncation, foreign file, wrong record multiple
+    bad = bytearray(raw)
+    bad[len(bad) // 2] ^= 0x40
+    (tmp_path / "flip.b2pt").write_bytes(bad)
+    with pytest.raises(scene.SceneFileError, match="checksum"):
+        scene.load_scene(tmp_path / "flip.b2pt")
+    (tmp_path / "cut.b2pt").write_bytes(raw[: len(raw) - 100])
+    with pytest.raises(scene.SceneFileError, match="truncated"):
+        scene.load_scene(tmp_path / "cut.b2pt")
+    (tmp_path / "other.b2pt").write_bytes(b"OBJ " * 100)
+    with pytest.raises(scene.SceneFileError, match="not a scene file"):
+        scene.load_scene(tmp_path / "other.b2pt")
+    with pytest.raises(scene.SceneFileError):
+        scene.load_scene(tmp_path / "missing.b2pt")
+    with pytest.raises(scene.SceneFileError, match="multiple"):
+        scene.save_scene(tmp_path / "x.b2pt", dict(cornell_blobs, nodes=cornell_blobs["nodes"][:-1]))
+    # cached_scene: builds once, then reads
+    calls = []
+    make = lambda: (calls.append(1), cornell_blobs)[1]
+    a = scene.cached_scene(str(tmp_path / "c.b2pt"), make)
+    b = scene.cached_scene(str(tmp_path / "c.b2pt"), make)
+    assert len(calls) == 1 and all(np.array_equal(a[k], b[k]) for k in scene.BLOB_NAMES)
