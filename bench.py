@@ -47,9 +47,10 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--bounce-limit", type=int, default=8)
-    ap.add_argument("--workload", default="atrium", choices=["atrium", "cornell", "soup"])
+    ap.add_argument("--workload", default="atrium", choices=["atrium", "cornell", "soup", "statue"])
     ap.add_argument("--soup-triangles", type=int, default=10_000_000)
     ap.add_argument("--obj", default=None, help="path of a real sponza.obj (optional; replaces the stand-in)")
+    ap.add_argument("--gpu-bvh", action="store_true", help="build the reference BVH2 of the procedural scenes with b200pt_build_bvh")
     ap.add_argument("--pipeline", type=int, default=1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="960x540x12", help="WxHxframes of the CPU baseline sample")
@@ -63,6 +64,8 @@ def make_workload(args):
     """-> (blobs, PushConstants, config dict)."""
     from ray_tracer_b200 import PushConstants, scenes
     W, H = args.width, args.height
+    if args.gpu_bvh and args.impl == "b200":
+        scenes.GPU_BVH = (int(os.environ.get("LOCAL_RANK", "0")), 4096)
     if args.workload == "atrium":
         if args.obj:
             from ray_tracer_b200 import scene as hs
@@ -79,6 +82,10 @@ def make_workload(args):
             name = "C4 Sponza STAND-IN: procedural atrium (sponza.obj absent from the reference checkout)"
         pc = PushConstants(W, H, blobs["spheres"].size // 32, info["objects"])
         scenes.atrium_camera(pc)
+    elif args.workload == "statue":
+        blobs, info = scenes.statue_room(800_000)
+        pc = PushConstants(W, H, blobs["spheres"].size // 32, info["objects"])
+        name = "C3 dragon STAND-IN: mirror statue, ~800k triangles, in a Cornell-style room (dragon.obj absent from the reference checkout)"
     elif args.workload == "soup":
         blobs, info = scenes.soup(args.soup_triangles)
         pc = PushConstants(W, H, 0, 1)
@@ -224,7 +231,10 @@ def main():
         dist.barrier()
     import ray_tracer_b200 as rt
 
+    t_build = time.time()
     blobs, pc, cfg = make_workload(args)
+    cfg["scene_build_s"] = round(time.time() - t_build, 3)
+    cfg["bvh2_builder"] = "b200pt_build_bvh (GPU)" if args.gpu_bvh else "host"
     W, H, F, N = args.width, args.height, args.frames_per_step, world
     cp = rt.ComputePass(W, H, device=local)
     stream = torch.cuda.Stream(dev)              # a real (non-default) stream: handle 0 would mean "the context's own"

@@ -14,6 +14,16 @@ import numpy as np
 from . import scene as _scene
 
 
+GPU_BVH = None     # (device, min_triangles): objects at least that large get their BVH2 from b200pt_build_bvh (same bytes)
+
+
+def _builder():
+    b = _scene.SceneBuilder()
+    if GPU_BVH is not None:
+        b.use_gpu_bvh(*GPU_BVH)
+    return b
+
+
 def _pack(tri_pos, tri_nrm):
     """(n,3,3) positions + (n,3,3) normals -> (n,3,8) TrianglePoints (uv = 0)."""
     n = tri_pos.shape[0]
@@ -164,7 +174,7 @@ def atrium(detail=0.89, with_light=True, seed=1):
             c = np.array([rng.uniform(-2.8, 2.8), rng.uniform(-4.5, 0.3), rng.uniform(-4.8, 8.8)])
             h = rng.uniform(0.03, 0.12, 3)
             groups[g].append(_box(c - h, c + h))
-    b = _scene.SceneBuilder()
+    b = _builder()
     b.set_spheres(np.zeros(320, np.uint8))      # spheres.resize(10): ten zero spheres, always (src/vk_engine.cpp:682)
     albedo = rng.uniform(0.25, 0.9, (25, 3))
     albedo[13], albedo[14], albedo[15] = (0.8, 0.15, 0.12), (0.15, 0.7, 0.2), (0.15, 0.2, 0.8)
@@ -191,7 +201,7 @@ def statue_room(triangles=800_000, statue_material=4, seed=7):
     red and green side walls, the reference's light material on a box at the hard-wired NEE quad - around one
     high-polygon statue (bumpy blob, ~`triangles` triangles) with the reference's mirror material 4 (gold-metal
     dragon preset) or dielectric 5. Materials 0..5 are the reference's defaults (src/vk_engine.cpp:689-722)."""
-    b = _scene.SceneBuilder()
+    b = _builder()
     b.set_spheres(np.zeros(320, np.uint8))
     b.add_material(_scene.material(albedo=(1, 1, 1)))
     b.add_material(_scene.material(albedo=(1, 0, 0)))
@@ -219,7 +229,7 @@ def soup(n, seed=0x5EED, edge=0.01):
     p = c + rng.uniform(-edge, edge, (n, 3, 3))
     fn = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
     fn /= np.maximum(np.linalg.norm(fn, axis=1, keepdims=True), 1e-30)
-    b = _scene.SceneBuilder()
+    b = _builder()
     b.add_material(_scene.material())
     b.add_mesh(_pack(p, np.repeat(fn[:, None, :], 3, 1)), material=0)
     return b.blobs(), dict(triangles=n, objects=1)
