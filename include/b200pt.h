@@ -138,7 +138,9 @@ int b200pt_build_bvh(int device, const void* tri_points, uint32_t n_points, void
  * "textures" 0/1: texture extension (albedo / metalness maps; off = the HEAD shader, which never samples);
  * "storage_rgba8" 0/1: b200pt_render stores the image at unorm8 precision, as the reference's rgba8 image does;
  * "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32: scheduling of the wavefront kernels
- * (results do not depend on them). Unknown keys fail. */
+ * (results do not depend on them); "wide_build" 1 (default) / 0: the internal wide BVH of all triangles is built on
+ * the device / on the host at b200pt_upload_scene and b200pt_update_* (read before the upload; images do not depend
+ * on it). Read-only: "last_scene_build_us", "last_wide_device_us". Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
 

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200pt.so")
-SOURCES = ["api.cu", "megakernel.cu", "wavefront.cu", "bvh2_build.cu"]
+SOURCES = ["api.cu", "megakernel.cu", "wavefront.cu", "bvh2_build.cu", "wide_build.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-O2,-fno-fast-math,-ffp-contract=off", "-shared",
               "-cudart", "static"]

@@ -428,6 +428,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "trav_tri_vote") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_tri_vote must be 1..32"); c->triVote32 = (int)v; return 0; }
     if (k == "trav_fetch_idle") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_fetch_idle must be 1..32"); c->fetchMinIdle = (int)v; return 0; }
     if (k == "share_primary") { c->sharePrimary = v != 0; return 0; }
+    if (k == "wide_build") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "wide_build must be 0 (host) or 1 (device)"); c->wideBuild = (int)v; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
@@ -441,6 +442,9 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "trav_tri_vote") { *v = c->triVote32; return 0; }
     if (k == "trav_fetch_idle") { *v = c->fetchMinIdle; return 0; }
     if (k == "share_primary") { *v = c->sharePrimary; return 0; }
+    if (k == "wide_build") { *v = c->wideBuild; return 0; }
+    if (k == "last_scene_build_us") { *v = (int64_t)(c->lastSceneBuildMs * 1000.0); return 0; }      // read-only
+    if (k == "last_wide_device_us") { *v = (int64_t)(c->lastWideDeviceMs * 1000.0); return 0; }      // read-only
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 

@@ -159,7 +159,7 @@ __device__ __forceinline__ uint32_t dest(uint32_t k, uint32_t n, bool isLeft, ui
 }
 
 // One block per node of the level list: best split, partition, children.
-__global__ void k_split(Dev d, const uint32_t* __restrict__ list, uint32_t nList) {
+__global__ void __launch_bounds__(1024) k_split(Dev d, const uint32_t* __restrict__ list, uint32_t nList) {
     __shared__ SplitShared s;
     const uint32_t tid = threadIdx.x, nT = blockDim.x;
     for (uint32_t item = blockIdx.x; item < nList; item += gridDim.x) {

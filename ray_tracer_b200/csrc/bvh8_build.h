@@ -6,6 +6,8 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -31,7 +33,54 @@ struct WideSceneHost {
     uint32_t uniqSphereMask = 0, emisSphereMask = 0, plainSphereMask = 0;
     bool emissionFinite = true;
     float emisLo[3] = {0, 0, 0}, emisHi[3] = {0, 0, 0};
+    // for the device build of `all` (wide_build.cu): every (object, triangle) instance and the BVH2 leaf of each triangle
+    std::vector<uint32_t> instObject, instTri, leafOf;
 };
+
+struct WideBox { float lo[3], hi[3]; };
+
+// Records of one (object, triangle) instance; shared by the host builder and the device build so both produce the
+// same bytes. Returns false when a world-space vertex is not finite (such a triangle can never be hit: dropped).
+PT_HD bool wide_make_records(uint32_t o, uint32_t t, const ptl::RenderObject& ob, const ptl::Triangle& tr, const ptl::TrianglePoint& a,
+                             const ptl::TrianglePoint& b, const ptl::TrianglePoint& c, uint32_t leaf, const UpNode* up, uint32_t xformId,
+                             bool em, PrimRecord& r, ShadeRecord& s, UvRecord& uvr, WideBox& bx) {
+    v3 pa = mk3(a.px, a.py, a.pz), pb = mk3(b.px, b.py, b.pz), pc = mk3(c.px, c.py, c.pz);
+    TriEdges te = tri_edges(pa, pb, pc);
+    r.p0x = te.p0.x; r.p0y = te.p0.y; r.p0z = te.p0.z; r.objectIndex = o;
+    r.e1x = te.e1.x; r.e1y = te.e1.y; r.e1z = te.e1.z;
+    r.triIndexFlags = (t & PT_PRIM_TRIMASK) | (tr.frontOnly ? PT_PRIM_FRONTONLY : 0u) | (em ? PT_PRIM_EMISSIVE : 0u);
+    if (leaf != 0xffffffffu) {
+        const UpNode lf = up[leaf];
+        if (lf.minX == lf.maxX) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_X;
+        if (lf.minY == lf.maxY) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Y;
+        if (lf.minZ == lf.maxZ) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Z;
+        if (lf.parent == 0xffffffffu) r.triIndexFlags |= PT_PRIM_LEAF_IS_ROOT;
+    }
+    r.e2x = te.e2.x; r.e2y = te.e2.y; r.e2z = te.e2.z; r.xformId = xformId;
+    r.nx = te.n.x; r.ny = te.n.y; r.nz = te.n.z; r.leafNode = leaf;
+    s.n0x = a.nx; s.n0y = a.ny; s.n0z = a.nz; s.materialIndex = ob.materialIndex;
+    s.n1x = b.nx; s.n1y = b.ny; s.n1z = b.nz; s.objectIndex = o;
+    s.n2x = c.nx; s.n2y = c.ny; s.n2z = c.nz; s.triIndex = t;
+    // world box, padded: the hit the object-space test accepts lies within rounding of it
+    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] = 1e30f; bx.hi[ax] = -1e30f; }
+    v3 w[3] = {mul_point(ob.m, pa), mul_point(ob.m, pb), mul_point(ob.m, pc)};
+    bool finite = true;
+    for (int k = 0; k < 3; ++k) {
+        float q[3] = {w[k].x, w[k].y, w[k].z};
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(fabsf(q[ax]) < 1e30f)) finite = false;
+            bx.lo[ax] = fminf(bx.lo[ax], q[ax]); bx.hi[ax] = fmaxf(bx.hi[ax], q[ax]);
+        }
+    }
+    float mag = 0.f;
+    for (int ax = 0; ax < 3; ++ax) mag = fmaxf(mag, fmaxf(fabsf(bx.lo[ax]), fabsf(bx.hi[ax])));
+    float pad = 1e-5f * mag + 1e-7f;
+    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
+    uvr.u0 = a.u; uvr.v0 = a.v; uvr.u1 = b.u; uvr.v1 = b.v; uvr.u2 = c.u; uvr.v2 = c.v;
+    uvr.samplerIndex = ob.samplerIndex;
+    uvr.degenerate = ((a.u == b.u && a.v == b.v) || (b.u == c.u && b.v == c.v) || (c.u == a.u && c.v == a.v)) ? 1u : 0u;
+    return finite;
+}
 
 namespace b8 {
 
@@ -266,19 +315,25 @@ inline void bvh8_build(const std::vector<b8::Box>& boxes, const std::vector<b8::
     out.nodes.clear(); out.prims.clear(); out.shade.clear(); out.uvs.clear(); out.maxDepth = 0;
     out.nodes.resize(1);
     if (boxes.empty()) { std::memset(&out.nodes[0], 0, sizeof(Bvh8Node)); return; }
+    auto t0 = std::chrono::steady_clock::now();
     b8::Builder2 B(boxes);
     uint32_t root = B.build(0, (uint32_t)boxes.size());
+    auto t1 = std::chrono::steady_clock::now();
     out.prims.reserve(boxes.size()); out.shade.reserve(boxes.size()); out.uvs.reserve(boxes.size());
     bvh8_emit(B, inst, primOf, shadeOf, uvOf, root, 0, 1, out);
+    if (std::getenv("B200PT_BUILD_TIMING"))
+        fprintf(stderr, "[bvh8] %zu prims: binary build %.3f s, collapse+emit %.3f s\n", boxes.size(),
+                std::chrono::duration<double>(t1 - t0).count(), std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count());
 }
 
 // Reference-layout buffers -> WideSceneHost. Returns nullptr on success or a message.
 inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials,
                                     const std::vector<ptl::TrianglePoint>& points, const std::vector<ptl::Triangle>& tris,
                                     const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes,
-                                    WideSceneHost& out) {
+                                    WideSceneHost& out, bool buildAll = true) {
     using namespace b8;
     out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
+    out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
     auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
     out.uniqSphereMask = out.emisSphereMask = out.plainSphereMask = 0;
     for (size_t i = 0; i < spheres.size(); ++i) {
@@ -322,6 +377,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
         else { out.up[nodes[i].index].parent = (uint32_t)i; out.up[nodes[i].index + 1].parent = (uint32_t)i; }
     }
 
+    auto tPrep = std::chrono::steady_clock::now();
     std::vector<Box> boxes, boxesE;
     std::vector<Instance> inst, instE;
     std::vector<PrimRecord> prim, primE;
@@ -342,48 +398,14 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
         bool em = emissive(ob.materialIndex);
         if (em && !triList.empty()) out.anyEmissive = true;
         for (uint32_t t : triList) {
+            if (!buildAll) { out.instObject.push_back((uint32_t)o); out.instTri.push_back(t); if (!em) continue; }
             const ptl::Triangle& tr = tris[t];
-            const ptl::TrianglePoint& a = points[tr.v0]; const ptl::TrianglePoint& b = points[tr.v1]; const ptl::TrianglePoint& c = points[tr.v2];
-            v3 pa = mk3(a.px, a.py, a.pz), pb = mk3(b.px, b.py, b.pz), pc = mk3(c.px, c.py, c.pz);
-            TriEdges te = tri_edges(pa, pb, pc);
-            PrimRecord r;
-            r.p0x = te.p0.x; r.p0y = te.p0.y; r.p0z = te.p0.z; r.objectIndex = (uint32_t)o;
-            r.e1x = te.e1.x; r.e1y = te.e1.y; r.e1z = te.e1.z;
-            r.triIndexFlags = (t & PT_PRIM_TRIMASK) | (tr.frontOnly ? PT_PRIM_FRONTONLY : 0u) | (em ? PT_PRIM_EMISSIVE : 0u);
-            if (leafOf[t] != 0xffffffffu) {
-                const UpNode& lf = out.up[leafOf[t]];
-                if (lf.minX == lf.maxX) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_X;
-                if (lf.minY == lf.maxY) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Y;
-                if (lf.minZ == lf.maxZ) r.triIndexFlags |= PT_PRIM_LEAF_FLAT_Z;
-                if (lf.parent == 0xffffffffu) r.triIndexFlags |= PT_PRIM_LEAF_IS_ROOT;
-            }
-            r.e2x = te.e2.x; r.e2y = te.e2.y; r.e2z = te.e2.z; r.xformId = out.objXform[o];
-            r.nx = te.n.x; r.ny = te.n.y; r.nz = te.n.z; r.leafNode = leafOf[t];
-            ShadeRecord s;
-            s.n0x = a.nx; s.n0y = a.ny; s.n0z = a.nz; s.materialIndex = ob.materialIndex;
-            s.n1x = b.nx; s.n1y = b.ny; s.n1z = b.nz; s.objectIndex = (uint32_t)o;
-            s.n2x = c.nx; s.n2y = c.ny; s.n2z = c.nz; s.triIndex = t;
-            // world box, padded: the hit the object-space test accepts lies within rounding of it
-            Box bx; box_reset(bx);
-            v3 w[3] = {mul_point(ob.m, pa), mul_point(ob.m, pb), mul_point(ob.m, pc)};
-            bool finite = true;
-            for (int k = 0; k < 3; ++k) {
-                float q[3] = {w[k].x, w[k].y, w[k].z};
-                for (int ax = 0; ax < 3; ++ax) {
-                    if (!(std::fabs(q[ax]) < 1e30f)) finite = false;
-                    bx.lo[ax] = std::min(bx.lo[ax], q[ax]); bx.hi[ax] = std::max(bx.hi[ax], q[ax]);
-                }
-            }
-            if (!finite) continue;     // NaN/Inf vertices can never produce an accepted hit (all comparisons false)
-            float mag = 0.f;
-            for (int ax = 0; ax < 3; ++ax) mag = std::max(mag, std::max(std::fabs(bx.lo[ax]), std::fabs(bx.hi[ax])));
-            float pad = 1e-5f * mag + 1e-7f;
-            for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
-            UvRecord uvr;
-            uvr.u0 = a.u; uvr.v0 = a.v; uvr.u1 = b.u; uvr.v1 = b.v; uvr.u2 = c.u; uvr.v2 = c.v;
-            uvr.samplerIndex = ob.samplerIndex;
-            uvr.degenerate = ((a.u == b.u && a.v == b.v) || (b.u == c.u && b.v == c.v) || (c.u == a.u && c.v == a.v)) ? 1u : 0u;
-            boxes.push_back(bx); inst.push_back({(uint32_t)o, t}); prim.push_back(r); shade.push_back(s); uvs.push_back(uvr);
+            PrimRecord r; ShadeRecord s; UvRecord uvr; WideBox wb;
+            if (!wide_make_records((uint32_t)o, t, ob, tr, points[tr.v0], points[tr.v1], points[tr.v2], leafOf[t], out.up.data(),
+                                   out.objXform[o], em, r, s, uvr, wb)) continue;   // NaN/Inf vertices can never produce an accepted hit
+            Box bx;
+            for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] = wb.lo[ax]; bx.hi[ax] = wb.hi[ax]; }
+            if (buildAll) { boxes.push_back(bx); inst.push_back({(uint32_t)o, t}); prim.push_back(r); shade.push_back(s); uvs.push_back(uvr); }
             if (em) { boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); uvsE.push_back(uvr); }
         }
     }
@@ -398,7 +420,10 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             out.emisLo[a] = u.lo[a] - (1e-4f * mag + 1e-6f); out.emisHi[a] = u.hi[a] + (1e-4f * mag + 1e-6f);
         }
     }
-    bvh8_build(boxes, inst, prim, shade, uvs, out.all);
+    if (std::getenv("B200PT_BUILD_TIMING"))
+        fprintf(stderr, "[bvh8] records of %zu triangles: %.3f s\n", boxes.size(), std::chrono::duration<double>(std::chrono::steady_clock::now() - tPrep).count());
+    if (buildAll) bvh8_build(boxes, inst, prim, shade, uvs, out.all);
+    else out.leafOf = leafOf;      // `all` is built on the device from instObject / instTri / leafOf
     bvh8_build(boxesE, instE, primE, shadeE, uvsE, out.emis);
     if (out.all.maxDepth > PT_BVH8_MAX_DEPTH || out.emis.maxDepth > PT_BVH8_MAX_DEPTH) return "wide BVH deeper than the traversal stack";
     return nullptr;

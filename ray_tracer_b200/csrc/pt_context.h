@@ -61,6 +61,8 @@ struct b200pt_ctx {
     int triVote32 = 8;            // see WfParams
     int fetchMinIdle = 8;
     int sharePrimary = 1;         // trace the primary ray once per pixel and share the hit between frame slots (A-Q4)
+    int wideBuild = 1;            // 1: the wide BVH of all triangles is built on the device (wide_build.cu), 0: on the host
+    double lastSceneBuildMs = 0.0, lastWideDeviceMs = 0.0;   // wall time of the last re-layout; device part of it
 
     // counters (host side; device-side ray counters are folded in by the wavefront)
     uint64_t counters[16] = {0};

@@ -12,6 +12,7 @@
 #include "bvh8_build.h"
 #include "pt_wavefront.h"
 #include "wavefront.h"
+#include "wide_build.h"
 
 namespace pt {
 
@@ -426,14 +427,32 @@ int wavefront_build_scene(b200pt_ctx* c) {
     }
     WavefrontState* w = c->wf;
     WideSceneHost host;
-    if (const char* err = build_wide_scene(c->hSpheres, c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, host)) {
+    const auto tBuild = std::chrono::steady_clock::now();
+    const bool onDevice = c->wideBuild != 0;
+    if (const char* err = build_wide_scene(c->hSpheres, c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, host, !onDevice)) {
         c->error = std::string("scene re-layout: ") + err;
         return 1;
     }
-    WCU(wf_upload(c, w->dNodes, host.all.nodes));
-    WCU(wf_upload(c, w->dPrims, host.all.prims));
-    WCU(wf_upload(c, w->dShade, host.all.shade));
-    WCU(wf_upload(c, w->dUv, host.all.uvs));
+    uint32_t nNodesAll, nPrimsAll, depthAll;
+    c->lastWideDeviceMs = 0.0;
+    if (onDevice) {
+        WideDeviceInputs in{(const ptl::TrianglePoint*)c->dPoints.p, (const ptl::Triangle*)c->dTris.p, (const ptl::RenderObject*)c->dObjects.p,
+                            (const ptl::Material*)c->dMaterials.p};
+        WideDeviceResult res;
+        if (const char* err = wide_build_device(c->stream, in, host, res)) { c->error = err; return 2; }
+        wf_free(w->dNodes); wf_free(w->dPrims); wf_free(w->dShade); wf_free(w->dUv);
+        w->dNodes = {res.nodes, (size_t)res.nNodes * sizeof(Bvh8Node)}; w->dPrims = {res.prims, (size_t)res.nPrims * sizeof(PrimRecord)};
+        w->dShade = {res.shade, (size_t)res.nPrims * sizeof(ShadeRecord)}; w->dUv = {res.uv, (size_t)res.nPrims * sizeof(UvRecord)};
+        nNodesAll = res.nNodes; nPrimsAll = res.nPrims; depthAll = res.maxDepth;
+        c->lastWideDeviceMs = res.deviceMs;
+        if (depthAll > PT_BVH8_MAX_DEPTH) { c->error = "scene re-layout: wide BVH deeper than the traversal stack"; return 1; }
+    } else {
+        WCU(wf_upload(c, w->dNodes, host.all.nodes));
+        WCU(wf_upload(c, w->dPrims, host.all.prims));
+        WCU(wf_upload(c, w->dShade, host.all.shade));
+        WCU(wf_upload(c, w->dUv, host.all.uvs));
+        nNodesAll = (uint32_t)host.all.nodes.size(); nPrimsAll = (uint32_t)host.all.prims.size(); depthAll = host.all.maxDepth;
+    }
     WCU(wf_upload(c, w->dNodesE, host.emis.nodes));
     WCU(wf_upload(c, w->dPrimsE, host.emis.prims));
     WCU(wf_upload(c, w->dShadeE, host.emis.shade));
@@ -442,7 +461,7 @@ int wavefront_build_scene(b200pt_ctx* c) {
     WCU(wf_upload(c, w->dUp, host.up));
     WCU(cudaStreamSynchronize(c->stream));        // `host` is a local
     WideScene& s = w->scene;
-    s.all = {(const Bvh8Node*)w->dNodes.p, (const PrimRecord*)w->dPrims.p, (uint32_t)host.all.nodes.size(), (uint32_t)host.all.prims.size()};
+    s.all = {(const Bvh8Node*)w->dNodes.p, (const PrimRecord*)w->dPrims.p, nNodesAll, nPrimsAll};
     s.emis = {(const Bvh8Node*)w->dNodesE.p, (const PrimRecord*)w->dPrimsE.p, (uint32_t)host.emis.nodes.size(), (uint32_t)host.emis.prims.size()};
     s.shade = (const ShadeRecord*)w->dShade.p;
     s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
@@ -458,7 +477,8 @@ int wavefront_build_scene(b200pt_ctx* c) {
     s.emissionFinite = host.emissionFinite ? 1u : 0u;
     for (int a = 0; a < 3; ++a) {     s.emisLo[a] = host.emisLo[a];     s.emisHi[a] = host.emisHi[a]; }
     s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
-    w->maxDepth = host.all.maxDepth;
+    w->maxDepth = depthAll;
+    c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
     return 0;
 }
 

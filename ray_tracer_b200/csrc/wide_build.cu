@@ -1,0 +1,454 @@
+// Device build of the internal 8-wide BVH over every (object, triangle) instance (pt_bvh8.h) — the upload-time work
+// of b200pt_upload_scene / b200pt_update_objects, which the host builder (bvh8_build.h) does in 13.5 s for 10 M
+// triangles. Same algorithm as the host builder: world boxes -> binned-SAH binary tree (16 bins, leaves of <= 3
+// triangles) -> greedy collapse to 8 children -> octant-ordered slots -> 8-bit planes rounded outward. Traversal
+// results do not depend on the tree (every accepted hit is the reference's own triangle test, confirmed against
+// the reference's BVH2: pt_traverse.h), so there is no bit-exactness requirement against the host tree — only
+// that boxes are conservative; tests/test_gpu_parity.py runs every parity case through this build.
+//   k_wide_records   one thread per instance: PrimRecord / ShadeRecord / UvRecord / padded world box
+//   k_wide_split     one block per binary node and level: bounds, bins, SAH, stable partition, children
+//   k_wide_emit      one thread per wide node and level: collapse, slots, quantisation, record copies
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "bvh8_build.h"
+#include "wide_build.h"
+
+namespace pt {
+namespace wb {
+
+constexpr int NB = 16;
+
+struct Node2 {                               // binary SAH tree (as b8::Node2)
+    float lo[3], hi[3];
+    uint32_t left, right;                    // children (count == 0)
+    uint32_t first, count;                   // index range (leaf)
+};
+
+struct EmitItem { uint32_t n2, me, depth; };
+
+struct Dev {
+    // inputs
+    const ptl::TrianglePoint* points; const ptl::Triangle* tris; const ptl::RenderObject* objects; const ptl::Material* materials;
+    const UpNode* up; const uint32_t* leafOf; const uint32_t* objXform; const uint32_t* instObject; const uint32_t* instTri;
+    uint32_t nInst;
+    // per-instance records
+    PrimRecord* prim; ShadeRecord* shade; UvRecord* uv; WideBox* box;
+    // binary build
+    uint32_t* idx; uint32_t* idxTmp; Node2* nodes2;
+    uint32_t* counters;                      // [0] valid instances [1] binary nodes [2..4] next split lists [5] wide nodes [6] prims out
+                                             // [7] next emit list [8] max depth
+    uint32_t* nextList[3];
+    int maxLeaf; float travCost;
+    // output
+    Bvh8Node* outNodes; PrimRecord* outPrim; ShadeRecord* outShade; UvRecord* outUv;
+    EmitItem* emitNext;
+};
+
+__device__ __forceinline__ uint32_t f2o(float f) { uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__device__ __forceinline__ float o2f(uint32_t o) { return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o); }
+
+__global__ void k_wide_records(Dev d) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d.nInst) return;
+    const uint32_t o = d.instObject[i], t = d.instTri[i];
+    const ptl::RenderObject ob = d.objects[o];
+    const ptl::Triangle tr = d.tris[t];
+    const bool em = !(d.materials[ob.materialIndex].emissionStrength == 0.f);
+    PrimRecord r; ShadeRecord s; UvRecord u; WideBox b;
+    bool ok = wide_make_records(o, t, ob, tr, d.points[tr.v0], d.points[tr.v1], d.points[tr.v2], d.leafOf[t], d.up, d.objXform[o], em, r, s, u, b);
+    d.prim[i] = r; d.shade[i] = s; d.uv[i] = u; d.box[i] = b;
+    if (ok) d.idx[atomicAdd(&d.counters[0], 1u)] = i;          // order is irrelevant to the tree
+}
+
+struct SplitShared {
+    uint32_t lo[3], hi[3], cLo[3], cHi[3];
+    uint32_t binCount[3][NB];
+    uint32_t binLo[3][NB][3], binHi[3][NB][3];
+    uint32_t warpSum[32];
+    int axis, bin, leaf;
+    uint32_t kids;
+};
+
+__device__ __forceinline__ uint32_t block_exclusive(SplitShared& s, bool flag, uint32_t& total) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nWarps = blockDim.x >> 5;
+    const unsigned ballot = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) s.warpSum[warp] = (uint32_t)__popc(ballot);
+    __syncthreads();
+    uint32_t before = 0, all = 0;
+    for (unsigned w = 0; w < nWarps; ++w) { uint32_t c = s.warpSum[w]; all += c; if (w < warp) before += c; }
+    __syncthreads();
+    total = all;
+    return before + (uint32_t)__popc(ballot & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ float half_area(const float* lo, const float* hi) {
+    float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+    return x * y + y * z + z * x;
+}
+__device__ __forceinline__ int bin_of(float c, float lo, float scale) { return min(NB - 1, (int)((c - lo) * scale)); }
+
+// b8::Builder2::build for one node (bvh8_build.h), one block per node
+__global__ void __launch_bounds__(1024) k_wide_split(Dev d, const uint32_t* __restrict__ list, uint32_t nList) {
+    __shared__ SplitShared s;
+    const uint32_t tid = threadIdx.x, nT = blockDim.x;
+    for (uint32_t item = blockIdx.x; item < nList; item += gridDim.x) {
+        const uint32_t me = list[item];
+        const uint32_t first = d.nodes2[me].first, n = d.nodes2[me].count;
+        uint32_t* idx = d.idx + first;
+        if (tid < 3) { s.lo[tid] = s.cLo[tid] = 0xffffffffu; s.hi[tid] = s.cHi[tid] = 0u; }
+        for (uint32_t i = tid; i < 3 * NB; i += nT) {
+            (&s.binCount[0][0])[i] = 0u;
+            for (int c = 0; c < 3; ++c) { (&s.binLo[0][0][0])[i * 3 + c] = 0xffffffffu; (&s.binHi[0][0][0])[i * 3 + c] = 0u; }
+        }
+        __syncthreads();
+        {
+            uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u}, clo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, chi[3] = {0u, 0u, 0u};
+            for (uint32_t k = tid; k < n; k += nT) {
+                const WideBox b = d.box[idx[k]];
+                for (int a = 0; a < 3; ++a) {
+                    uint32_t oc = f2o(0.5f * (b.lo[a] + b.hi[a]));
+                    lo[a] = min(lo[a], f2o(b.lo[a])); hi[a] = max(hi[a], f2o(b.hi[a]));
+                    clo[a] = min(clo[a], oc); chi[a] = max(chi[a], oc);
+                }
+            }
+            for (int a = 0; a < 3; ++a) {
+                uint32_t l = __reduce_min_sync(0xffffffffu, lo[a]), h = __reduce_max_sync(0xffffffffu, hi[a]);
+                uint32_t cl = __reduce_min_sync(0xffffffffu, clo[a]), ch = __reduce_max_sync(0xffffffffu, chi[a]);
+                if ((tid & 31u) == 0) { atomicMin(&s.lo[a], l); atomicMax(&s.hi[a], h); atomicMin(&s.cLo[a], cl); atomicMax(&s.cHi[a], ch); }
+            }
+        }
+        __syncthreads();
+        float lo[3], hi[3], cLo[3], ext[3], scale[3];
+        for (int a = 0; a < 3; ++a) {
+            lo[a] = o2f(s.lo[a]); hi[a] = o2f(s.hi[a]); cLo[a] = o2f(s.cLo[a]); ext[a] = o2f(s.cHi[a]) - cLo[a];
+            scale[a] = (float)NB / ext[a];
+        }
+        if (tid < 3) { d.nodes2[me].lo[tid] = lo[tid]; d.nodes2[me].hi[tid] = hi[tid]; }
+        if (n == 1) { __syncthreads(); continue; }            // leaf of one triangle (first / count already set)
+        for (uint32_t k = tid; k < n; k += nT) {
+            const WideBox b = d.box[idx[k]];
+            for (int a = 0; a < 3; ++a) {
+                if (!(ext[a] > 0.f)) continue;
+                int bin = bin_of(0.5f * (b.lo[a] + b.hi[a]), cLo[a], scale[a]);
+                atomicAdd(&s.binCount[a][bin], 1u);
+                for (int c = 0; c < 3; ++c) { atomicMin(&s.binLo[a][bin][c], f2o(b.lo[c])); atomicMax(&s.binHi[a][bin][c], f2o(b.hi[c])); }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int bestAxis = -1, bestBin = -1;
+            float bestCost = 1e30f;
+            for (int a = 0; a < 3; ++a) {
+                if (!(ext[a] > 0.f)) continue;
+                float rightArea[NB]; uint32_t rightCnt[NB];
+                float alo[3] = {1e30f, 1e30f, 1e30f}, ahi[3] = {-1e30f, -1e30f, -1e30f};
+                uint32_t cnt = 0;
+                for (int k = NB - 1; k > 0; --k) {
+                    for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(s.binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(s.binHi[a][k][c])); }
+                    cnt += s.binCount[a][k];
+                    rightArea[k] = cnt ? half_area(alo, ahi) : 0.f; rightCnt[k] = cnt;
+                }
+                for (int c = 0; c < 3; ++c) { alo[c] = 1e30f; ahi[c] = -1e30f; }
+                cnt = 0;
+                for (int k = 0; k < NB - 1; ++k) {
+                    for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(s.binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(s.binHi[a][k][c])); }
+                    cnt += s.binCount[a][k];
+                    if (cnt == 0 || rightCnt[k + 1] == 0) continue;
+                    float cost = half_area(alo, ahi) * (float)cnt + rightArea[k + 1] * (float)rightCnt[k + 1];
+                    if (cost < bestCost) { bestCost = cost; bestAxis = a; bestBin = k; }
+                }
+            }
+            int leaf = 0;
+            if (n <= (uint32_t)d.maxLeaf) {                   // leaves hold at most 3 triangles (unary count of a node slot)
+                float area = half_area(lo, hi);
+                float leafCost = area * (float)n;
+                float splitCost = bestAxis < 0 ? 1e30f : area * d.travCost + bestCost;
+                if (!(splitCost < leafCost)) leaf = 1;
+            }
+            s.axis = bestAxis; s.bin = bestBin; s.leaf = leaf;
+            if (!leaf) s.kids = atomicAdd(&d.counters[1], 2u);
+        }
+        __syncthreads();
+        if (s.leaf) { __syncthreads(); continue; }
+        uint32_t mid = n / 2;
+        if (s.axis >= 0) {                                    // stable partition: bin <= bestBin first
+            const int a = s.axis, bb = s.bin;
+            uint32_t nLeft = 0;
+            for (uint32_t k = tid; k < n; k += nT) {
+                const WideBox b = d.box[idx[k]];
+                if (bin_of(0.5f * (b.lo[a] + b.hi[a]), cLo[a], scale[a]) <= bb) nLeft++;
+            }
+            nLeft = __reduce_add_sync(0xffffffffu, nLeft);
+            if (tid == 0) s.warpSum[0] = 0;
+            __syncthreads();
+            if ((tid & 31u) == 0 && nLeft) atomicAdd(&s.warpSum[0], nLeft);
+            __syncthreads();
+            const uint32_t totalLeft = s.warpSum[0];
+            __syncthreads();
+            if (totalLeft != 0 && totalLeft != n) {
+                uint32_t* tmp = d.idxTmp + first;
+                uint32_t runL = 0, runR = 0;
+                for (uint32_t base = 0; base < n; base += nT) {
+                    const uint32_t k = base + tid;
+                    uint32_t p = 0; bool isLeft = false;
+                    if (k < n) { p = idx[k]; const WideBox b = d.box[p]; isLeft = bin_of(0.5f * (b.lo[a] + b.hi[a]), cLo[a], scale[a]) <= bb; }
+                    uint32_t tot;
+                    uint32_t ex = block_exclusive(s, isLeft, tot);
+                    if (k < n) tmp[isLeft ? runL + ex : totalLeft + runR + (k - base - ex)] = p;
+                    runL += tot; runR += min(nT, n - base) - tot;
+                }
+                __syncthreads();
+                for (uint32_t k = tid; k < n; k += nT) idx[k] = tmp[k];
+                mid = totalLeft;
+            }
+        }
+        __syncthreads();                                      // idx of this range is final
+        if (tid < 2) {
+            Node2 c;
+            for (int a = 0; a < 3; ++a) { c.lo[a] = 0.f; c.hi[a] = 0.f; }
+            c.left = c.right = 0;
+            c.first = tid ? first + mid : first;
+            c.count = tid ? n - mid : mid;
+            const uint32_t kid = s.kids + tid;
+            if (c.count == 1) {                               // single triangle: its box is the node's box, nothing to split
+                const WideBox b = d.box[d.idx[c.first]];
+                for (int a = 0; a < 3; ++a) { c.lo[a] = b.lo[a]; c.hi[a] = b.hi[a]; }
+            }
+            d.nodes2[kid] = c;
+            if (c.count > 1) {
+                const int cls = c.count <= 64 ? 0 : (c.count <= 4096 ? 1 : 2);
+                d.nextList[cls][atomicAdd(&d.counters[2 + cls], 1u)] = kid;
+            }
+            if (tid == 0) { d.nodes2[me].left = s.kids; d.nodes2[me].right = s.kids + 1; d.nodes2[me].count = 0; }
+        }
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ uint8_t exponent_for(float extent) {     // smallest e with 2^e * 255 >= extent, biased
+    if (!(extent > 0.f)) return 0;
+    int e;
+    (void)frexpf(extent / 255.f, &e);
+    int b = e + 127;
+    return (uint8_t)max(1, min(254, b));
+}
+
+// bvh8_emit (bvh8_build.h) for one wide node: gather up to 8 children by opening the largest inner child, assign
+// octant-ordered slots, quantise, copy the leaf triangles' records, queue the inner children for the next level.
+__global__ void k_wide_emit(Dev d, const EmitItem* __restrict__ items, uint32_t nItems) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nItems) return;
+    const EmitItem it = items[i];
+    atomicMax(&d.counters[8], it.depth);
+    uint32_t ch[8]; Node2 cn[8]; int nch = 0;
+    const Node2 root = d.nodes2[it.n2];
+    if (root.count) { ch[0] = it.n2; cn[0] = root; nch = 1; }
+    else { ch[0] = root.left; ch[1] = root.right; cn[0] = d.nodes2[ch[0]]; cn[1] = d.nodes2[ch[1]]; nch = 2; }
+    while (nch < 8) {
+        int best = -1; float bestA = -1.f;
+        for (int k = 0; k < nch; ++k) {
+            if (cn[k].count) continue;
+            float a = half_area(cn[k].lo, cn[k].hi);
+            if (a > bestA) { bestA = a; best = k; }
+        }
+        if (best < 0) break;
+        const uint32_t l = cn[best].left, r = cn[best].right;
+        ch[best] = l; cn[best] = d.nodes2[l];
+        ch[nch] = r; cn[nch] = d.nodes2[r]; nch++;
+    }
+    // slots: greedy assignment minimising (child centre - node centre) . d_s (traversal priority is slot ^ (7 - octant))
+    float ncx[3];
+    for (int a = 0; a < 3; ++a) ncx[a] = 0.5f * (root.lo[a] + root.hi[a]);
+    float cost[8][8];
+    for (int c = 0; c < nch; ++c) {
+        float dd[3];
+        for (int a = 0; a < 3; ++a) dd[a] = 0.5f * (cn[c].lo[a] + cn[c].hi[a]) - ncx[a];
+        for (int sl = 0; sl < 8; ++sl)
+            cost[c][sl] = dd[0] * ((sl & 4) ? -1.f : 1.f) + dd[1] * ((sl & 2) ? -1.f : 1.f) + dd[2] * ((sl & 1) ? -1.f : 1.f);
+    }
+    int slotOf[8], childIn[8];
+    for (int k = 0; k < 8; ++k) { slotOf[k] = -1; childIn[k] = -1; }
+    for (int k = 0; k < nch; ++k) {
+        int bc = -1, bs = -1; float bv = 1e30f;
+        for (int c = 0; c < nch; ++c) if (slotOf[c] < 0)
+            for (int sl = 0; sl < 8; ++sl) if (childIn[sl] < 0 && cost[c][sl] < bv) { bv = cost[c][sl]; bc = c; bs = sl; }
+        if (bc < 0) {                                          // non-finite costs: first free pair
+            for (int c = 0; c < nch && bc < 0; ++c) if (slotOf[c] < 0) bc = c;
+            for (int sl = 0; sl < 8 && bs < 0; ++sl) if (childIn[sl] < 0) bs = sl;
+        }
+        slotOf[bc] = bs; childIn[bs] = bc;
+    }
+    Bvh8Node node;
+    memset(&node, 0, sizeof(node));
+    node.px = root.lo[0]; node.py = root.lo[1]; node.pz = root.lo[2];
+    uint8_t eb[3]; float sc[3];
+    for (int a = 0; a < 3; ++a) {
+        eb[a] = exponent_for(root.hi[a] - root.lo[a]);
+        for (;;) {                                             // the largest plane must be representable after rounding
+            sc[a] = __uint_as_float((uint32_t)eb[a] << 23);
+            if (eb[a] == 0 || eb[a] >= 254 || root.lo[a] + 255.f * sc[a] >= root.hi[a]) break;
+            eb[a]++;
+        }
+    }
+    node.ex = eb[0]; node.ey = eb[1]; node.ez = eb[2];
+    uint32_t nInner = 0, nLeafTris = 0;
+    for (int sl = 0; sl < 8; ++sl) if (childIn[sl] >= 0) { if (cn[childIn[sl]].count == 0) nInner++; else nLeafTris += cn[childIn[sl]].count; }
+    node.childBase = nInner ? atomicAdd(&d.counters[5], nInner) : 0u;
+    node.primBase = nLeafTris ? atomicAdd(&d.counters[6], nLeafTris) : 0u;
+    const uint32_t emitBase = nInner ? atomicAdd(&d.counters[7], nInner) : 0u;
+    uint32_t innerSeen = 0, primOff = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        const int c = childIn[sl];
+        if (c < 0) continue;
+        const Node2& k = cn[c];
+        uint8_t* qlo[3] = {node.qlox, node.qloy, node.qloz};
+        uint8_t* qhi[3] = {node.qhix, node.qhiy, node.qhiz};
+        const float p[3] = {node.px, node.py, node.pz};
+        for (int a = 0; a < 3; ++a) {
+            int l = 0, h = 0;
+            if (sc[a] > 0.f) {
+                l = (int)floorf((k.lo[a] - p[a]) / sc[a]);
+                h = (int)ceilf((k.hi[a] - p[a]) / sc[a]);
+                l = max(0, min(255, l)); h = max(0, min(255, h));
+                while (l > 0 && p[a] + (float)l * sc[a] > k.lo[a]) l--;        // outward after rounding
+                while (h < 255 && p[a] + (float)h * sc[a] < k.hi[a]) h++;
+            }
+            qlo[a][sl] = (uint8_t)l; qhi[a][sl] = (uint8_t)h;
+        }
+        if (k.count == 0) {
+            node.imask |= (uint8_t)(1u << sl);
+            node.meta[sl] = (uint8_t)((1u << 5) | (24u + sl));
+            EmitItem nx; nx.n2 = ch[c]; nx.me = node.childBase + innerSeen; nx.depth = it.depth + 1;
+            d.emitNext[emitBase + innerSeen] = nx;
+            innerSeen++;
+        } else {
+            const uint32_t unary = k.count == 1 ? 1u : (k.count == 2 ? 3u : 7u);
+            node.meta[sl] = (uint8_t)((unary << 5) | primOff);
+            for (uint32_t q = 0; q < k.count; ++q) {
+                const uint32_t id = d.idx[k.first + q], dst = node.primBase + primOff + q;
+                d.outPrim[dst] = d.prim[id]; d.outShade[dst] = d.shade[id]; d.outUv[dst] = d.uv[id];
+            }
+            primOff += k.count;
+        }
+    }
+    d.outNodes[it.me] = node;
+}
+
+}  // namespace wb
+
+namespace {
+struct Scratch {                             // everything except the four result buffers
+    std::vector<void*> ptrs;
+    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
+    template <class T> cudaError_t get(T** p, size_t count) {
+        cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) ptrs.push_back(*p);
+        return e;
+    }
+    void release(void* p) { ptrs.erase(std::remove(ptrs.begin(), ptrs.end(), p), ptrs.end()); }
+};
+thread_local char g_msg[256];
+}  // namespace
+
+#define WBC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(g_msg, sizeof g_msg, "wide BVH device build: %s: %s", #x, cudaGetErrorString(e_)); return g_msg; } } while (0)
+
+const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out) {
+    using namespace wb;
+    const size_t n = host.instTri.size();
+    Scratch mem;
+    Dev d{};
+    d.points = in.points; d.tris = in.tris; d.objects = in.objects; d.materials = in.materials;
+    d.nInst = (uint32_t)n;
+    d.maxLeaf = 3; d.travCost = 1.0f;
+    if (const char* e = std::getenv("B200PT_BVH_LEAF")) d.maxLeaf = std::max(1, std::min(3, std::atoi(e)));
+    if (const char* e = std::getenv("B200PT_BVH_CT")) d.travCost = (float)std::atof(e);
+    UpNode* up; uint32_t *leafOf, *objXform, *instObject, *instTri, *lists[6];
+    EmitItem* emit[2];
+    WBC(mem.get(&up, host.up.size())); WBC(mem.get(&leafOf, host.leafOf.size())); WBC(mem.get(&objXform, host.objXform.size()));
+    WBC(mem.get(&instObject, n)); WBC(mem.get(&instTri, n));
+    WBC(mem.get(&d.prim, n)); WBC(mem.get(&d.shade, n)); WBC(mem.get(&d.uv, n)); WBC(mem.get(&d.box, n));
+    WBC(mem.get(&d.idx, n)); WBC(mem.get(&d.idxTmp, n)); WBC(mem.get(&d.nodes2, 2 * n + 1)); WBC(mem.get(&d.counters, 16));
+    for (auto& p : lists) WBC(mem.get(&p, n / 2 + 1));        // a listed node holds at least 2 triangles
+    WBC(mem.get(&emit[0], n + 1)); WBC(mem.get(&emit[1], n + 1));
+    WBC(mem.get(&d.outNodes, n + 1)); WBC(mem.get(&d.outPrim, n)); WBC(mem.get(&d.outShade, n)); WBC(mem.get(&d.outUv, n));
+    auto h2d = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess; };
+    WBC(h2d(up, host.up.data(), host.up.size() * sizeof(UpNode)));
+    WBC(h2d(leafOf, host.leafOf.data(), host.leafOf.size() * 4));
+    WBC(h2d(objXform, host.objXform.data(), host.objXform.size() * 4));
+    WBC(h2d(instObject, host.instObject.data(), n * 4));
+    WBC(h2d(instTri, host.instTri.data(), n * 4));
+    d.up = up; d.leafOf = leafOf; d.objXform = objXform; d.instObject = instObject; d.instTri = instTri;
+    cudaEvent_t e0, e1;
+    WBC(cudaEventCreate(&e0)); WBC(cudaEventCreate(&e1));
+    WBC(cudaMemsetAsync(d.counters, 0, 64, st));
+    WBC(cudaEventRecord(e0, st));
+    uint32_t h[16] = {0};
+    if (n) k_wide_records<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d);
+    WBC(cudaMemcpyAsync(h, d.counters, 64, cudaMemcpyDeviceToHost, st));
+    WBC(cudaStreamSynchronize(st));
+    const uint32_t nValid = h[0];
+    if (nValid == 0) {                        // no triangles: one empty node, as the host builder
+        Bvh8Node zero; memset(&zero, 0, sizeof zero);
+        WBC(cudaMemcpyAsync(d.outNodes, &zero, sizeof zero, cudaMemcpyHostToDevice, st));
+        out.nNodes = 1; out.nPrims = 0; out.maxDepth = 0;
+    } else {
+        Node2 root{};
+        root.first = 0; root.count = nValid;
+        WBC(cudaMemcpyAsync(d.nodes2, &root, sizeof root, cudaMemcpyHostToDevice, st));
+        uint32_t init[16] = {nValid, 1, 0, 0, 0, 1, 0, 0, 0};
+        const int cls0 = nValid <= 64 ? 0 : (nValid <= 4096 ? 1 : 2);
+        init[2 + cls0] = 1;
+        uint32_t zeroId = 0;
+        WBC(cudaMemcpyAsync(lists[cls0], &zeroId, 4, cudaMemcpyHostToDevice, st));
+        WBC(cudaMemcpyAsync(d.counters, init, 64, cudaMemcpyHostToDevice, st));
+        const unsigned threadsOf[3] = {32, 256, 1024};
+        int cur = 0;
+        for (int level = 0;; ++level) {
+            WBC(cudaMemcpyAsync(h, d.counters, 64, cudaMemcpyDeviceToHost, st));
+            WBC(cudaStreamSynchronize(st));
+            if (h[2] + h[3] + h[4] == 0) break;
+            if (level > 4096) return "wide BVH device build: binary tree does not terminate";
+            const uint32_t* curList[3] = {lists[cur * 3], lists[cur * 3 + 1], lists[cur * 3 + 2]};
+            cur ^= 1;
+            for (int c = 0; c < 3; ++c) d.nextList[c] = lists[cur * 3 + c];
+            WBC(cudaMemsetAsync(d.counters + 2, 0, 12, st));
+            for (int c = 0; c < 3; ++c)
+                if (h[2 + c]) k_wide_split<<<std::min<uint32_t>(h[2 + c], 1u << 20), threadsOf[c], 0, st>>>(d, curList[c], h[2 + c]);
+            WBC(cudaGetLastError());
+        }
+        // collapse + emit, level by level from the root (wide node 0 <- binary node 0)
+        EmitItem first{0u, 0u, 1u};
+        WBC(cudaMemcpyAsync(emit[0], &first, sizeof first, cudaMemcpyHostToDevice, st));
+        uint32_t nItems = 1;
+        int ecur = 0;
+        while (nItems) {
+            d.emitNext = emit[ecur ^ 1];
+            WBC(cudaMemsetAsync(d.counters + 7, 0, 4, st));
+            k_wide_emit<<<(nItems + 63) / 64, 64, 0, st>>>(d, emit[ecur], nItems);
+            WBC(cudaGetLastError());
+            WBC(cudaMemcpyAsync(h, d.counters, 64, cudaMemcpyDeviceToHost, st));
+            WBC(cudaStreamSynchronize(st));
+            nItems = h[7];
+            ecur ^= 1;
+        }
+        out.nNodes = h[5]; out.nPrims = h[6]; out.maxDepth = h[8];
+        if (out.nPrims != nValid) return "wide BVH device build: triangle count mismatch";
+    }
+    WBC(cudaEventRecord(e1, st));
+    WBC(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    out.deviceMs = ms;
+    out.nodes = d.outNodes; out.prims = d.outPrim; out.shade = d.outShade; out.uv = d.outUv;
+    mem.release(d.outNodes); mem.release(d.outPrim); mem.release(d.outShade); mem.release(d.outUv);
+    return nullptr;
+}
+
+}  // namespace pt

@@ -1,0 +1,23 @@
+// Device build of the wide BVH of all instance triangles (wide_build.cu); the host keeps the small parts
+// (bvh8_build.h: transforms, parent links of the reference BVH2, the instance list, the emissive-only BVH).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "bvh8_build.h"
+
+namespace pt {
+
+struct WideDeviceInputs {                    // reference-layout buffers already on the device (b200pt_upload_scene)
+    const ptl::TrianglePoint* points; const ptl::Triangle* tris; const ptl::RenderObject* objects; const ptl::Material* materials;
+};
+struct WideDeviceResult {                    // cudaMalloc'ed, owned by the caller after success
+    void* nodes = nullptr; void* prims = nullptr; void* shade = nullptr; void* uv = nullptr;
+    uint32_t nNodes = 0, nPrims = 0, maxDepth = 0;
+    double deviceMs = 0.0;
+};
+// host: result of build_wide_scene(..., buildAll = false) (instObject / instTri / leafOf / up / objXform filled).
+// Returns nullptr or an error text.
+const char* wide_build_device(cudaStream_t stream, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out);
+
+}  // namespace pt
