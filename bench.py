@@ -249,6 +249,8 @@ def main():
     cp.copy_buffers(blobs)
     cp.sync()
     upload_s = time.perf_counter() - t_up
+    wide_build = dict(where="device" if cp.get_option("wide_build") else "host", relayout_ms=cp.get_option("last_scene_build_us") / 1e3,
+                      device_ms=cp.get_option("last_wide_device_us") / 1e3)
 
     # rank-local step buffer (attached as the context's accumulator) and, on rank 0, the running total
     stepbuf = torch.zeros(H, W, 4, dtype=torch.float32, device=dev)
@@ -402,7 +404,7 @@ def main():
         cfg.update(parallelism="spp-split x%d (frames f = r mod N) + NCCL reduce per step" % N if N > 1 else "single GPU",
                    l2="path state per step %.0f MB >> 126 MB L2; scene (%.0f MB) is re-read by every frame by design; no flush"
                       % (W * H * F * 160 / 1e6, cfg["scene_reference_layout_mb"]),
-                   frames_rendered=frames_done, mean_radiance=mean_rgb, scene_upload_s=round(upload_s, 3),
+                   frames_rendered=frames_done, mean_radiance=mean_rgb, scene_upload_s=round(upload_s, 3), wide_bvh_build=wide_build,
                    rays_per_path=(counters["extension_rays"] + counters["shadow_rays"]) / max(counters["paths"], 1))
         out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=N, steps=args.steps, warmup=args.warmup,
                    ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32",
