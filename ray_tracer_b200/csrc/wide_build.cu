@@ -40,9 +40,9 @@ struct Dev {
     // per-instance records
     PrimRecord* prim; ShadeRecord* shade; UvRecord* uv; WideBox* box;
     // binary build
-    uint32_t* idx; uint32_t* idxTmp; Node2* nodes2;
+    uint32_t* idx; uint32_t* idxTmp; Node2* nodes2; uint8_t* valid;
     uint32_t* counters;                      // [0] valid instances [1] binary nodes [2..4] next split lists [5] wide nodes [6] prims out
-                                             // [7] next emit list [8] max depth
+                                             // [7] next emit list [8] max depth [9] instances dropped (non-finite vertices)
     uint32_t* nextList[3];
     int maxLeaf; float travCost;
     // output
@@ -63,7 +63,9 @@ __global__ void k_wide_records(Dev d) {
     PrimRecord r; ShadeRecord s; UvRecord u; WideBox b;
     bool ok = wide_make_records(o, t, ob, tr, d.points[tr.v0], d.points[tr.v1], d.points[tr.v2], d.leafOf[t], d.up, d.objXform[o], em, r, s, u, b);
     d.prim[i] = r; d.shade[i] = s; d.uv[i] = u; d.box[i] = b;
-    if (ok) d.idx[atomicAdd(&d.counters[0], 1u)] = i;          // order is irrelevant to the tree
+    d.idx[i] = i;                                               // instance order: the same tree on every build
+    d.valid[i] = ok ? 1 : 0;
+    if (!ok) atomicAdd(&d.counters[9], 1u);
 }
 
 struct SplitShared {
@@ -373,7 +375,7 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     WBC(mem.get(&up, host.up.size())); WBC(mem.get(&leafOf, host.leafOf.size())); WBC(mem.get(&objXform, host.objXform.size()));
     WBC(mem.get(&instObject, n)); WBC(mem.get(&instTri, n));
     WBC(mem.get(&d.prim, n)); WBC(mem.get(&d.shade, n)); WBC(mem.get(&d.uv, n)); WBC(mem.get(&d.box, n));
-    WBC(mem.get(&d.idx, n)); WBC(mem.get(&d.idxTmp, n)); WBC(mem.get(&d.nodes2, 2 * n + 1)); WBC(mem.get(&d.counters, 16));
+    WBC(mem.get(&d.idx, n)); WBC(mem.get(&d.idxTmp, n)); WBC(mem.get(&d.valid, n)); WBC(mem.get(&d.nodes2, 2 * n + 1)); WBC(mem.get(&d.counters, 16));
     for (auto& p : lists) WBC(mem.get(&p, n / 2 + 1));        // a listed node holds at least 2 triangles
     WBC(mem.get(&emit[0], n + 1)); WBC(mem.get(&emit[1], n + 1));
     WBC(mem.get(&d.outNodes, n + 1)); WBC(mem.get(&d.outPrim, n)); WBC(mem.get(&d.outShade, n)); WBC(mem.get(&d.outUv, n));
@@ -392,7 +394,18 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     if (n) k_wide_records<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(d);
     WBC(cudaMemcpyAsync(h, d.counters, 64, cudaMemcpyDeviceToHost, st));
     WBC(cudaStreamSynchronize(st));
-    const uint32_t nValid = h[0];
+    uint32_t nValid = (uint32_t)n;
+    if (h[9]) {                               // rare: drop the instances with non-finite vertices, keeping the order
+        std::vector<uint8_t> valid(n);
+        WBC(cudaMemcpyAsync(valid.data(), d.valid, n, cudaMemcpyDeviceToHost, st));
+        WBC(cudaStreamSynchronize(st));
+        std::vector<uint32_t> keep;
+        keep.reserve(n);
+        for (size_t i = 0; i < n; ++i) if (valid[i]) keep.push_back((uint32_t)i);
+        nValid = (uint32_t)keep.size();
+        WBC(h2d(d.idx, keep.data(), keep.size() * 4));
+        WBC(cudaStreamSynchronize(st));
+    }
     if (nValid == 0) {                        // no triangles: one empty node, as the host builder
         Bvh8Node zero; memset(&zero, 0, sizeof zero);
         WBC(cudaMemcpyAsync(d.outNodes, &zero, sizeof zero, cudaMemcpyHostToDevice, st));

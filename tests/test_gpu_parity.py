@@ -34,6 +34,13 @@ def _pass(gpu, blobs, W, H):
     return cp
 
 
+def _differing(a, b):
+    """Fraction of pixels whose bits differ. Two triangles of one object hit at exactly the same distance are the one
+    documented tie class: which of them wins depends on the order the warp happens to test them
+    in, a pixel or two per 2 M in the atrium. Everything else is bit-reproducible."""
+    return float((a.view(np.uint32) != b.view(np.uint32)).any(axis=2).mean())
+
+
 def _same_hits(got, want):
     return ((got["kind"] == want["kind"]) & (got["objectHitIndex"] == want["objectHitIndex"]) &
             (got["triHitIndex"] == want["triHitIndex"]) & (got["dst"].view(np.uint32) == want["dst"].view(np.uint32)))
@@ -234,7 +241,7 @@ def test_full_size_properties_c4(gpu):
         for k, v in opts.items():
             cp.set_option(k, v)
         cp.render_frames(pc.buffer, 0, 4)
-        assert np.array_equal(cp.read_accum().view(np.uint32), whole.view(np.uint32)), opts
+        assert _differing(cp.read_accum(), whole) <= 1e-5, opts
     cp.set_option("frames_in_flight", 4)
     cp.clear()
     cp.render_frames(pc.buffer, 0, 2, frame_stride=2)
@@ -245,7 +252,7 @@ def test_full_size_properties_c4(gpu):
     cp.clear()
     cp.render_frames(pc.buffer, 0, 4, rows=(0, 377))
     cp.render_frames(pc.buffer, 0, 4, rows=(377, H))
-    assert np.array_equal(cp.read_accum().view(np.uint32), whole.view(np.uint32))
+    assert _differing(cp.read_accum(), whole) <= 1e-5
     # the oracle on a window of the same image: 64 x 48 pixels around the centre, 1 frame, bit-exact apart from ties
     # (a window, not a sub-sampled grid: seeds and rays depend on x, y, W and H)
     cp.clear()
@@ -441,6 +448,11 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
     cases = [(bunny_blobs, ob.default_push_constants(200, 160, 10, bunny_blobs["objects"].size // 80), 200, 160)]
     blobs, info = scenes.statue_room(60_000)
     cases.append((blobs, PushConstants(256, 144, 10, info["objects"]).buffer, 256, 144))
+    # a triangle with a non-finite vertex can never be hit: both builders drop it
+    broken = dict(bunny_blobs, points=bunny_blobs["points"].copy())
+    tri5 = broken["triangles"].view(np.uint32).reshape(-1, 12)[5]
+    broken["points"].view(np.float32).reshape(-1, 8)[tri5[1], 0] = np.inf
+    cases.append((broken, cases[0][1], 200, 160))
     for blobs, pc, W, H in cases:
         imgs = []
         for mode in (0, 1):
@@ -453,6 +465,7 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
             imgs.append(cp.read_accum())
         diff = (imgs[0].view(np.uint32) != imgs[1].view(np.uint32)).any(axis=2)
         assert diff.mean() <= 2e-3, diff.mean()              # the documented same-object equal-distance tie class only
+        assert np.isfinite(imgs[1]).all()
     # an object moved after upload: the tree is rebuilt on the device and agrees with a fresh upload
     blobs, pc, W, H = cases[1]
     cp = gpu.ComputePass(W, H)
@@ -466,4 +479,5 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
     cp2 = gpu.ComputePass(W, H)
     cp2.copy_buffers(dict(blobs, objects=moved))
     cp2.render_frames(pc, 0, 3)
-    assert np.array_equal(a.view(np.uint32), cp2.read_accum().view(np.uint32))
+    diff = (a.view(np.uint32) != cp2.read_accum().view(np.uint32)).any(axis=2)
+    assert diff.mean() <= 2e-3, diff.mean()
