@@ -343,6 +343,28 @@ def main():
     ms_inter = float(ms_inter.item()) / n_inter
     cp.attach_accum(stepbuf.data_ptr())
 
+    # the engine's own per-frame call: b200pt_render = one literal dispatch (progressive blend into the storage image).
+    # 1-sample dispatches are served by the wavefront kernels; pipeline 0 is the per-pixel reference-order kernel.
+    def dispatches(k, first):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fence()
+        e0.record(stream)
+        for f in range(k):
+            pc["frameCount"] = first + f
+            cp.run_compute(pc.buffer)
+        e1.record(stream)
+        fence()
+        return e0.elapsed_time(e1) / k
+    keep_progressive = int(pc["progressive"])
+    pc["progressive"] = 1
+    dispatches(2, 0)
+    ms_dispatch = dispatches(n_inter, 2)
+    cp.set_option("pipeline", 0)
+    ms_dispatch_ref = dispatches(2, 2 + n_inter)
+    cp.set_option("pipeline", args.pipeline)
+    pc["progressive"] = keep_progressive
+    pc["frameCount"] = 0
+
     paths_per_step = W * H * F * N
     value = paths_per_step * args.steps / (ms * 1e-3) / 1e6
     e2e_value = paths_per_step * args.steps / (ms_e2e * 1e-3) / 1e6
@@ -413,7 +435,7 @@ def main():
                             ms_per_step=ms_e2e / args.steps),
                    gpu_launches=counters["launches"], roofline=roofline, cpu_baseline=cpu,
                    ms_per_frame_1spp=ms / args.steps / F,
-                   interactive=dict(ms_per_frame=ms_inter, frames=n_inter, split="row bands over %d GPU(s), gathered on rank 0" % N,
+                   interactive=dict(ms_per_frame=ms_inter, frames=n_inter, run_compute_ms=ms_dispatch, run_compute_pipeline0_ms=ms_dispatch_ref, split="row bands over %d GPU(s), gathered on rank 0" % N,
                                     note="one 1-spp progressive frame at a time (latency), vs ms_per_frame_1spp = throughput mode / frames"))
         print(json.dumps(out), flush=True)
     cp.attach_accum(0)

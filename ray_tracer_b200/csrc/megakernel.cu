@@ -18,17 +18,7 @@ __global__ void __launch_bounds__(64) k_ref_dispatch(RefScene sc, const __grid_c
     RefPixel px = ref_pixel(sc, c_pc, cp, gx, gy, W, H);
     float4 old = image[p];
     v3 fin = ref_resolve(c_pc, px, mk3(old.x, old.y, old.z));
-    if (storeUnorm8) {
-        // option "storage_rgba8": the reference's storage image is rgba8 (raytrace.comp:120,593) — what the next dispatch
-        // reads back is the 8-bit value. Vulkan unorm conversion: clamp, scale, round to nearest even; no transfer
-        // function (A-Q3: whether MoltenVK applies sRGB on a storage image is driver-defined — parity unpinned).
-        auto q = [](float f) -> float {
-            if (!(f > 0.f)) return 0.f;
-            if (f >= 1.f) return 1.f;
-            return float(__float2int_rn(f * 255.f)) / 255.f;
-        };
-        fin = mk3(q(fin.x), q(fin.y), q(fin.z));
-    }
+    if (storeUnorm8) fin = mk3(unorm8_round(fin.x), unorm8_round(fin.y), unorm8_round(fin.z));
     image[p] = make_float4(fin.x, fin.y, fin.z, 1.f);
     stats[p] = make_float2(px.stats0, px.stats1);
 }

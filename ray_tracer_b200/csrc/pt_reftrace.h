@@ -182,6 +182,19 @@ PT_HD RefPixel ref_pixel(const RefScene& sc, const ptl::PushConstants& pc, const
     return r;
 }
 
+// option "storage_rgba8": the reference's storage image is rgba8 (raytrace.comp:120,593) — what the next dispatch reads
+// back is the 8-bit value. Vulkan unorm conversion: clamp, scale, round to nearest even; no transfer function (A-Q3:
+// whether MoltenVK applies sRGB on a storage image is driver-defined — parity unpinned).
+PT_HD float unorm8_round(float f) {
+    if (!(f > 0.f)) return 0.f;
+    if (f >= 1.f) return 1.f;
+#if defined(__CUDA_ARCH__)
+    return float(__float2int_rn(f * 255.f)) / 255.f;
+#else
+    return float((int)nearbyintf(f * 255.f)) / 255.f;
+#endif
+}
+
 // main() after the sample loop, raytrace.comp:576-591: progressive blend, NaN/Inf -> magenta,
 // debug heat-maps. `old` is the stored colour of this pixel.
 PT_HD v3 ref_resolve(const ptl::PushConstants& pc, const RefPixel& px, v3 old) {

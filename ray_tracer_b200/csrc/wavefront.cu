@@ -11,6 +11,7 @@
 
 #include "bvh8_build.h"
 #include "pt_wavefront.h"
+#include "pt_reftrace.h"
 #include "wavefront.h"
 #include "wide_build.h"
 
@@ -347,6 +348,22 @@ __global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant
         stage_accumulate(P, A, accum, pix);
 }
 
+// One literal dispatch served by the wavefront: main() after trace() (raytrace.comp:568-593) for 1-sample dispatches.
+// outColor of the single frame slot goes through the same ref_resolve as the per-pixel kernel (progressive blend with
+// the stored image, NaN/Inf -> magenta) and, with option storage_rgba8, the same unorm8 rounding.
+__global__ void __launch_bounds__(WF_THREADS) k_dispatch_resolve(const __grid_constant__ WfParams P, PathArrays A, float4* image, int storeUnorm8) {
+    uint32_t n = P.rows * (uint32_t)P.W;
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < n; pix += gridDim.x * blockDim.x) {
+        RefPixel px;
+        px.outColor = xyz(A.total[pix]);
+        px.stats0 = 0.f; px.stats1 = 0.f;
+        float4 old = image[pix];
+        v3 fin = ref_resolve(P.pc, px, mk3(old.x, old.y, old.z));
+        if (storeUnorm8) fin = mk3(unorm8_round(fin.x), unorm8_round(fin.y), unorm8_round(fin.z));
+        image[pix] = make_float4(fin.x, fin.y, fin.z, 1.f);
+    }
+}
+
 // ray counters: [0] += extension rays (sum of qCount), [1] += NEE/pdf queries (2 per connect item)
 __global__ void k_fold(const uint32_t* qCount, const uint32_t* sCount, uint32_t nBounce, unsigned long long* rayCounters) {
     if (blockIdx.x || threadIdx.x) return;
@@ -530,7 +547,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
 }
 
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
-                            uint32_t row0, uint32_t row1) {
+                            uint32_t row0, uint32_t row1, float4* dispatchImage) {
     WavefrontState* w = c->wf;
     if (!w) { c->error = "wavefront: no scene"; return 3; }
     if (n == 0 || row1 <= row0) return 0;
@@ -623,7 +640,8 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         }
         c->counters[0] += 1;
         wf_mark(c, ST_ACCUMULATE);
-        k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
+        if (dispatchImage) k_dispatch_resolve<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, dispatchImage, c->storageRgba8);
+        else k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
         k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
         wf_mark(c, -1);
         c->counters[0] += 3;

@@ -481,3 +481,34 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
     cp2.render_frames(pc, 0, 3)
     diff = (a.view(np.uint32) != cp2.read_accum().view(np.uint32)).any(axis=2)
     assert diff.mean() <= 2e-3, diff.mean()
+
+
+def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, bunny_blobs):
+    # b200pt_render with raysPerPixel = 1 (the engine's per-frame call, src/vk_engine.cpp:1663-1665) is served by the
+    # wavefront kernels; the image must equal the literal per-pixel dispatch (pipeline 0) and the oracle's main()
+    W, H = 160, 120
+    for blobs in (cornell_blobs, bunny_blobs):
+        sc = ob.OracleScene(blobs)
+        pc = ob.default_push_constants(W, H, 10, blobs["objects"].size // 80)
+        pc[160] = 1                            # progressive
+        fast, slow = _pass(gpu, blobs, W, H), _pass(gpu, blobs, W, H)
+        slow.set_option("pipeline", 0)
+        image = np.zeros((H, W, 4), np.float32)
+        with ob.math_mode(1):
+            for f in range(4):
+                pc.view(np.uint32)[50] = f
+                sc.render_dispatch(pc, W, H, image=image)
+                fast.run_compute(pc)
+                slow.run_compute(pc)
+        a, b = fast.read_image(), slow.read_image()
+        assert _differing(a, b) <= 2e-3 and _differing(a, image) <= 2e-3
+        assert fast.counters()["paths"] == 4 * W * H and fast.counters()["extension_rays"] > 4 * W * H
+        assert np.array_equal(fast.read_rgba8(), np.clip(np.rint(np.clip(a, 0, 1) * 255), 0, 255).astype(np.uint8))
+        # not progressive: the image is replaced; storage at 8-bit precision
+        pc[160] = 0
+        for cp in (fast, slow):
+            cp.set_option("storage_rgba8", 1)
+            cp.run_compute(pc)
+        a, b = fast.read_image(), slow.read_image()
+        assert _differing(a, b) <= 2e-3
+        assert np.array_equal(a[..., :3], np.rint(a[..., :3] * 255) / np.float32(255))
