@@ -83,10 +83,10 @@ int b200pt_upload_texture(b200pt_ctx* ctx, uint32_t slot, const void* rgba8, uin
 /* One reference dispatch: main() of raytrace.comp for every pixel with the 208-byte push-constant
  * block; read-modify-writes the float storage image (the reference's image is rgba8; see
  * b200pt_read_rgba8). Honours progressive, singleRender, raysPerPixel, sampleLimit, bounceLimit,
- * debug, frameCount. With one sample per dispatch and no debug heat-map (the engine's interactive default) the
- * frame is traced by the wavefront kernels and finished by the same main() tail; several samples per dispatch
- * (which share one RNG stream), the debug modes and option "pipeline" = 0 use the one-thread-per-pixel kernel in the
- * reference's traversal order, which is also the only one that fills b200pt_read_stats. */
+ * debug, frameCount. Without a debug heat-map the frame is traced by the wavefront kernels (several samples per
+ * dispatch as consecutive passes that hand the pixel's RNG state over) and finished by the same main() tail; the
+ * debug modes and option "pipeline" = 0 use the one-thread-per-pixel kernel in the reference's traversal order,
+ * which is also the only one that fills b200pt_read_stats. */
 int b200pt_render(b200pt_ctx* ctx, const void* push_constants_208);
 
 /* Throughput entry: progressive frames first_frame .. first_frame+n_frames-1 (frameCount = f,

@@ -316,11 +316,11 @@ int b200pt_render(b200pt_ctx* c, const void* pc208) {
     if (int rc = check_render(c, pc208, pc)) return rc;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaEventRecord(c->evStart, c->stream));
-    // 1-sample dispatches without a debug heat-map go through the wavefront kernels (same image; the box/triangle test
+    // dispatches without a debug heat-map go through the wavefront kernels (same image; the box/triangle test
     // counters of b200pt_read_stats exist only on the reference-order kernel: pipeline 0 or a debug mode)
     const uint64_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
     const bool heatmap = pc.params.debug >= 0 && pc.params.debug <= 2;
-    if (c->pipeline == 1 && samples == 1 && !heatmap) {
+    if (c->pipeline == 1 && samples >= 1 && !heatmap) {
         CU(c, cudaMemsetAsync(c->dStats.p, 0, (size_t)c->W * c->H * 8, c->stream));
         if (int rc = wavefront_render_frames(c, pc, pc.frameCount, 1, 1, 0, (uint32_t)c->H, (float4*)c->dImage.p)) return rc;
     } else {

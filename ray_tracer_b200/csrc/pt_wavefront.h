@@ -49,6 +49,7 @@ struct WfParams {
     uint32_t sharePrimary;          // bounce 0: the hit of path p is stored at p % (rows * W) (one primary ray per pixel)
     uint32_t connectAfterExtend;    // connect of bounce j runs after extend of bounce j+1 (A.hit is the NEXT hit)
     uint32_t useTextures;           // texture extension on (option "textures"); 0 = the HEAD shader's behaviour
+    uint32_t continueSample;        // sample s > 0 of a multi-sample dispatch: generate continues the RNG stream in rayD[p].w
 };
 
 PT_HD v3 xyz(const float4& f) { return mk3(f.x, f.y, f.z); }
@@ -61,7 +62,9 @@ PT_HD void stage_generate(const WfParams& P, const PathArrays& A, uint32_t p) {
     uint32_t gy = P.row0 + rem / (uint32_t)P.W, gx = rem % (uint32_t)P.W;
     uint32_t frame = P.firstFrame + k * P.stride;
     Ray r = primary_ray(P.pc.cam, P.cp, gx, gy, P.W, P.H);
-    uint32_t state = gy * (uint32_t)P.W + gx + frame_seed(frame);
+    // samples of one dispatch share the pixel's RNG stream (raytrace.comp:562-570): sample s > 0 continues from the state
+    // the path of sample s-1 ended with, which every exit of stage_shade leaves in rayD[p].w
+    uint32_t state = P.continueSample ? as_uint(A.rayD[p].w) : gy * (uint32_t)P.W + gx + frame_seed(frame);
     A.rayO[p] = f4(r.o, 1.f);                       // misWeight = 1
     A.rayD[p] = f4(r.d, as_float(state));
     A.atten[p] = make_float4(1.f, 1.f, 1.f, 0.f);
@@ -256,8 +259,11 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
     float rr = gmax(gmax(atten.x, atten.y), atten.z);            // :519-524
     rr = gmin(rr, 0.95f);
     rr = j <= 5 ? 1.f : rr;
-    if (rng_next(state) > rr) return 0u;                         // break: pending direct light is dropped
-    if (j >= td.bounceLimit) return 0u;                          // loop ends: nothing computed now is consumed
+    const bool stop = rng_next(state) > rr;                      // break: pending direct light is dropped
+    if (stop || j >= td.bounceLimit) {                           // or the loop ends: nothing computed now is consumed,
+        reinterpret_cast<float*>(&A.rayD[p])[3] = as_float(state);   // except the RNG state (next sample of the dispatch)
+        return 0u;
+    }
     atten = atten * (1.f / rr);
 
     A.atten[p] = f4(atten, 0.f);

@@ -25,7 +25,7 @@ struct WavefrontState {
     uint32_t maxDepth = 0;
     // path state
     DeviceBuffer dPaths[9];
-    DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters;
+    DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters, dSampleSum;
     PathArrays arrays{};
     size_t capacity = 0;
     uint32_t countSlots = 0;
@@ -348,6 +348,17 @@ __global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant
         stage_accumulate(P, A, accum, pix);
 }
 
+// Multi-sample dispatches (raysPerPixel / sampleLimit > 1, raytrace.comp:568-574): outColor = (sum of the samples in
+// order) / samples. After the last sample the mean replaces A.total, which accumulate / dispatch_resolve read.
+__global__ void __launch_bounds__(WF_THREADS) k_sample_sum(PathArrays A, float4* sum, uint32_t nPaths, uint32_t sample, uint32_t samples) {
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < nPaths; p += gridDim.x * blockDim.x) {
+        v3 acc = sample ? xyz(sum[p]) : splat3(0.f);
+        acc = acc + xyz(A.total[p]);
+        if (sample + 1 == samples) A.total[p] = f4(acc / float(samples), 0.f);
+        else sum[p] = f4(acc, 0.f);
+    }
+}
+
 // One literal dispatch served by the wavefront: main() after trace() (raytrace.comp:568-593) for 1-sample dispatches.
 // outColor of the single frame slot goes through the same ref_resolve as the per-pixel kernel (progressive blend with
 // the stored image, NaN/Inf -> magenta) and, with option storage_rgba8, the same unorm8 rounding.
@@ -511,7 +522,7 @@ void wavefront_destroy(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w) return;
     DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dUv, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
-                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters};
+                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters, &w->dSampleSum};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
@@ -551,9 +562,9 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     WavefrontState* w = c->wf;
     if (!w) { c->error = "wavefront: no scene"; return 3; }
     if (n == 0 || row1 <= row0) return 0;
-    uint32_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
-    if (samples != 1) {
-        // samples inside one dispatch share a sequential RNG state (A-Q5): served by the per-pixel kernel
+    const uint32_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
+    if (samples == 0) {
+        // no sample: outColor = 0/0 (raytrace.comp:574) — the per-pixel kernel produces exactly that
         cudaError_t e = launch_ref_frames(c, pc, first, n, stride, row0, row1);
         if (e != cudaSuccess) return wf_fail(c, 2, "launch_ref_frames", e);
         return 0;
@@ -604,48 +615,56 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         P.nSlots = std::min(slots, n - done);
         P.firstFrame = first + done * stride;
         P.nPaths = (uint32_t)(perSlot * P.nSlots);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
-        uint32_t* qa = (uint32_t*)w->dQueue[0].p;
-        uint32_t* qb = (uint32_t*)w->dQueue[1].p;
-        if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
-        wf_mark(c, ST_GENERATE);
-        // the primary ray of a pixel is the same in every frame (no jitter: raytrace.comp:541, A-Q4): with several
-        // frame slots in a batch it is traced once (slot 0) and the hit is shared; shade reads hit[p % perSlot] at j = 0
-        P.sharePrimary = (c->sharePrimary && P.nSlots > 1) ? 1u : 0u;
-        k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount, primaryCount);
-        // Order per bounce: shade(j), extend(j+1), connect(j). Connect comes AFTER the next extension so that NEE rays of
-        // paths whose next ray escapes (their direct light is dropped, raytrace.comp:531-534) are not traced at all.
-        P.connectAfterExtend = 1u;
-        wf_mark(c, ST_EXTEND);
-        k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
-        for (uint32_t j = 0; j < nB; ++j) {
-            wf_mark(c, ST_SHADE);
-            k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
-                                                        (uint32_t*)w->dShadowQ.p, sCount + j, j);
-            if (j + 1 < nB) {
-                wf_mark(c, ST_EXTEND);
-                k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
-                wf_mark(c, ST_CONNECT);
-                k_connect_prep<<<w->gridPrep, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
-                                                                   (uint32_t*)w->dJobQ.p, oCount + j);
-                wf_mark(c, ST_OCCLUDE);
-                k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
-                wf_mark(c, ST_FINISH);
-                k_connect_finish<<<w->gridFinish, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
-                                                                     (uint32_t*)w->dJobQ.p, mCount + j);
-                k_connect_mis<<<w->smCount, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
+        if (samples > 1) WCU(wf_resize(w->dSampleSum, (size_t)P.nPaths * 16));
+        for (uint32_t smp = 0; smp < samples; ++smp) {            // samples of one dispatch run one after the other: they share the RNG stream
+            P.continueSample = smp ? 1u : 0u;
+            WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
+            uint32_t* qa = (uint32_t*)w->dQueue[0].p;
+            uint32_t* qb = (uint32_t*)w->dQueue[1].p;
+            if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
+            wf_mark(c, ST_GENERATE);
+            // the primary ray of a pixel is the same in every frame (no jitter: raytrace.comp:541, A-Q4): with several
+            // frame slots in a batch it is traced once (slot 0) and the hit is shared; shade reads hit[p % perSlot] at j = 0
+            P.sharePrimary = (c->sharePrimary && P.nSlots > 1) ? 1u : 0u;
+            k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount, primaryCount);
+            // Order per bounce: shade(j), extend(j+1), connect(j). Connect comes AFTER the next extension so that NEE rays of
+            // paths whose next ray escapes (their direct light is dropped, raytrace.comp:531-534) are not traced at all.
+            P.connectAfterExtend = 1u;
+            wf_mark(c, ST_EXTEND);
+            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
+            for (uint32_t j = 0; j < nB; ++j) {
+                wf_mark(c, ST_SHADE);
+                k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
+                                                            (uint32_t*)w->dShadowQ.p, sCount + j, j);
+                if (j + 1 < nB) {
+                    wf_mark(c, ST_EXTEND);
+                    k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
+                    wf_mark(c, ST_CONNECT);
+                    k_connect_prep<<<w->gridPrep, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                                                                       (uint32_t*)w->dJobQ.p, oCount + j);
+                    wf_mark(c, ST_OCCLUDE);
+                    k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
+                    wf_mark(c, ST_FINISH);
+                    k_connect_finish<<<w->gridFinish, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                                                                         (uint32_t*)w->dJobQ.p, mCount + j);
+                    k_connect_mis<<<w->smCount, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
+                }
+                std::swap(qa, qb);
+                c->counters[0] += (j + 1 < nB) ? 6 : 1;
             }
-            std::swap(qa, qb);
-            c->counters[0] += (j + 1 < nB) ? 6 : 1;
+            k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
+            c->counters[0] += 3;                                      // generate, extend(0), fold
+            if (samples > 1) {
+                k_sample_sum<<<grid, WF_THREADS, 0, c->stream>>>(w->arrays, (float4*)w->dSampleSum.p, P.nPaths, smp, samples);
+                c->counters[0] += 1;
+            }
         }
-        c->counters[0] += 1;
         wf_mark(c, ST_ACCUMULATE);
         if (dispatchImage) k_dispatch_resolve<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, dispatchImage, c->storageRgba8);
         else k_accumulate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, c->accum);
-        k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
         wf_mark(c, -1);
-        c->counters[0] += 3;
-        c->counters[1] += P.nPaths;
+        c->counters[0] += 1;
+        c->counters[1] += (uint64_t)P.nPaths * samples;
         WCU(cudaGetLastError());
     }
     return 0;

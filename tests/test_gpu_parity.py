@@ -121,10 +121,13 @@ def test_radiance_bunny_env(gpu, bunny_blobs):
 
 
 def test_run_compute_dispatch_semantics(gpu, cornell_blobs):
-    # b200pt_render = one literal dispatch: progressive blend, multi-sample, stats, debug heat-map
+    # b200pt_render = one literal dispatch: progressive blend, multi-sample, stats, debug heat-map — on the per-pixel
+    # reference-order kernel (pipeline 0: the only one with the box / triangle test counters; the wavefront form of the
+    # same dispatches is covered by the two tests at the end of this file)
     W = H = 96
     sc = ob.OracleScene(cornell_blobs)
     cp = _pass(gpu, cornell_blobs, W, H)
+    cp.set_option("pipeline", 0)
     pc = ob.default_push_constants(W, H, 10, 9)
     pc[160] = 1                            # progressive
     pc.view(np.uint32)[43] = 2             # raysPerPixel
@@ -512,3 +515,43 @@ def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, b
         a, b = fast.read_image(), slow.read_image()
         assert _differing(a, b) <= 2e-3
         assert np.array_equal(a[..., :3], np.rint(a[..., :3] * 255) / np.float32(255))
+
+
+def test_multi_sample_dispatches_share_the_rng_stream(gpu, cornell_blobs):
+    # raysPerPixel / sampleLimit > 1: the samples of one dispatch continue ONE RNG stream per pixel (raytrace.comp:562-574).
+    # The wavefront runs them as consecutive passes handing the state over; compare with the literal per-pixel kernel and
+    # with the oracle, for b200pt_render and for accumulated frames.
+    W, H = 128, 96
+    sc = ob.OracleScene(cornell_blobs)
+    fast, slow = _pass(gpu, cornell_blobs, W, H), _pass(gpu, cornell_blobs, W, H)
+    slow.set_option("pipeline", 0)
+    for rpp, single in ((3, 0), (2, 1)):
+        pc = ob.default_push_constants(W, H, 10, 9)
+        pc[160] = 1
+        if single:
+            pc[164] = 1                                         # singleRender: sampleLimit samples
+            pc.view(np.uint32)[49] = rpp                        # sampleLimit
+        else:
+            pc.view(np.uint32)[43] = rpp
+        image = np.zeros((H, W, 4), np.float32)
+        fast.clear(); slow.clear()
+        with ob.math_mode(1):
+            for f in range(2):
+                pc.view(np.uint32)[50] = f
+                sc.render_dispatch(pc, W, H, image=image)
+                fast.run_compute(pc)
+                slow.run_compute(pc)
+        a, b = fast.read_image(), slow.read_image()
+        assert _differing(a, b) <= 2e-3, (rpp, single)
+        assert _differing(a, image) <= 2e-3, (rpp, single)
+        assert fast.counters()["paths"] == 2 * rpp * W * H
+    # accumulated progressive frames with 2 samples each, several frames in flight
+    pc = ob.default_push_constants(W, H, 10, 9)
+    pc.view(np.uint32)[43] = 2
+    fast.clear(); slow.clear()
+    fast.set_option("frames_in_flight", 3)
+    fast.render_frames(pc, 0, 5)
+    slow.render_frames(pc, 0, 5)
+    a, b = fast.read_accum(), slow.read_accum()
+    assert np.array_equal(a[..., 3], np.full((H, W), 5, np.float32))
+    assert _differing(a, b) <= 2e-3
