@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--frames-per-step", type=int, default=8)
+    ap.add_argument("--frames-per-step", type=int, default=24)
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--bounce-limit", type=int, default=8)
@@ -401,8 +401,9 @@ def main():
         achieved = stage_bytes[dom] * paths_rank / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else None
         traffic = None
         try:
-            if (args.width, args.height, F, args.obj) == (1920, 1080, 8, None):      # the configuration the capture was taken on
-                traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dom)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            if (args.width, args.height, F, args.obj) == (1920, 1080, tj.get("frames_in_flight"), None):      # the configuration the capture was taken on
+                traffic = tj.get(args.workload, {}).get(dom)
         except (OSError, ValueError):
             pass
         # second candidate bound of SURVEY.md §8(d3): FP32 issue. Flops per path of the extension rays in the
