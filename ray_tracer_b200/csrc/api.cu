@@ -223,7 +223,7 @@ int b200pt_update_materials(b200pt_ctx* c, const void* materials, uint32_t n) {
     if (const char* why = validate_scene(c)) { c->hMaterials = old; return fail(c, B200PT_ERR_ARG, "update_materials: %s", why); }
     if (int rc = upload_vec(c, c->dMaterials, c->hMaterials)) return rc;
     CU(c, cudaStreamSynchronize(c->stream));
-    return wavefront_build_scene(c);      // emissive/non-emissive split depends on the materials
+    return wavefront_build_scene(c, pt::WF_CHANGED_MATERIALS);      // emissive/non-emissive split depends on the materials
 }
 
 int b200pt_update_spheres(b200pt_ctx* c, const void* spheres, uint32_t n) {
@@ -236,7 +236,7 @@ int b200pt_update_spheres(b200pt_ctx* c, const void* spheres, uint32_t n) {
     if (const char* why = validate_scene(c)) { c->hSpheres = old; return fail(c, B200PT_ERR_ARG, "update_spheres: %s", why); }
     if (int rc = upload_vec(c, c->dSpheres, c->hSpheres)) return rc;
     CU(c, cudaStreamSynchronize(c->stream));
-    return wavefront_build_scene(c);
+    return wavefront_build_scene(c, pt::WF_CHANGED_SPHERES);
 }
 
 int b200pt_update_objects(b200pt_ctx* c, const void* objects, uint32_t n) {

@@ -326,16 +326,12 @@ inline void bvh8_build(const std::vector<b8::Box>& boxes, const std::vector<b8::
                 std::chrono::duration<double>(t1 - t0).count(), std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count());
 }
 
-// Reference-layout buffers -> WideSceneHost. Returns nullptr on success or a message.
-inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials,
-                                    const std::vector<ptl::TrianglePoint>& points, const std::vector<ptl::Triangle>& tris,
-                                    const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes,
-                                    WideSceneHost& out, bool buildAll = true) {
-    using namespace b8;
-    out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
-    out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
+// Sphere slot masks (WideScene) and the flags that depend only on spheres and materials; also used alone when only
+// those two buffers changed and no triangle moved between the emissive and the non-emissive set.
+inline void wide_sphere_masks(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials, WideSceneHost& out) {
     auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
     out.uniqSphereMask = out.emisSphereMask = out.plainSphereMask = 0;
+    out.anyEmissive = false;
     for (size_t i = 0; i < spheres.size(); ++i) {
         bool em = emissive(spheres[i].materialIndex);
         if (em) out.anyEmissive = true;
@@ -349,6 +345,21 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
         if (firstAll) out.uniqSphereMask |= 1u << i;
         if (firstClass) (em ? out.emisSphereMask : out.plainSphereMask) |= 1u << i;
     }
+    out.emissionFinite = true;
+    for (const auto& m : materials)
+        for (int k = 0; k < 3; ++k) if (!std::isfinite(m.emissionColor[k] * m.emissionStrength)) out.emissionFinite = false;
+}
+
+// Reference-layout buffers -> WideSceneHost. Returns nullptr on success or a message.
+inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials,
+                                    const std::vector<ptl::TrianglePoint>& points, const std::vector<ptl::Triangle>& tris,
+                                    const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes,
+                                    WideSceneHost& out, bool buildAll = true) {
+    using namespace b8;
+    out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
+    out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
+    auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
+    wide_sphere_masks(spheres, materials, out);
 
     // distinct object matrices (bit pattern): objects that share one share the transformed ray
     for (size_t o = 0; o < objects.size(); ++o) {
@@ -409,9 +420,6 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             if (em) { boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); uvsE.push_back(uvr); }
         }
     }
-    out.emissionFinite = true;
-    for (const auto& m : materials)
-        for (int k = 0; k < 3; ++k) if (!std::isfinite(m.emissionColor[k] * m.emissionStrength)) out.emissionFinite = false;
     {
         b8::Box u; b8::box_reset(u);
         for (const auto& bx : boxesE) b8::box_grow(u, bx);

@@ -27,6 +27,8 @@ struct WavefrontState {
     DeviceBuffer dPaths[9];
     DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters, dSampleSum;
     PathArrays arrays{};
+    std::vector<uint8_t> objEmissive;  // per object: material emits (decides which tree a triangle is in)
+    bool haveScene = false, anyEmissiveTri = false;
     size_t capacity = 0;
     uint32_t countSlots = 0;
     int smCount = 148;
@@ -447,7 +449,7 @@ static cudaError_t wf_upload(b200pt_ctx* c, DeviceBuffer& d, const std::vector<T
     return e;
 }
 
-int wavefront_build_scene(b200pt_ctx* c) {
+int wavefront_build_scene(b200pt_ctx* c, int changed) {
     if (!c->wf) {
         c->wf = new WavefrontState();
         cudaDeviceProp prop;
@@ -456,6 +458,23 @@ int wavefront_build_scene(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     WideSceneHost host;
     const auto tBuild = std::chrono::steady_clock::now();
+    // Only spheres or materials changed and no object moved between the emissive and the non-emissive set: triangles,
+    // trees and records stay; the sphere slot masks and the scene-wide flags are recomputed.
+    std::vector<uint8_t> objEmissive(c->hObjects.size());
+    for (size_t o = 0; o < c->hObjects.size(); ++o)
+        objEmissive[o] = !(c->hMaterials[c->hObjects[o].materialIndex].emissionStrength == 0.f);
+    if (changed != WF_CHANGED_ALL && w->haveScene && objEmissive == w->objEmissive) {
+        wide_sphere_masks(c->hSpheres, c->hMaterials, host);
+        WideScene& s = w->scene;
+        s.spheres = c->ref.spheres; s.materials = c->ref.materials;
+        s.anyEmissive = (host.anyEmissive || w->anyEmissiveTri) ? 1u : 0u;
+        s.emissionFinite = host.emissionFinite ? 1u : 0u;
+        s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
+        c->lastWideDeviceMs = 0.0;
+        c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
+        return 0;
+    }
+    w->objEmissive = objEmissive; w->haveScene = false;
     const bool onDevice = c->wideBuild != 0;
     if (const char* err = build_wide_scene(c->hSpheres, c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, host, !onDevice)) {
         c->error = std::string("scene re-layout: ") + err;
@@ -506,6 +525,8 @@ int wavefront_build_scene(b200pt_ctx* c) {
     for (int a = 0; a < 3; ++a) {     s.emisLo[a] = host.emisLo[a];     s.emisHi[a] = host.emisHi[a]; }
     s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
     w->maxDepth = depthAll;
+    w->haveScene = true;
+    w->anyEmissiveTri = !host.emis.prims.empty();
     c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
     return 0;
 }

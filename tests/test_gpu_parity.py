@@ -555,3 +555,40 @@ def test_multi_sample_dispatches_share_the_rng_stream(gpu, cornell_blobs):
     a, b = fast.read_accum(), slow.read_accum()
     assert np.array_equal(a[..., 3], np.full((H, W), 5, np.float32))
     assert _differing(a, b) <= 2e-3
+
+
+def test_material_and_sphere_updates_rebuild_only_when_needed(gpu, cornell_blobs):
+    # UI "update materials" / "update spheres" (src/vk_engine.cpp:1545,1572): the internal trees are rebuilt only when an
+    # object switches between emitting and not emitting; either way the next frames must equal a fresh upload's
+    W, H = 96, 72
+    pc = ob.default_push_constants(W, H, 10, 9)
+    cp = _pass(gpu, cornell_blobs, W, H)
+
+    def check(blobs):
+        cp.clear()
+        cp.render_frames(pc, 0, 3)
+        with ob.math_mode(1):
+            want, _ = ob.OracleScene(blobs).render_frames(pc, W, H, 0, 3)
+        assert _differing(cp.read_accum(), want) <= 2e-3
+
+    mats = cornell_blobs["materials"].copy()
+    mats.view(np.float32).reshape(-1, 16)[1, 0:3] = (0.1, 0.8, 0.3)          # recolour: nothing moves between the trees
+    cp.update_buffer("materials", mats)
+    assert cp.get_option("last_wide_device_us") == 0
+    check(dict(cornell_blobs, materials=mats))
+    sph = cornell_blobs["spheres"].copy()
+    sph.view(np.float32).reshape(-1, 8)[1, 0:4] = (0.3, -0.2, 0.1, 0.25)     # move + resize a sphere
+    sph.view(np.float32).reshape(-1, 8)[3, 0:4] = (0.3, -0.2, 0.1, 0.25)     # and make a duplicate slot (mask classes change)
+    cp.update_buffer("spheres", sph)
+    assert cp.get_option("last_wide_device_us") == 0
+    check(dict(cornell_blobs, materials=mats, spheres=sph))
+    mats2 = mats.copy()
+    mats2.view(np.float32).reshape(-1, 16)[2, 4:8] = (0.5, 1.0, 0.5, 1.5)    # the green wall starts to emit: trees change
+    cp.update_buffer("materials", mats2)
+    assert cp.get_option("last_wide_device_us") > 0
+    check(dict(cornell_blobs, materials=mats2, spheres=sph))
+    mats3 = mats2.copy()
+    mats3.view(np.float32).reshape(-1, 16)[5, 7] = 3.0                       # the dielectric sphere's material emits: spheres only
+    cp.update_buffer("materials", mats3)
+    assert cp.get_option("last_wide_device_us") == 0
+    check(dict(cornell_blobs, materials=mats3, spheres=sph))
