@@ -385,6 +385,12 @@ struct Buffers {                             // freed on every exit path
     }
 };
 
+struct Events {
+    cudaEvent_t e[2] = {nullptr, nullptr};
+    cudaError_t create() { cudaError_t r = cudaEventCreate(&e[0]); return r != cudaSuccess ? r : cudaEventCreate(&e[1]); }
+    ~Events() { for (cudaEvent_t x : e) if (x) cudaEventDestroy(x); }
+};
+
 }  // namespace bvh2
 
 #define BCU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { char m_[256]; snprintf(m_, sizeof m_, "b200pt_build_bvh: %s: %s", #x, cudaGetErrorString(e_)); pt::set_global_error(m_); return 2; } } while (0)
@@ -415,8 +421,9 @@ extern "C" int b200pt_build_bvh(int device, const void* triPointsV, uint32_t nPo
     BCU(mem.get(&counters, 4)); BCU(mem.get(&nodes, maxNodes));
     for (auto& p : lists) BCU(mem.get(&p, n / 3 + 1));       // a listed node holds at least 3 triangles
     cudaStream_t st = 0;
-    cudaEvent_t e0, e1;
-    BCU(cudaEventCreate(&e0)); BCU(cudaEventCreate(&e1));
+    Events ev;                                               // destroyed on every exit path
+    BCU(ev.create());
+    cudaEvent_t e0 = ev.e[0], e1 = ev.e[1];
     BCU(cudaMemcpyAsync(dPts, points + vLo, nP * sizeof(ptl::TrianglePoint), cudaMemcpyHostToDevice, st));
     BCU(cudaMemcpyAsync(dTris, tris, n * sizeof(ptl::Triangle), cudaMemcpyHostToDevice, st));
     BCU(cudaEventRecord(e0, st));
@@ -472,6 +479,5 @@ extern "C" int b200pt_build_bvh(int device, const void* triPointsV, uint32_t nPo
     BCU(cudaMemcpyAsync(tris, dTrisOut, n * sizeof(ptl::Triangle), cudaMemcpyDeviceToHost, st));
     BCU(cudaStreamSynchronize(st));
     if (deviceMs) { float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1); *deviceMs = ms; }
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;
 }

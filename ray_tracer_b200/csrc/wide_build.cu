@@ -386,8 +386,12 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     WBC(h2d(instObject, host.instObject.data(), n * 4));
     WBC(h2d(instTri, host.instTri.data(), n * 4));
     d.up = up; d.leafOf = leafOf; d.objXform = objXform; d.instObject = instObject; d.instTri = instTri;
-    cudaEvent_t e0, e1;
-    WBC(cudaEventCreate(&e0)); WBC(cudaEventCreate(&e1));
+    struct Events {
+        cudaEvent_t e[2] = {nullptr, nullptr};
+        ~Events() { for (cudaEvent_t x : e) if (x) cudaEventDestroy(x); }
+    } ev;                                                   // destroyed on every exit path
+    WBC(cudaEventCreate(&ev.e[0])); WBC(cudaEventCreate(&ev.e[1]));
+    cudaEvent_t e0 = ev.e[0], e1 = ev.e[1];
     WBC(cudaMemsetAsync(d.counters, 0, 64, st));
     WBC(cudaEventRecord(e0, st));
     uint32_t h[16] = {0};
@@ -457,7 +461,6 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     WBC(cudaStreamSynchronize(st));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
-    cudaEventDestroy(e0); cudaEventDestroy(e1);
     out.deviceMs = ms;
     out.nodes = d.outNodes; out.prims = d.outPrim; out.shade = d.outShade; out.uv = d.outUv;
     mem.release(d.outNodes); mem.release(d.outPrim); mem.release(d.outShade); mem.release(d.outUv);
