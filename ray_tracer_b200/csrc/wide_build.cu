@@ -10,6 +10,7 @@
 //   k_wide_emit      one thread per wide node and level: collapse, slots, quantisation, record copies
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -426,9 +427,17 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
         WBC(cudaMemcpyAsync(d.counters, init, 64, cudaMemcpyHostToDevice, st));
         const unsigned threadsOf[3] = {32, 256, 1024};
         int cur = 0;
+        const bool timing = std::getenv("B200PT_BUILD_TIMING") != nullptr;
+        auto tLevel = std::chrono::steady_clock::now();
         for (int level = 0;; ++level) {
             WBC(cudaMemcpyAsync(h, d.counters, 64, cudaMemcpyDeviceToHost, st));
             WBC(cudaStreamSynchronize(st));
+            if (timing) {
+                auto now = std::chrono::steady_clock::now();
+                fprintf(stderr, "[wide] level %d done in %.3f ms; next lists %u / %u / %u nodes\n", level - 1,
+                        std::chrono::duration<double, std::milli>(now - tLevel).count(), h[2], h[3], h[4]);
+                tLevel = now;
+            }
             if (h[2] + h[3] + h[4] == 0) break;
             if (level > 4096) return "wide BVH device build: binary tree does not terminate";
             const uint32_t* curList[3] = {lists[cur * 3], lists[cur * 3 + 1], lists[cur * 3 + 2]};
@@ -445,6 +454,11 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
         uint32_t nItems = 1;
         int ecur = 0;
         while (nItems) {
+            if (timing) {
+                auto now = std::chrono::steady_clock::now();
+                fprintf(stderr, "[wide] emit level: %u nodes (previous step %.3f ms)\n", nItems, std::chrono::duration<double, std::milli>(now - tLevel).count());
+                tLevel = now;
+            }
             d.emitNext = emit[ecur ^ 1];
             WBC(cudaMemsetAsync(d.counters + 7, 0, 4, st));
             k_wide_emit<<<(nItems + 63) / 64, 64, 0, st>>>(d, emit[ecur], nItems);
