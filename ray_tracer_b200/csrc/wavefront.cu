@@ -27,6 +27,9 @@ struct WavefrontState {
     DeviceBuffer dPaths[9];
     DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters, dSampleSum;
     PathArrays arrays{};
+    WideDeviceResult wideRes;          // device-built tree (owned here; dNodes / dPrims / dShade / dUv alias it while wideOnDevice)
+    WideBuildCache wideCache;
+    bool wideOnDevice = false;
     std::vector<uint8_t> objEmissive;  // per object: material emits (decides which tree a triangle is in)
     bool haveScene = false, anyEmissiveTri = false;
     size_t capacity = 0;
@@ -441,6 +444,18 @@ static cudaError_t wf_resize(DeviceBuffer& b, size_t bytes) {
     return e;
 }
 static void wf_free(DeviceBuffer& b) { if (b.p) cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
+// frees a device-built tree (the four DeviceBuffers only alias it); host-uploaded trees stay until overwritten
+static void wf_release_tree(WavefrontState* w) {
+    if (!w->wideOnDevice) return;
+    w->dNodes = DeviceBuffer{}; w->dPrims = DeviceBuffer{}; w->dShade = DeviceBuffer{}; w->dUv = DeviceBuffer{};
+    WideDeviceResult& r = w->wideRes;
+    if (r.nodes) cudaFree(r.nodes);
+    if (r.prims) cudaFree(r.prims);
+    if (r.shade) cudaFree(r.shade);
+    if (r.uv) cudaFree(r.uv);
+    r = WideDeviceResult{};
+    w->wideOnDevice = false;
+}
 
 template <class T>
 static cudaError_t wf_upload(b200pt_ctx* c, DeviceBuffer& d, const std::vector<T>& h) {
@@ -482,18 +497,24 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     }
     uint32_t nNodesAll, nPrimsAll, depthAll;
     c->lastWideDeviceMs = 0.0;
+    const bool timing = std::getenv("B200PT_BUILD_TIMING") != nullptr;
+    if (timing) fprintf(stderr, "[relayout] host part %.3f ms\n", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count());
     if (onDevice) {
         WideDeviceInputs in{(const ptl::TrianglePoint*)c->dPoints.p, (const ptl::Triangle*)c->dTris.p, (const ptl::RenderObject*)c->dObjects.p,
                             (const ptl::Material*)c->dMaterials.p};
-        WideDeviceResult res;
-        if (const char* err = wide_build_device(c->stream, in, host, res)) { c->error = err; return 2; }
-        wf_free(w->dNodes); wf_free(w->dPrims); wf_free(w->dShade); wf_free(w->dUv);
+        if (!w->wideOnDevice) { wf_free(w->dNodes); wf_free(w->dPrims); wf_free(w->dShade); wf_free(w->dUv); }
+        WideDeviceResult& res = w->wideRes;
+        if (const char* err = wide_build_device(c->stream, in, host, res, &w->wideCache)) { c->error = err; wf_release_tree(w); return 2; }
+        w->wideOnDevice = true;
         w->dNodes = {res.nodes, (size_t)res.nNodes * sizeof(Bvh8Node)}; w->dPrims = {res.prims, (size_t)res.nPrims * sizeof(PrimRecord)};
         w->dShade = {res.shade, (size_t)res.nPrims * sizeof(ShadeRecord)}; w->dUv = {res.uv, (size_t)res.nPrims * sizeof(UvRecord)};
         nNodesAll = res.nNodes; nPrimsAll = res.nPrims; depthAll = res.maxDepth;
         c->lastWideDeviceMs = res.deviceMs;
+        if (timing) fprintf(stderr, "[relayout] + device build (alloc, copies, kernels %.3f ms): %.3f ms\n", res.deviceMs,
+                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count());
         if (depthAll > PT_BVH8_MAX_DEPTH) { c->error = "scene re-layout: wide BVH deeper than the traversal stack"; return 1; }
     } else {
+        wf_release_tree(w);
         WCU(wf_upload(c, w->dNodes, host.all.nodes));
         WCU(wf_upload(c, w->dPrims, host.all.prims));
         WCU(wf_upload(c, w->dShade, host.all.shade));
@@ -542,6 +563,7 @@ void wavefront_set_textures(b200pt_ctx* c) {
 void wavefront_destroy(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w) return;
+    wf_release_tree(w);
     DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dUv, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
                            &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters, &w->dSampleSum};
     for (DeviceBuffer* b : all) wf_free(*b);
@@ -581,7 +603,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
                             uint32_t row0, uint32_t row1, float4* dispatchImage) {
     WavefrontState* w = c->wf;
-    if (!w) { c->error = "wavefront: no scene"; return 3; }
+    if (!w || !w->haveScene) { c->error = "wavefront: no scene (the last upload or update failed)"; return 3; }
     if (n == 0 || row1 <= row0) return 0;
     const uint32_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
     if (samples == 0) {
@@ -693,7 +715,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
 
 int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits) {
     WavefrontState* w = c->wf;
-    if (!w) { c->error = "wavefront: no scene"; return 3; }
+    if (!w || !w->haveScene) { c->error = "wavefront: no scene (the last upload or update failed)"; return 3; }
     if (n == 0) return 0;
     k_wide_trace_batch<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(w->scene, pc.params.sphereCount, pc.params.objectCount,
                                                                          (const float4*)dRays, n, dHits);

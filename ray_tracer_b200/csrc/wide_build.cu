@@ -346,25 +346,14 @@ __global__ void k_wide_emit(Dev d, const EmitItem* __restrict__ items, uint32_t 
 }  // namespace wb
 
 namespace {
-struct Scratch {                             // everything except the four result buffers
-    std::vector<void*> ptrs;
-    ~Scratch() { for (void* p : ptrs) cudaFree(p); }
-    template <class T> cudaError_t get(T** p, size_t count) {
-        cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
-        if (e == cudaSuccess) ptrs.push_back(*p);
-        return e;
-    }
-    void release(void* p) { ptrs.erase(std::remove(ptrs.begin(), ptrs.end(), p), ptrs.end()); }
-};
 thread_local char g_msg[256];
 }  // namespace
 
 #define WBC(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(g_msg, sizeof g_msg, "wide BVH device build: %s: %s", #x, cudaGetErrorString(e_)); return g_msg; } } while (0)
 
-const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out) {
+const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out, WideBuildCache* cache) {
     using namespace wb;
     const size_t n = host.instTri.size();
-    Scratch mem;
     Dev d{};
     d.points = in.points; d.tris = in.tris; d.objects = in.objects; d.materials = in.materials;
     d.nInst = (uint32_t)n;
@@ -373,13 +362,46 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     if (const char* e = std::getenv("B200PT_BVH_CT")) d.travCost = (float)std::atof(e);
     UpNode* up; uint32_t *leafOf, *objXform, *instObject, *instTri, *lists[6];
     EmitItem* emit[2];
-    WBC(mem.get(&up, host.up.size())); WBC(mem.get(&leafOf, host.leafOf.size())); WBC(mem.get(&objXform, host.objXform.size()));
-    WBC(mem.get(&instObject, n)); WBC(mem.get(&instTri, n));
-    WBC(mem.get(&d.prim, n)); WBC(mem.get(&d.shade, n)); WBC(mem.get(&d.uv, n)); WBC(mem.get(&d.box, n));
-    WBC(mem.get(&d.idx, n)); WBC(mem.get(&d.idxTmp, n)); WBC(mem.get(&d.valid, n)); WBC(mem.get(&d.nodes2, 2 * n + 1)); WBC(mem.get(&d.counters, 16));
-    for (auto& p : lists) WBC(mem.get(&p, n / 2 + 1));        // a listed node holds at least 2 triangles
-    WBC(mem.get(&emit[0], n + 1)); WBC(mem.get(&emit[1], n + 1));
-    WBC(mem.get(&d.outNodes, n + 1)); WBC(mem.get(&d.outPrim, n)); WBC(mem.get(&d.outShade, n)); WBC(mem.get(&d.outUv, n));
+    // One arena for all scratch (cudaMalloc / cudaFree of two dozen buffers cost as much as the kernels for a
+    // 265 k-triangle scene); kept in `cache` between builds while it is small enough to be worth holding on to.
+    WideBuildCache local;
+    WideBuildCache& arena = cache ? *cache : local;
+    size_t need = 0;
+    auto plan = [&](size_t count, size_t elem) { size_t off = need; need += (std::max<size_t>(count, 1) * elem + 255) & ~(size_t)255; return off; };
+    const size_t oUp = plan(host.up.size(), sizeof(UpNode)), oLeaf = plan(host.leafOf.size(), 4), oObjX = plan(host.objXform.size(), 4),
+                 oInstO = plan(n, 4), oInstT = plan(n, 4), oPrim = plan(n, sizeof(PrimRecord)), oShade = plan(n, sizeof(ShadeRecord)),
+                 oUv = plan(n, sizeof(UvRecord)), oBox = plan(n, sizeof(WideBox)), oIdx = plan(n, 4), oIdxT = plan(n, 4), oValid = plan(n, 1),
+                 oNodes2 = plan(2 * n + 1, sizeof(Node2)), oCnt = plan(16, 4), oEmit0 = plan(n + 1, sizeof(EmitItem)), oEmit1 = plan(n + 1, sizeof(EmitItem));
+    size_t oList[6];
+    for (auto& o : oList) o = plan(n / 2 + 1, 4);              // a listed node holds at least 2 triangles
+    if (arena.bytes < need) {
+        if (arena.p) cudaFree(arena.p);
+        arena.p = nullptr; arena.bytes = 0;
+        WBC(cudaMalloc(&arena.p, need));
+        arena.bytes = need;
+    }
+    char* base = (char*)arena.p;
+    up = (UpNode*)(base + oUp); leafOf = (uint32_t*)(base + oLeaf); objXform = (uint32_t*)(base + oObjX);
+    instObject = (uint32_t*)(base + oInstO); instTri = (uint32_t*)(base + oInstT);
+    d.prim = (PrimRecord*)(base + oPrim); d.shade = (ShadeRecord*)(base + oShade); d.uv = (UvRecord*)(base + oUv); d.box = (WideBox*)(base + oBox);
+    d.idx = (uint32_t*)(base + oIdx); d.idxTmp = (uint32_t*)(base + oIdxT); d.valid = (uint8_t*)(base + oValid);
+    d.nodes2 = (Node2*)(base + oNodes2); d.counters = (uint32_t*)(base + oCnt);
+    emit[0] = (EmitItem*)(base + oEmit0); emit[1] = (EmitItem*)(base + oEmit1);
+    for (int i = 0; i < 6; ++i) lists[i] = (uint32_t*)(base + oList[i]);
+    // the four result buffers: the caller's previous ones are written again when they are large enough
+    struct Fresh { std::vector<void*> p; ~Fresh() { for (void* q : p) cudaFree(q); } } fresh;      // freed unless handed over
+    const size_t capNodes = (n + 1) * sizeof(Bvh8Node), capPrim = std::max<size_t>(n, 1) * sizeof(PrimRecord),
+                 capShade = std::max<size_t>(n, 1) * sizeof(ShadeRecord), capUv = std::max<size_t>(n, 1) * sizeof(UvRecord);
+    const bool recycle = out.nodes && out.prims && out.shade && out.uv && out.capacityInstances >= n;
+    if (recycle) {
+        d.outNodes = (Bvh8Node*)out.nodes; d.outPrim = (PrimRecord*)out.prims; d.outShade = (ShadeRecord*)out.shade; d.outUv = (UvRecord*)out.uv;
+    } else {
+        void* q;
+        WBC(cudaMalloc(&q, capNodes)); fresh.p.push_back(q); d.outNodes = (Bvh8Node*)q;
+        WBC(cudaMalloc(&q, capPrim)); fresh.p.push_back(q); d.outPrim = (PrimRecord*)q;
+        WBC(cudaMalloc(&q, capShade)); fresh.p.push_back(q); d.outShade = (ShadeRecord*)q;
+        WBC(cudaMalloc(&q, capUv)); fresh.p.push_back(q); d.outUv = (UvRecord*)q;
+    }
     auto h2d = [&](void* dst, const void* src, size_t bytes) { return bytes ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess; };
     WBC(h2d(up, host.up.data(), host.up.size() * sizeof(UpNode)));
     WBC(h2d(leafOf, host.leafOf.data(), host.leafOf.size() * 4));
@@ -476,8 +498,16 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     float ms = 0.f;
     cudaEventElapsedTime(&ms, e0, e1);
     out.deviceMs = ms;
+    if (!recycle) {
+        if (out.nodes) cudaFree(out.nodes);
+        if (out.prims) cudaFree(out.prims);
+        if (out.shade) cudaFree(out.shade);
+        if (out.uv) cudaFree(out.uv);
+        out.capacityInstances = n;
+        fresh.p.clear();                      // handed over
+    }
     out.nodes = d.outNodes; out.prims = d.outPrim; out.shade = d.outShade; out.uv = d.outUv;
-    mem.release(d.outNodes); mem.release(d.outPrim); mem.release(d.outShade); mem.release(d.outUv);
+    if (arena.bytes > WideBuildCache::kKeepBytes && cache) { cudaFree(cache->p); cache->p = nullptr; cache->bytes = 0; }
     return nullptr;
 }
 

@@ -11,13 +11,24 @@ namespace pt {
 struct WideDeviceInputs {                    // reference-layout buffers already on the device (b200pt_upload_scene)
     const ptl::TrianglePoint* points; const ptl::Triangle* tris; const ptl::RenderObject* objects; const ptl::Material* materials;
 };
-struct WideDeviceResult {                    // cudaMalloc'ed, owned by the caller after success
-    void* nodes = nullptr; void* prims = nullptr; void* shade = nullptr; void* uv = nullptr;
+struct WideDeviceResult {                    // cudaMalloc'ed, owned by the caller. In/out: buffers of an earlier build with room for
+    void* nodes = nullptr; void* prims = nullptr; void* shade = nullptr; void* uv = nullptr;   // as many instances are written again,
+    size_t capacityInstances = 0;                                                               // otherwise freed and replaced
     uint32_t nNodes = 0, nPrims = 0, maxDepth = 0;
     double deviceMs = 0.0;
 };
+struct WideBuildCache {                      // scratch arena kept between builds (released by the owner's destructor)
+    static constexpr size_t kKeepBytes = (size_t)1 << 30;      // larger arenas are freed after the build
+    void* p = nullptr;
+    size_t bytes = 0;
+    WideBuildCache() = default;
+    WideBuildCache(const WideBuildCache&) = delete;
+    WideBuildCache& operator=(const WideBuildCache&) = delete;
+    ~WideBuildCache() { if (p) cudaFree(p); }
+};
 // host: result of build_wide_scene(..., buildAll = false) (instObject / instTri / leafOf / up / objXform filled).
 // Returns nullptr or an error text.
-const char* wide_build_device(cudaStream_t stream, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out);
+const char* wide_build_device(cudaStream_t stream, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out,
+                              WideBuildCache* cache = nullptr);
 
 }  // namespace pt
