@@ -24,6 +24,7 @@ namespace pt {
 namespace wb {
 
 constexpr int NB = 16;
+constexpr uint32_t HUGE_MIN = 32768;         // nodes with more triangles are split by many blocks (k_huge_*)
 
 struct Node2 {                               // binary SAH tree (as b8::Node2)
     float lo[3], hi[3];
@@ -42,9 +43,9 @@ struct Dev {
     PrimRecord* prim; ShadeRecord* shade; UvRecord* uv; WideBox* box;
     // binary build
     uint32_t* idx; uint32_t* idxTmp; Node2* nodes2; uint8_t* valid;
-    uint32_t* counters;                      // [0] valid instances [1] binary nodes [2..4] next split lists [5] wide nodes [6] prims out
+    uint32_t* counters;                      // [0] valid instances [1] binary nodes [10..13] next split lists [5] wide nodes [6] prims out
                                              // [7] next emit list [8] max depth [9] instances dropped (non-finite vertices)
-    uint32_t* nextList[3];
+    uint32_t* nextList[4];                   // by triangle count: <= 64, <= 4096, <= HUGE_MIN, above
     int maxLeaf; float travCost;
     // output
     Bvh8Node* outNodes; PrimRecord* outPrim; ShadeRecord* outShade; UvRecord* outUv;
@@ -95,6 +96,31 @@ __device__ __forceinline__ float half_area(const float* lo, const float* hi) {
     return x * y + y * z + z * x;
 }
 __device__ __forceinline__ int bin_of(float c, float lo, float scale) { return min(NB - 1, (int)((c - lo) * scale)); }
+
+// binned SAH over the three axes (b8::Builder2::build): best (axis, last bin of the left side), first of equal costs
+__device__ void sah_best(const uint32_t (*binCount)[NB], const uint32_t (*binLo)[NB][3], const uint32_t (*binHi)[NB][3], const float* ext,
+                         int& bestAxis, int& bestBin, float& bestCost) {
+    for (int a = 0; a < 3; ++a) {
+        if (!(ext[a] > 0.f)) continue;
+        float rightArea[NB]; uint32_t rightCnt[NB];
+        float alo[3] = {1e30f, 1e30f, 1e30f}, ahi[3] = {-1e30f, -1e30f, -1e30f};
+        uint32_t cnt = 0;
+        for (int k = NB - 1; k > 0; --k) {
+            for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(binHi[a][k][c])); }
+            cnt += binCount[a][k];
+            rightArea[k] = cnt ? half_area(alo, ahi) : 0.f; rightCnt[k] = cnt;
+        }
+        for (int c = 0; c < 3; ++c) { alo[c] = 1e30f; ahi[c] = -1e30f; }
+        cnt = 0;
+        for (int k = 0; k < NB - 1; ++k) {
+            for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(binHi[a][k][c])); }
+            cnt += binCount[a][k];
+            if (cnt == 0 || rightCnt[k + 1] == 0) continue;
+            float cost = half_area(alo, ahi) * (float)cnt + rightArea[k + 1] * (float)rightCnt[k + 1];
+            if (cost < bestCost) { bestCost = cost; bestAxis = a; bestBin = k; }
+        }
+    }
+}
 
 // b8::Builder2::build for one node (bvh8_build.h), one block per node
 __global__ void __launch_bounds__(1024) k_wide_split(Dev d, const uint32_t* __restrict__ list, uint32_t nList) {
@@ -147,26 +173,7 @@ __global__ void __launch_bounds__(1024) k_wide_split(Dev d, const uint32_t* __re
         if (tid == 0) {
             int bestAxis = -1, bestBin = -1;
             float bestCost = 1e30f;
-            for (int a = 0; a < 3; ++a) {
-                if (!(ext[a] > 0.f)) continue;
-                float rightArea[NB]; uint32_t rightCnt[NB];
-                float alo[3] = {1e30f, 1e30f, 1e30f}, ahi[3] = {-1e30f, -1e30f, -1e30f};
-                uint32_t cnt = 0;
-                for (int k = NB - 1; k > 0; --k) {
-                    for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(s.binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(s.binHi[a][k][c])); }
-                    cnt += s.binCount[a][k];
-                    rightArea[k] = cnt ? half_area(alo, ahi) : 0.f; rightCnt[k] = cnt;
-                }
-                for (int c = 0; c < 3; ++c) { alo[c] = 1e30f; ahi[c] = -1e30f; }
-                cnt = 0;
-                for (int k = 0; k < NB - 1; ++k) {
-                    for (int c = 0; c < 3; ++c) { alo[c] = fminf(alo[c], o2f(s.binLo[a][k][c])); ahi[c] = fmaxf(ahi[c], o2f(s.binHi[a][k][c])); }
-                    cnt += s.binCount[a][k];
-                    if (cnt == 0 || rightCnt[k + 1] == 0) continue;
-                    float cost = half_area(alo, ahi) * (float)cnt + rightArea[k + 1] * (float)rightCnt[k + 1];
-                    if (cost < bestCost) { bestCost = cost; bestAxis = a; bestBin = k; }
-                }
-            }
+            sah_best(s.binCount, s.binLo, s.binHi, ext, bestAxis, bestBin, bestCost);
             int leaf = 0;
             if (n <= (uint32_t)d.maxLeaf) {                   // leaves hold at most 3 triangles (unary count of a node slot)
                 float area = half_area(lo, hi);
@@ -225,13 +232,200 @@ __global__ void __launch_bounds__(1024) k_wide_split(Dev d, const uint32_t* __re
             }
             d.nodes2[kid] = c;
             if (c.count > 1) {
-                const int cls = c.count <= 64 ? 0 : (c.count <= 4096 ? 1 : 2);
-                d.nextList[cls][atomicAdd(&d.counters[2 + cls], 1u)] = kid;
+                const int cls = c.count <= 64 ? 0 : (c.count <= 4096 ? 1 : (c.count <= HUGE_MIN ? 2 : 3));
+                d.nextList[cls][atomicAdd(&d.counters[10 + cls], 1u)] = kid;
             }
             if (tid == 0) { d.nodes2[me].left = s.kids; d.nodes2[me].right = s.kids + 1; d.nodes2[me].count = 0; }
         }
         __syncthreads();
     }
+}
+
+// ---- nodes above HUGE_MIN triangles: the same steps as k_wide_split, spread over all SMs ----------------------------
+// One block per node would leave the first levels of a large scene on a handful of SMs (10 M triangles: 282 of
+// 338 ms in the top seven levels). Such nodes are cut into chunks of HUGE_CHUNK positions; each step is one launch
+// over all chunks of all huge nodes of the level, with per-node accumulators in global memory.
+constexpr uint32_t HUGE_CHUNK = 4096;
+constexpr uint32_t HUGE_THREADS = 256;
+
+struct HugeNode {
+    uint32_t id, first, count, chunk0, nChunks;
+    uint32_t lo[3], hi[3], cLo[3], cHi[3];   // ordered uints
+    uint32_t binCount[3][NB];
+    uint32_t binLo[3][NB][3], binHi[3][NB][3];
+    int axis, bin;
+    uint32_t totalLeft, doPartition, kids;
+};
+struct HugeChunk { uint32_t slot, begin, len; };
+
+__global__ void k_huge_init(Dev d, HugeNode* hn, uint32_t nHuge, const uint32_t* __restrict__ list) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nHuge) return;
+    HugeNode& h = hn[i];
+    h.id = list[i]; h.first = d.nodes2[h.id].first; h.count = d.nodes2[h.id].count;
+    for (int a = 0; a < 3; ++a) { h.lo[a] = h.cLo[a] = 0xffffffffu; h.hi[a] = h.cHi[a] = 0u; }
+    for (int k = 0; k < 3 * NB; ++k) {
+        (&h.binCount[0][0])[k] = 0u;
+        for (int c = 0; c < 3; ++c) { (&h.binLo[0][0][0])[k * 3 + c] = 0xffffffffu; (&h.binHi[0][0][0])[k * 3 + c] = 0u; }
+    }
+    h.axis = -1; h.bin = -1; h.totalLeft = 0; h.doPartition = 0; h.kids = 0;
+}
+
+__global__ void __launch_bounds__(HUGE_THREADS) k_huge_bounds(Dev d, HugeNode* hn, const HugeChunk* __restrict__ chunks) {
+    const HugeChunk ck = chunks[blockIdx.x];
+    HugeNode& h = hn[ck.slot];
+    const uint32_t* idx = d.idx + h.first + ck.begin;
+    uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u}, clo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, chi[3] = {0u, 0u, 0u};
+    for (uint32_t k = threadIdx.x; k < ck.len; k += HUGE_THREADS) {
+        const WideBox b = d.box[idx[k]];
+        for (int a = 0; a < 3; ++a) {
+            uint32_t oc = f2o(0.5f * (b.lo[a] + b.hi[a]));
+            lo[a] = min(lo[a], f2o(b.lo[a])); hi[a] = max(hi[a], f2o(b.hi[a]));
+            clo[a] = min(clo[a], oc); chi[a] = max(chi[a], oc);
+        }
+    }
+    __shared__ uint32_t sLo[3], sHi[3], sCLo[3], sCHi[3];
+    if (threadIdx.x < 3) { sLo[threadIdx.x] = sCLo[threadIdx.x] = 0xffffffffu; sHi[threadIdx.x] = sCHi[threadIdx.x] = 0u; }
+    __syncthreads();
+    for (int a = 0; a < 3; ++a) {
+        uint32_t l = __reduce_min_sync(0xffffffffu, lo[a]), hh = __reduce_max_sync(0xffffffffu, hi[a]);
+        uint32_t cl = __reduce_min_sync(0xffffffffu, clo[a]), ch = __reduce_max_sync(0xffffffffu, chi[a]);
+        if ((threadIdx.x & 31u) == 0) { atomicMin(&sLo[a], l); atomicMax(&sHi[a], hh); atomicMin(&sCLo[a], cl); atomicMax(&sCHi[a], ch); }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        atomicMin(&h.lo[threadIdx.x], sLo[threadIdx.x]); atomicMax(&h.hi[threadIdx.x], sHi[threadIdx.x]);
+        atomicMin(&h.cLo[threadIdx.x], sCLo[threadIdx.x]); atomicMax(&h.cHi[threadIdx.x], sCHi[threadIdx.x]);
+    }
+}
+
+__global__ void __launch_bounds__(HUGE_THREADS) k_huge_bins(Dev d, HugeNode* hn, const HugeChunk* __restrict__ chunks) {
+    __shared__ uint32_t binCount[3][NB], binLo[3][NB][3], binHi[3][NB][3];
+    const HugeChunk ck = chunks[blockIdx.x];
+    HugeNode& h = hn[ck.slot];
+    const uint32_t* idx = d.idx + h.first + ck.begin;
+    for (uint32_t i = threadIdx.x; i < 3 * NB; i += HUGE_THREADS) {
+        (&binCount[0][0])[i] = 0u;
+        for (int c = 0; c < 3; ++c) { (&binLo[0][0][0])[i * 3 + c] = 0xffffffffu; (&binHi[0][0][0])[i * 3 + c] = 0u; }
+    }
+    float cLo[3], ext[3], scale[3];
+    for (int a = 0; a < 3; ++a) { cLo[a] = o2f(h.cLo[a]); ext[a] = o2f(h.cHi[a]) - cLo[a]; scale[a] = (float)NB / ext[a]; }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < ck.len; k += HUGE_THREADS) {
+        const WideBox b = d.box[idx[k]];
+        for (int a = 0; a < 3; ++a) {
+            if (!(ext[a] > 0.f)) continue;
+            int bin = bin_of(0.5f * (b.lo[a] + b.hi[a]), cLo[a], scale[a]);
+            atomicAdd(&binCount[a][bin], 1u);
+            for (int c = 0; c < 3; ++c) { atomicMin(&binLo[a][bin][c], f2o(b.lo[c])); atomicMax(&binHi[a][bin][c], f2o(b.hi[c])); }
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 3 * NB; i += HUGE_THREADS) {
+        uint32_t cnt = (&binCount[0][0])[i];
+        if (!cnt) continue;
+        atomicAdd(&(&h.binCount[0][0])[i], cnt);
+        for (int c = 0; c < 3; ++c) { atomicMin(&(&h.binLo[0][0][0])[i * 3 + c], (&binLo[0][0][0])[i * 3 + c]); atomicMax(&(&h.binHi[0][0][0])[i * 3 + c], (&binHi[0][0][0])[i * 3 + c]); }
+    }
+}
+
+__global__ void k_huge_sah(Dev d, HugeNode* hn, uint32_t nHuge) {       // huge nodes are never leaves (count > maxLeaf)
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nHuge) return;
+    HugeNode& h = hn[i];
+    float ext[3];
+    for (int a = 0; a < 3; ++a) { d.nodes2[h.id].lo[a] = o2f(h.lo[a]); d.nodes2[h.id].hi[a] = o2f(h.hi[a]); ext[a] = o2f(h.cHi[a]) - o2f(h.cLo[a]); }
+    int bestAxis = -1, bestBin = -1;
+    float bestCost = 1e30f;
+    sah_best(h.binCount, h.binLo, h.binHi, ext, bestAxis, bestBin, bestCost);
+    h.axis = bestAxis; h.bin = bestBin;
+    h.kids = atomicAdd(&d.counters[1], 2u);
+}
+
+__device__ __forceinline__ bool huge_is_left(const Dev& d, const HugeNode& h, uint32_t p, float cLo, float scale) {
+    const WideBox b = d.box[p];
+    return bin_of(0.5f * (b.lo[h.axis] + b.hi[h.axis]), cLo, scale) <= h.bin;
+}
+
+__global__ void __launch_bounds__(HUGE_THREADS) k_huge_count(Dev d, HugeNode* hn, const HugeChunk* __restrict__ chunks, uint32_t* chunkLeft) {
+    const HugeChunk ck = chunks[blockIdx.x];
+    const HugeNode& h = hn[ck.slot];
+    uint32_t nLeft = 0;
+    if (h.axis >= 0) {
+        const float cLo = o2f(h.cLo[h.axis]), scale = (float)NB / (o2f(h.cHi[h.axis]) - cLo);
+        const uint32_t* idx = d.idx + h.first + ck.begin;
+        for (uint32_t k = threadIdx.x; k < ck.len; k += HUGE_THREADS) nLeft += huge_is_left(d, h, idx[k], cLo, scale) ? 1u : 0u;
+    }
+    __shared__ uint32_t total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    nLeft = __reduce_add_sync(0xffffffffu, nLeft);
+    if ((threadIdx.x & 31u) == 0 && nLeft) atomicAdd(&total, nLeft);
+    __syncthreads();
+    if (threadIdx.x == 0) chunkLeft[blockIdx.x] = total;
+}
+
+// per node: exclusive prefix of its chunks' left counts (in place) and the decision whether the partition is proper
+__global__ void k_huge_scan(HugeNode* hn, uint32_t nHuge, uint32_t* chunkLeft) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nHuge) return;
+    HugeNode& h = hn[i];
+    uint32_t run = 0;
+    for (uint32_t c = h.chunk0; c < h.chunk0 + h.nChunks; ++c) { uint32_t v = chunkLeft[c]; chunkLeft[c] = run; run += v; }
+    h.totalLeft = run;
+    h.doPartition = (h.axis >= 0 && run != 0 && run != h.count) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(HUGE_THREADS) k_huge_scatter(Dev d, HugeNode* hn, const HugeChunk* __restrict__ chunks, const uint32_t* __restrict__ chunkLeft) {
+    __shared__ SplitShared s;
+    const HugeChunk ck = chunks[blockIdx.x];
+    const HugeNode& h = hn[ck.slot];
+    if (!h.doPartition) return;
+    const float cLo = o2f(h.cLo[h.axis]), scale = (float)NB / (o2f(h.cHi[h.axis]) - cLo);
+    const uint32_t* idx = d.idx + h.first + ck.begin;
+    uint32_t* tmp = d.idxTmp + h.first;
+    uint32_t runL = chunkLeft[blockIdx.x], runR = ck.begin - runL;           // lefts / rights of the node before this chunk
+    for (uint32_t base = 0; base < ck.len; base += HUGE_THREADS) {
+        const uint32_t k = base + threadIdx.x;
+        uint32_t p = 0; bool isLeft = false;
+        if (k < ck.len) { p = idx[k]; isLeft = huge_is_left(d, h, p, cLo, scale); }
+        uint32_t tot;
+        uint32_t ex = block_exclusive(s, isLeft, tot);
+        if (k < ck.len) tmp[isLeft ? runL + ex : h.totalLeft + runR + (threadIdx.x - ex)] = p;
+        runL += tot; runR += min(HUGE_THREADS, ck.len - base) - tot;
+    }
+}
+
+__global__ void __launch_bounds__(HUGE_THREADS) k_huge_copyback(Dev d, HugeNode* hn, const HugeChunk* __restrict__ chunks) {
+    const HugeChunk ck = chunks[blockIdx.x];
+    const HugeNode& h = hn[ck.slot];
+    if (!h.doPartition) return;
+    const uint32_t o = h.first + ck.begin;
+    for (uint32_t k = threadIdx.x; k < ck.len; k += HUGE_THREADS) d.idx[o + k] = d.idxTmp[o + k];
+}
+
+__global__ void k_huge_children(Dev d, HugeNode* hn, uint32_t nHuge) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 2 * nHuge) return;
+    const HugeNode& h = hn[i >> 1];
+    const uint32_t side = i & 1u;
+    const uint32_t mid = h.doPartition ? h.totalLeft : h.count / 2;
+    Node2 c;
+    for (int a = 0; a < 3; ++a) { c.lo[a] = 0.f; c.hi[a] = 0.f; }
+    c.left = c.right = 0;
+    c.first = side ? h.first + mid : h.first;
+    c.count = side ? h.count - mid : mid;
+    const uint32_t kid = h.kids + side;
+    if (c.count == 1) {
+        const WideBox b = d.box[d.idx[c.first]];
+        for (int a = 0; a < 3; ++a) { c.lo[a] = b.lo[a]; c.hi[a] = b.hi[a]; }
+    }
+    d.nodes2[kid] = c;
+    if (c.count > 1) {
+        const int cls = c.count <= 64 ? 0 : (c.count <= 4096 ? 1 : (c.count <= HUGE_MIN ? 2 : 3));
+        d.nextList[cls][atomicAdd(&d.counters[10 + cls], 1u)] = kid;
+    }
+    if (side == 0) { d.nodes2[h.id].left = h.kids; d.nodes2[h.id].right = h.kids + 1; d.nodes2[h.id].count = 0; }
 }
 
 __device__ __forceinline__ uint8_t exponent_for(float extent) {     // smallest e with 2^e * 255 >= extent, biased
@@ -360,19 +554,22 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     d.maxLeaf = 3; d.travCost = 1.0f;
     if (const char* e = std::getenv("B200PT_BVH_LEAF")) d.maxLeaf = std::max(1, std::min(3, std::atoi(e)));
     if (const char* e = std::getenv("B200PT_BVH_CT")) d.travCost = (float)std::atof(e);
-    UpNode* up; uint32_t *leafOf, *objXform, *instObject, *instTri, *lists[6];
+    UpNode* up; uint32_t *leafOf, *objXform, *instObject, *instTri, *lists[8], *chunkLeft;
     EmitItem* emit[2];
+    HugeNode* hugeNodes; HugeChunk* hugeChunks;
     // One arena for all scratch (cudaMalloc / cudaFree of two dozen buffers cost as much as the kernels for a
     // 265 k-triangle scene); kept in `cache` between builds while it is small enough to be worth holding on to.
     WideBuildCache local;
     WideBuildCache& arena = cache ? *cache : local;
     size_t need = 0;
     auto plan = [&](size_t count, size_t elem) { size_t off = need; need += (std::max<size_t>(count, 1) * elem + 255) & ~(size_t)255; return off; };
+    const size_t maxHuge = n / HUGE_MIN + 1, maxChunks = n / HUGE_CHUNK + maxHuge + 1;
     const size_t oUp = plan(host.up.size(), sizeof(UpNode)), oLeaf = plan(host.leafOf.size(), 4), oObjX = plan(host.objXform.size(), 4),
                  oInstO = plan(n, 4), oInstT = plan(n, 4), oPrim = plan(n, sizeof(PrimRecord)), oShade = plan(n, sizeof(ShadeRecord)),
                  oUv = plan(n, sizeof(UvRecord)), oBox = plan(n, sizeof(WideBox)), oIdx = plan(n, 4), oIdxT = plan(n, 4), oValid = plan(n, 1),
-                 oNodes2 = plan(2 * n + 1, sizeof(Node2)), oCnt = plan(16, 4), oEmit0 = plan(n + 1, sizeof(EmitItem)), oEmit1 = plan(n + 1, sizeof(EmitItem));
-    size_t oList[6];
+                 oNodes2 = plan(2 * n + 1, sizeof(Node2)), oCnt = plan(16, 4), oEmit0 = plan(n + 1, sizeof(EmitItem)), oEmit1 = plan(n + 1, sizeof(EmitItem)),
+                 oHuge = plan(maxHuge, sizeof(HugeNode)), oChunks = plan(maxChunks, sizeof(HugeChunk)), oChunkLeft = plan(maxChunks, 4);
+    size_t oList[8];
     for (auto& o : oList) o = plan(n / 2 + 1, 4);              // a listed node holds at least 2 triangles
     if (arena.bytes < need) {
         if (arena.p) cudaFree(arena.p);
@@ -387,7 +584,8 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     d.idx = (uint32_t*)(base + oIdx); d.idxTmp = (uint32_t*)(base + oIdxT); d.valid = (uint8_t*)(base + oValid);
     d.nodes2 = (Node2*)(base + oNodes2); d.counters = (uint32_t*)(base + oCnt);
     emit[0] = (EmitItem*)(base + oEmit0); emit[1] = (EmitItem*)(base + oEmit1);
-    for (int i = 0; i < 6; ++i) lists[i] = (uint32_t*)(base + oList[i]);
+    hugeNodes = (HugeNode*)(base + oHuge); hugeChunks = (HugeChunk*)(base + oChunks); chunkLeft = (uint32_t*)(base + oChunkLeft);
+    for (int i = 0; i < 8; ++i) lists[i] = (uint32_t*)(base + oList[i]);
     // the four result buffers: the caller's previous ones are written again when they are large enough
     struct Fresh { std::vector<void*> p; ~Fresh() { for (void* q : p) cudaFree(q); } } fresh;      // freed unless handed over
     const size_t capNodes = (n + 1) * sizeof(Bvh8Node), capPrim = std::max<size_t>(n, 1) * sizeof(PrimRecord),
@@ -442,12 +640,14 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
         root.first = 0; root.count = nValid;
         WBC(cudaMemcpyAsync(d.nodes2, &root, sizeof root, cudaMemcpyHostToDevice, st));
         uint32_t init[16] = {nValid, 1, 0, 0, 0, 1, 0, 0, 0};
-        const int cls0 = nValid <= 64 ? 0 : (nValid <= 4096 ? 1 : 2);
-        init[2 + cls0] = 1;
+        const int cls0 = nValid <= 64 ? 0 : (nValid <= 4096 ? 1 : (nValid <= HUGE_MIN ? 2 : 3));
+        init[10 + cls0] = 1;
         uint32_t zeroId = 0;
         WBC(cudaMemcpyAsync(lists[cls0], &zeroId, 4, cudaMemcpyHostToDevice, st));
         WBC(cudaMemcpyAsync(d.counters, init, 64, cudaMemcpyHostToDevice, st));
         const unsigned threadsOf[3] = {32, 256, 1024};
+        std::vector<HugeNode> hHuge;
+        std::vector<HugeChunk> hChunks;
         int cur = 0;
         const bool timing = std::getenv("B200PT_BUILD_TIMING") != nullptr;
         auto tLevel = std::chrono::steady_clock::now();
@@ -456,18 +656,43 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
             WBC(cudaStreamSynchronize(st));
             if (timing) {
                 auto now = std::chrono::steady_clock::now();
-                fprintf(stderr, "[wide] level %d done in %.3f ms; next lists %u / %u / %u nodes\n", level - 1,
-                        std::chrono::duration<double, std::milli>(now - tLevel).count(), h[2], h[3], h[4]);
+                fprintf(stderr, "[wide] level %d done in %.3f ms; next lists %u / %u / %u / %u nodes\n", level - 1,
+                        std::chrono::duration<double, std::milli>(now - tLevel).count(), h[10], h[11], h[12], h[13]);
                 tLevel = now;
             }
-            if (h[2] + h[3] + h[4] == 0) break;
+            if (h[10] + h[11] + h[12] + h[13] == 0) break;
             if (level > 4096) return "wide BVH device build: binary tree does not terminate";
-            const uint32_t* curList[3] = {lists[cur * 3], lists[cur * 3 + 1], lists[cur * 3 + 2]};
+            const uint32_t* curList[4] = {lists[cur * 4], lists[cur * 4 + 1], lists[cur * 4 + 2], lists[cur * 4 + 3]};
             cur ^= 1;
-            for (int c = 0; c < 3; ++c) d.nextList[c] = lists[cur * 3 + c];
-            WBC(cudaMemsetAsync(d.counters + 2, 0, 12, st));
+            for (int c = 0; c < 4; ++c) d.nextList[c] = lists[cur * 4 + c];
+            WBC(cudaMemsetAsync(d.counters + 10, 0, 16, st));
             for (int c = 0; c < 3; ++c)
-                if (h[2 + c]) k_wide_split<<<std::min<uint32_t>(h[2 + c], 1u << 20), threadsOf[c], 0, st>>>(d, curList[c], h[2 + c]);
+                if (h[10 + c]) k_wide_split<<<std::min<uint32_t>(h[10 + c], 1u << 20), threadsOf[c], 0, st>>>(d, curList[c], h[10 + c]);
+            if (const uint32_t nHuge = h[13]) {
+                k_huge_init<<<(nHuge + 63) / 64, 64, 0, st>>>(d, hugeNodes, nHuge, curList[3]);
+                hHuge.resize(nHuge);
+                WBC(cudaMemcpyAsync(hHuge.data(), hugeNodes, nHuge * sizeof(HugeNode), cudaMemcpyDeviceToHost, st));
+                WBC(cudaStreamSynchronize(st));
+                hChunks.clear();
+                for (uint32_t i = 0; i < nHuge; ++i) {
+                    hHuge[i].chunk0 = (uint32_t)hChunks.size();
+                    hHuge[i].nChunks = (hHuge[i].count + HUGE_CHUNK - 1) / HUGE_CHUNK;
+                    for (uint32_t b = 0; b < hHuge[i].count; b += HUGE_CHUNK) hChunks.push_back({i, b, std::min(HUGE_CHUNK, hHuge[i].count - b)});
+                }
+                const uint32_t nChunks = (uint32_t)hChunks.size();
+                if (nHuge > maxHuge || nChunks > maxChunks) return "wide BVH device build: chunk table overflow";
+                WBC(cudaMemcpyAsync(hugeNodes, hHuge.data(), nHuge * sizeof(HugeNode), cudaMemcpyHostToDevice, st));
+                WBC(cudaMemcpyAsync(hugeChunks, hChunks.data(), nChunks * sizeof(HugeChunk), cudaMemcpyHostToDevice, st));
+                const unsigned gN = (nHuge + 63) / 64;
+                k_huge_bounds<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks);
+                k_huge_bins<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks);
+                k_huge_sah<<<gN, 64, 0, st>>>(d, hugeNodes, nHuge);
+                k_huge_count<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks, chunkLeft);
+                k_huge_scan<<<gN, 64, 0, st>>>(hugeNodes, nHuge, chunkLeft);
+                k_huge_scatter<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks, chunkLeft);
+                k_huge_copyback<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks);
+                k_huge_children<<<(2 * nHuge + 63) / 64, 64, 0, st>>>(d, hugeNodes, nHuge);
+            }
             WBC(cudaGetLastError());
         }
         // collapse + emit, level by level from the root (wide node 0 <- binary node 0)
