@@ -107,7 +107,7 @@ struct Builder2 {
     std::vector<Node2> nodes;
     static const int NB = 16;
     int maxLeaf = 3;            // triangles per leaf slot, 1..3 (tuning: B200PT_BVH_LEAF)
-    float travCost = 1.0f;      // cost of one more box level relative to one triangle test (tuning: B200PT_BVH_CT)
+    float travCost = 0.5f;      // cost of one more box level relative to one triangle test (tuning: B200PT_BVH_CT)
 
     explicit Builder2(const std::vector<Box>& b) : boxes(b) {
         size_t n = b.size();
