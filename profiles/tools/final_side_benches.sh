@@ -1,6 +1,6 @@
 #!/bin/bash
 # the configurations beside the headline: C1 Cornell 512x512, C3 stand-in, soup 10 M (host and GPU BVH2 build)
-for w in ${SIDE_WORKLOADS:-"cornell --width 512 --height 512" "statue" "statue --gpu-bvh" "soup --bounce-limit 2 --gpu-bvh"}; do
+for w in "cornell --width 512 --height 512" "statue --gpu-bvh" "soup --bounce-limit 2 --gpu-bvh"; do
   tag=$(echo $w | tr -d ' -')
   timeout 900 python bench.py --workload $w --steps 4 --warmup 3 > gpurun_out/side_$tag.log 2> gpurun_out/side_$tag.err || { echo "$w FAILED"; tail -3 gpurun_out/side_$tag.err; continue; }
   python - "$w" gpurun_out/side_$tag.log <<PY
