@@ -52,6 +52,28 @@ def build_host(force=False, verbose=False):
     return HOST_LIB
 
 
+HEADLESS_BIN = os.path.join(HERE, "b200pt_headless")
+HEADLESS_SOURCES = ["headless_main.cpp", "headless_engine.cpp"]
+
+
+def build_headless(force=False, verbose=False):
+    """b200pt_headless: the C++ host program above the C ABI (host/headless_engine.h), linked against the two
+    libraries next to it (rpath $ORIGIN). Needs libb200pt.so and libb200pt_host.so to exist."""
+    srcs = [os.path.join(HOST_DIR, s) for s in HEADLESS_SOURCES]
+    deps = srcs + [os.path.join(HOST_DIR, "headless_engine.h"), os.path.join(HOST_DIR, "scene_builder.h"),
+                   os.path.join(HERE, "..", "include", "b200pt.h"), LIB, HOST_LIB]
+    if not force and os.path.exists(HEADLESS_BIN) and all(os.path.getmtime(d) <= os.path.getmtime(HEADLESS_BIN) for d in deps):
+        return HEADLESS_BIN
+    cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-o", HEADLESS_BIN] + srcs + \
+          ["-L" + HERE, "-lb200pt", "-lb200pt_host", "-Wl,-rpath,$ORIGIN"]
+    if verbose:
+        print(" ".join(cmd))
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + r.stdout + r.stderr)
+    return HEADLESS_BIN
+
+
 def build(force=False, verbose=False, extra=(), out=None):
     """out: alternative output path (A/B variants with -D flags in `extra`; loaded with B200PT_LIB=<path>)."""
     build_host(force=force, verbose=verbose)
@@ -72,3 +94,4 @@ def build(force=False, verbose=False, extra=(), out=None):
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose=True, extra=["-Xptxas", "-v"] if "--ptxas" in sys.argv else ()))
+    print(build_headless(force="--force" in sys.argv, verbose=True))
