@@ -69,8 +69,19 @@ PT_HD NodeWords load_node(const Bvh8Node* nodes, uint32_t idx) {
 }
 // Byte k of `word` dropped into the mantissa of 1.0f (bits 8..15): 1 + q * 2^-15, exact, one PRMT
 // on the device — no integer->float conversion (quarter-rate pipe) and no subtraction.
+#ifndef PT_UNIT_FROM_CONSTANT
+#define PT_UNIT_FROM_CONSTANT 1
+#endif
+#if defined(__CUDACC__) && PT_UNIT_FROM_CONSTANT
+// The bits of 1.0f read from constant memory: with BOTH PRMT inputs compile-time constants the compiler keeps 0x3F800000
+// as the immediate and re-materialises the four byte selectors into registers around every use (20 extra moves per
+// node); with this operand coming from the constant bank the selector is the immediate.
+static __constant__ uint32_t c_unit_float_bits = 0x3F800000u;
+#endif
 PT_HD float byte_as_unit_float(uint32_t word, int k) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && PT_UNIT_FROM_CONSTANT
+    return __uint_as_float(__byte_perm(word, c_unit_float_bits, 0x7604u + ((uint32_t)k << 4)));
+#elif defined(__CUDA_ARCH__)
     return __uint_as_float(__byte_perm(word, 0x3F800000u, 0x7604u + ((uint32_t)k << 4)));
 #else
     return as_float(0x3F800000u | (((word >> (8 * k)) & 0xffu) << 8));
@@ -279,13 +290,30 @@ PT_HD void trav_begin(Trav& t, const Ray& ray) {
 struct PrivateStack {
     uint32_t base[PT_BVH8_STACK], bits[PT_BVH8_STACK];
     PT_HD void put(int i, uint32_t b, uint32_t v) { base[i] = b; bits[i] = v; }
-    PT_HD void get(int i, uint32_t& b, uint32_t& v) const { b = base[i]; v = bits[i]; }
+    PT_HD void get(int i, uint32_t& b, uint32_t& v) { b = base[i]; v = bits[i]; }
+};
+// The same stack with its top entry held in two registers: a pop hands out registers and refills them with a load
+// nobody waits for until the next pop or push (the persistent kernels' pop was a load-to-use stall for the whole
+// converged warp, profiles/r01/k_extend_final_by_line.txt: pt_traverse.h trav_pop 7.4 % of the stall samples), and an
+// entry that is pushed and popped again before anything displaces it never goes through memory.
+// Invariant: with sp entries on the stack, entry sp-1 is in (topB, topV) and entries 0..sp-2 are in memory.
+struct TopCachedStack {
+    uint32_t base[PT_BVH8_STACK], bits[PT_BVH8_STACK];
+    uint32_t topB, topV;
+    PT_HD void put(int i, uint32_t b, uint32_t v) {
+        if (i > 0) { base[i - 1] = topB; bits[i - 1] = topV; }
+        topB = b; topV = v;
+    }
+    PT_HD void get(int i, uint32_t& b, uint32_t& v) {
+        b = topB; v = topV;
+        if (i > 0) { topB = base[i - 1]; topV = bits[i - 1]; }
+    }
 };
 PT_HD bool trav_has_node(const Trav& t) { return (t.gBits & 0xff000000u) != 0; }
 PT_HD bool trav_has_tri(const Trav& t) { return t.tBits != 0; }
 // Nothing in hand: take the next group from the stack. Returns false when the walk is over.
 template <class Stack>
-PT_HD bool trav_pop(Trav& t, const Stack& stack) {
+PT_HD bool trav_pop(Trav& t, Stack& stack) {
     if (t.sp == 0) return false;
     t.sp--;
     uint32_t b, bits;

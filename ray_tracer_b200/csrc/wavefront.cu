@@ -138,6 +138,9 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     return got;
 }
 
+#ifndef PT_STACK_TOS
+#define PT_STACK_TOS 0        /* top of the per-lane stack in registers (TopCachedStack, pt_traverse.h) */
+#endif
 #ifndef PT_SPLIT_STACK
 #define PT_SPLIT_STACK 0      /* A/B on B200: shared-memory stack 250.2, local-memory stack 252.3 Mpaths/s: local (L1-resident) wins */
 #endif
@@ -149,7 +152,7 @@ struct SplitStack {
         if (i < PT_BVH8_SHARED_STACK) sh[i * WF_THREADS] = make_uint2(b, v);
         else { base[i - PT_BVH8_SHARED_STACK] = b; bits[i - PT_BVH8_SHARED_STACK] = v; }
     }
-    __device__ __forceinline__ void get(int i, uint32_t& b, uint32_t& v) const {
+    __device__ __forceinline__ void get(int i, uint32_t& b, uint32_t& v) {
         if (i < PT_BVH8_SHARED_STACK) { uint2 e = sh[i * WF_THREADS]; b = e.x; v = e.y; }
         else { b = base[i - PT_BVH8_SHARED_STACK]; v = bits[i - PT_BVH8_SHARED_STACK]; }
     }
@@ -158,6 +161,8 @@ struct SplitStack {
     __shared__ uint2 name##_shared[PT_BVH8_SHARED_STACK * WF_THREADS];      \
     SplitStack name;                                                        \
     name.sh = name##_shared + threadIdx.x
+#elif PT_STACK_TOS
+#define PT_DECLARE_STACK(name) TopCachedStack name
 #else
 #define PT_DECLARE_STACK(name) PrivateStack name
 #endif
