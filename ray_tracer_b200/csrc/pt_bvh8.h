@@ -114,7 +114,9 @@ struct WideScene {
 // below PT_BVH8_POSTPONE_LIMIT entries: LIMIT + 1 + MAX_DEPTH < STACK.
 #define PT_BVH8_STACK 48
 #define PT_BVH8_MAX_DEPTH 30
+#ifndef PT_BVH8_POSTPONE_LIMIT
 #define PT_BVH8_POSTPONE_LIMIT 16
+#endif
 #define PT_BVH8_SHARED_STACK 20     /* entries per ray kept in shared memory by the persistent kernels */
 
 }  // namespace pt

@@ -46,6 +46,7 @@ struct WfParams {
     uint32_t nSlots, nPaths;        // nPaths = nSlots * rows * W
     uint32_t triVote32;             // persistent kernels: run a triangle step when >= triVote32/32 of the busy lanes hold triangles
     uint32_t fetchMinIdle;          // ... refill a warp once this many lanes are idle
+    uint32_t triVoteOccl32, fetchMinIdleOccl;   // the same two for k_occlude (any-hit walks: a hit ends the ray)
     uint32_t sharePrimary;          // bounce 0: the hit of path p is stored at p % (rows * W) (one primary ray per pixel)
     uint32_t connectAfterExtend;    // connect of bounce j runs after extend of bounce j+1 (A.hit is the NEXT hit)
     uint32_t useTextures;           // texture extension on (option "textures"); 0 = the HEAD shader's behaviour

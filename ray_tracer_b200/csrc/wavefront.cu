@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
         const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
         const unsigned votes = warp_votes(busy, hasTri, canNode);
         const unsigned nBusy = votes & 0xffu, nTri = (votes >> 8) & 0xffu, nNode = votes >> 16;
-        if (!feed.exhausted && 32u - nBusy >= P.fetchMinIdle) {
+        if (!feed.exhausted && 32u - nBusy >= P.fetchMinIdleOccl) {
             uint32_t qi;
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             continue;
         }
         if (nBusy == 0u) break;
-        if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
+        if (nNode == 0u || 32u * nTri >= P.triVoteOccl32 * nBusy) {
             if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
                 connect_job_occluded(A, job);
                 busy = false;
@@ -641,6 +641,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
     P.useTextures = (c->useTextures && c->dTexTable.p) ? 1u : 0u;
     P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
+    P.triVoteOccl32 = (uint32_t)c->triVoteOccl32; P.fetchMinIdleOccl = (uint32_t)c->fetchMinIdleOccl;
     uint32_t nB = pc.params.bounceLimit + 1;
     uint32_t* qCount = (uint32_t*)w->dCounts.p;
     uint32_t* sCount = qCount + w->countSlots;
