@@ -170,7 +170,14 @@ struct ObjRayCache { uint32_t xform; Ray r; };
 
 PT_HD const Ray& object_ray(ObjRayCache& c, const Xform* xforms, uint32_t xformId, const Ray& world) {
     if (c.xform != xformId) {
+#if defined(__CUDA_ARCH__)
+        float Minv[16];                       // four 16-byte loads (read element by element through a float* they were 12 scalar loads)
+        const float4* q = reinterpret_cast<const float4*>(xforms[xformId].Minv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { const float4 col = __ldg(q + j); Minv[4 * j] = col.x; Minv[4 * j + 1] = col.y; Minv[4 * j + 2] = col.z; Minv[4 * j + 3] = col.w; }
+#else
         const float* Minv = xforms[xformId].Minv;
+#endif
         c.r.d = mul_dir(Minv, world.d);       // raytrace.comp:292 (direction not renormalised: t stays world-parametric)
         c.r.o = mul_point(Minv, world.o);     // raytrace.comp:293
         c.xform = xformId;

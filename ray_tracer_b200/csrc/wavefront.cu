@@ -138,6 +138,10 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     return got;
 }
 
+#ifndef PT_STREAM_PREFETCH
+#define PT_STREAM_PREFETCH 0  /* grid-stride kernels request the next round's path state into L2 */
+#endif
+static __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 #ifndef PT_STACK_TOS
 #define PT_STACK_TOS 0        /* top of the per-lane stack in registers (TopCachedStack, pt_traverse.h) */
 #endif
@@ -262,9 +266,25 @@ __global__ void __launch_bounds__(SHADE_THREADS, PT_SHADE_MIN_BLOCKS) k_shade(co
                                                          uint32_t j) {
     const uint32_t n = *qCount;
     uint32_t* const counters[2] = {nextCount, shadowCount};
+#if PT_STREAM_PREFETCH
+    // The path state of the NEXT round of this thread is requested into L2 while this round is shaded (the index of
+    // the round after that is fetched at the same time): the kernel is bound by the latency of its dependent loads
+    // (path state -> shading record -> material), not by bandwidth (ncu: 55 % of DRAM peak, long-scoreboard stalls).
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t pNext = 0;
+    { const uint32_t i1 = blockIdx.x * blockDim.x + threadIdx.x + stride; if (i1 < n) pNext = queue[i1]; }
+#endif
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {      // block-uniform trip count
         const uint32_t i = base + threadIdx.x;
         uint32_t flags = 0, p = 0;
+#if PT_STREAM_PREFETCH
+        if (i + stride < n) {
+            const uint32_t q = pNext;
+            prefetch_l2(&A.rayO[q]); prefetch_l2(&A.rayD[q]); prefetch_l2(&A.total[q]); prefetch_l2(&A.atten[q]); prefetch_l2(&A.direct[q]);
+            if (!(j == 0 && P.sharePrimary)) prefetch_l2(&A.hit[q]);
+        }
+        if (i + 2u * stride < n) pNext = queue[i + 2u * stride];
+#endif
         if (i < n) { p = queue[i]; flags = stage_shade(P, sc, A, p, j); }
         const bool go = (flags & PT_SHADE_CONTINUE) != 0;
         const bool pred[2] = {go, go && (flags & PT_SHADE_CONNECT) != 0};
@@ -284,8 +304,17 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
                                                              uint32_t* jobQueue, uint32_t* jobCount) {
     uint32_t n = *sCount;
     uint32_t nRound = (n + 31u) & ~31u;           // whole warps stay together for the ballot
+#if PT_STREAM_PREFETCH
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t pNext = 0;
+    { const uint32_t i1 = blockIdx.x * blockDim.x + threadIdx.x + stride; if (i1 < n) pNext = queue[i1]; }
+#endif
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nRound; i += gridDim.x * blockDim.x) {
         uint32_t jobs = 0, p = 0;
+#if PT_STREAM_PREFETCH
+        if (i + stride < n) { const uint32_t q = pNext; prefetch_l2(&A.qA[q]); prefetch_l2(&A.qL[q]); prefetch_l2(&A.qO[q]); prefetch_l2(&A.hit[q]); }
+        if (i + 2u * stride < n) pNext = queue[i + 2u * stride];
+#endif
         if (i < n) { p = queue[i]; jobs = stage_connect_prep(P, sc, A, p); }
         uint32_t s0 = warp_push(jobCount, jobs != 0u);
         if (jobs) jobQueue[s0] = p;
