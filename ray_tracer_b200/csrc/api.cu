@@ -439,6 +439,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "occl_tri_vote") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "occl_tri_vote must be 1..32"); c->triVoteOccl32 = (int)v; return 0; }
     if (k == "occl_fetch_idle") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "occl_fetch_idle must be 1..32"); c->fetchMinIdleOccl = (int)v; return 0; }
     if (k == "share_primary") { c->sharePrimary = v != 0; return 0; }
+    if (k == "overlap_connect") { if (v < 0 || v > 2) return fail(c, B200PT_ERR_ARG, "overlap_connect must be 0..2"); c->overlapConnect = (int)v; return 0; }
     if (k == "wide_build") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "wide_build must be 0 (host) or 1 (device)"); c->wideBuild = (int)v; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
@@ -455,6 +456,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "occl_tri_vote") { *v = c->triVoteOccl32; return 0; }
     if (k == "occl_fetch_idle") { *v = c->fetchMinIdleOccl; return 0; }
     if (k == "share_primary") { *v = c->sharePrimary; return 0; }
+    if (k == "overlap_connect") { *v = c->overlapConnect; return 0; }
     if (k == "wide_build") { *v = c->wideBuild; return 0; }
     if (k == "last_scene_build_us") { *v = (int64_t)(c->lastSceneBuildMs * 1000.0); return 0; }      // read-only
     if (k == "last_wide_device_us") { *v = (int64_t)(c->lastWideDeviceMs * 1000.0); return 0; }      // read-only

@@ -44,6 +44,9 @@ struct WavefrontState {
     size_t eventsUsed = 0;
     double stageMs[PT_N_STAGES] = {0};
     uint64_t stageLaunches[PT_N_STAGES] = {0};
+    // second stream for the connect chain of a bounce (option overlap_connect)
+    cudaStream_t sideStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
 };
 
 enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4, ST_OCCLUDE = 5, ST_FINISH = 6 };
@@ -603,6 +606,9 @@ void wavefront_destroy(b200pt_ctx* c) {
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
+    if (w->evFork) cudaEventDestroy(w->evFork);
+    if (w->evJoin) cudaEventDestroy(w->evJoin);
+    if (w->sideStream) cudaStreamDestroy(w->sideStream);
     delete w;
     c->wf = nullptr;
 }
@@ -707,7 +713,17 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             k_generate<<<grid, WF_THREADS, 0, c->stream>>>(P, w->arrays, qa, qCount, primaryCount);
             // Order per bounce: shade(j), extend(j+1), connect(j). Connect comes AFTER the next extension so that NEE rays of
             // paths whose next ray escapes (their direct light is dropped, raytrace.comp:531-534) are not traced at all.
-            P.connectAfterExtend = 1u;
+            // With ONE frame in the batch the launches are small and the drain phase of every persistent launch (its last
+            // rays run in partly filled warps) is a large share of it: the connect chain of bounce j then runs on a second
+            // stream beside extend(j+1) — one's drain overlaps the other's work — and gives up dropping the NEE rays of
+            // escaping paths, which needs that extension's result (same image: trace() discards their direct light).
+            const bool overlap = !c->profileStages && (c->overlapConnect == 2 || (c->overlapConnect == 1 && P.nSlots == 1));
+            if (overlap && !w->sideStream) {
+                WCU(cudaStreamCreateWithFlags(&w->sideStream, cudaStreamNonBlocking));
+                WCU(cudaEventCreateWithFlags(&w->evFork, cudaEventDisableTiming));
+                WCU(cudaEventCreateWithFlags(&w->evJoin, cudaEventDisableTiming));
+            }
+            P.connectAfterExtend = overlap ? 0u : 1u;
             wf_mark(c, ST_EXTEND);
             k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
             for (uint32_t j = 0; j < nB; ++j) {
@@ -715,17 +731,27 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                 k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
                                                             (uint32_t*)w->dShadowQ.p, sCount + j, j);
                 if (j + 1 < nB) {
+                    cudaStream_t cs = c->stream;
+                    if (overlap) {
+                        WCU(cudaEventRecord(w->evFork, c->stream));
+                        WCU(cudaStreamWaitEvent(w->sideStream, w->evFork, 0));
+                        cs = w->sideStream;
+                    }
                     wf_mark(c, ST_EXTEND);
                     k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
                     wf_mark(c, ST_CONNECT);
-                    k_connect_prep<<<w->gridPrep, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                    k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                        (uint32_t*)w->dJobQ.p, oCount + j);
                     wf_mark(c, ST_OCCLUDE);
-                    k_occlude<<<w->gridOcclude, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
+                    k_occlude<<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
                     wf_mark(c, ST_FINISH);
-                    k_connect_finish<<<w->gridFinish, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
+                    k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                          (uint32_t*)w->dJobQ.p, mCount + j);
-                    k_connect_mis<<<w->smCount, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
+                    k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
+                    if (overlap) {
+                        WCU(cudaEventRecord(w->evJoin, w->sideStream));
+                        WCU(cudaStreamWaitEvent(c->stream, w->evJoin, 0));
+                    }
                 }
                 std::swap(qa, qb);
                 c->counters[0] += (j + 1 < nB) ? 6 : 1;

@@ -592,3 +592,28 @@ def test_material_and_sphere_updates_rebuild_only_when_needed(gpu, cornell_blobs
     cp.update_buffer("materials", mats3)
     assert cp.get_option("last_wide_device_us") == 0
     check(dict(cornell_blobs, materials=mats3, spheres=sph))
+
+
+def test_connect_chain_on_a_second_stream_gives_the_same_image(gpu, bunny_blobs):
+    # option overlap_connect: the NEE kernels of bounce j run beside extend(j+1) on a second stream (default for batches
+    # of one frame) and no longer skip the NEE rays of escaping paths — whose direct light trace() drops anyway
+    W, H = 160, 120
+    nobj = bunny_blobs["objects"].size // 80
+    pc = ob.default_push_constants(W, H, 10, nobj)
+    pc.view(np.float32)[39] = 1.0               # lightDir.w (byte 156): environment on, so that escaping paths carry light
+    images = {}
+    for mode, fif in ((0, 1), (1, 1), (2, 1), (0, 4), (2, 4)):
+        cp = _pass(gpu, bunny_blobs, W, H)
+        cp.set_option("overlap_connect", mode)
+        cp.set_option("frames_in_flight", fif)
+        for first in (0, 3):
+            cp.render_frames(pc, first, 3)
+        images[(mode, fif)] = cp.read_accum()
+        cp.close()
+    want = images[(0, 1)]
+    assert want[..., 3].min() == 6
+    for key, img in images.items():
+        assert _differing(img, want) <= 1e-4, key
+    with ob.math_mode(1):
+        exact, _ = ob.OracleScene(bunny_blobs).render_frames(pc, W, H, 0, 6)
+    assert _differing(images[(1, 1)], exact) <= 1e-4
