@@ -141,7 +141,7 @@ int b200pt_build_bvh(int device, const void* tri_points, uint32_t n_points, void
  * "textures" 0/1: texture extension (albedo / metalness maps; off = the HEAD shader, which never samples);
  * "storage_rgba8" 0/1: b200pt_render stores the image at unorm8 precision, as the reference's rgba8 image does;
  * "overlap_connect" 0/1/2: the NEE (connect) kernels of a bounce run on a second stream beside the next extension —
- * never / for batches of one frame (default) / always; "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32 (k_extend), "occl_tri_vote", "occl_fetch_idle" (k_occlude): scheduling of the wavefront kernels
+ * never / for batches of up to 8 frames (default) / always; "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32 (k_extend), "occl_tri_vote", "occl_fetch_idle" (k_occlude): scheduling of the wavefront kernels
  * (results do not depend on them); "wide_build" 1 (default) / 0: the internal wide BVH of all triangles is built on
  * the device / on the host at b200pt_upload_scene and b200pt_update_* (read before the upload; images do not depend
  * on it). Read-only: "last_scene_build_us", "last_wide_device_us". Unknown keys fail. */

@@ -61,7 +61,7 @@ struct b200pt_ctx {
     int triVote32 = 12;           // see WfParams; swept on the C4 stand-in: 8 / 10 / 11 / 12 / 13 / 16 -> 300.9 / 305.2 / 305.7 / 305.6 / 304.6 / 298.3 Mpaths/s
     int fetchMinIdle = 7;         // 4 / 6 / 7 / 8 / 10 / 12 -> 298.2 / 305.5 / 306.2 / 305.6 / 303.7 / 294.2 (with triVote32 = 12)
     int triVoteOccl32 = 12, fetchMinIdleOccl = 7;     // k_occlude's own pair
-    int overlapConnect = 1;       // connect chain of bounce j beside extend(j+1) on a second stream: 0 never, 1 for one-frame batches, 2 always
+    int overlapConnect = 1;       // connect chain of bounce j beside extend(j+1) on a second stream: 0 never, 1 for batches of up to 8 frames, 2 always
     int sharePrimary = 1;         // trace the primary ray once per pixel and share the hit between frame slots (A-Q4)
     int wideBuild = 1;            // 1: the wide BVH of all triangles is built on the device (wide_build.cu), 0: on the host
     double lastSceneBuildMs = 0.0, lastWideDeviceMs = 0.0;   // wall time of the last re-layout; device part of it
