@@ -32,8 +32,17 @@ namespace wb {
 // SAH bins per axis. Tree quality is worth a few per cent of tracing throughput (C4 stand-in, 24 frames in flight:
 // 16 bins 285.1 Mpaths/s, 32: 293.3, 64: 295.1, 128: 297.0, 256: 295.4; on the statue scene 64 and 128 are level), the sweep
 // over the bins is serial per node and axis, and most nodes are tiny: nodes of up to 64 triangles use NB_SMALL bins
-// (16, 32 or 64 there measure the same).
+// (16, 32 or 64 there measure the same). Tiers measured on the final traversal kernels (Mpaths/s, device build ms):
+// 64 everywhere above 64 triangles 310.3 / 5.7; 128 above 2048 triangles and 64 below 311.5 / 7.2; 128 everywhere 312.4 / 9.0;
+// 256 above 2048: 309.7 / 41.6 — differences at the level of scene-specific noise, 64 stays.
+#ifndef PT_WIDE_BINS_MID
+#define PT_WIDE_BINS_MID PT_WIDE_BINS       /* bins for nodes of 65 .. PT_WIDE_MID_MAX triangles */
+#endif
+#ifndef PT_WIDE_MID_MAX
+#define PT_WIDE_MID_MAX 2048
+#endif
 constexpr int NB = PT_WIDE_BINS;
+constexpr int NB_MID = PT_WIDE_BINS_MID;
 constexpr int NB_SMALL = PT_WIDE_BINS_SMALL;
 constexpr uint32_t HUGE_MIN = 32768;         // nodes with more triangles are split by many blocks (k_huge_*)
 
@@ -147,12 +156,13 @@ __global__ void __launch_bounds__(1024) k_wide_split(Dev d, const uint32_t* __re
     for (uint32_t item = blockIdx.x; item < nList; item += gridDim.x) {
         const uint32_t me = list[item];
         const uint32_t first = d.nodes2[me].first, n = d.nodes2[me].count;
-        const int nb = n > 64 ? NB : NB_SMALL;
+        const int nb = n > PT_WIDE_MID_MAX ? NB : n > 64 ? NB_MID : NB_SMALL;
         uint32_t* idx = d.idx + first;
         if (tid < 3) { s.lo[tid] = s.cLo[tid] = 0xffffffffu; s.hi[tid] = s.cHi[tid] = 0u; }
-        for (uint32_t i = tid; i < 3 * NB; i += nT) {
-            (&s.binCount[0][0])[i] = 0u;
-            for (int c = 0; c < 3; ++c) { (&s.binLo[0][0][0])[i * 3 + c] = 0xffffffffu; (&s.binHi[0][0][0])[i * 3 + c] = 0u; }
+        for (uint32_t i = tid; i < 3u * (uint32_t)nb; i += nT) {          // only the bins this node uses
+            const uint32_t a = i / (uint32_t)nb, k = i % (uint32_t)nb;
+            s.binCount[a][k] = 0u;
+            for (int c = 0; c < 3; ++c) { s.binLo[a][k][c] = 0xffffffffu; s.binHi[a][k][c] = 0u; }
         }
         __syncthreads();
         {
