@@ -252,3 +252,20 @@ def test_render_window_is_a_view_of_the_full_image(cornell_blobs):
     full, _ = sc.render_frames(pc, W, H, 2, 2)
     assert np.array_equal(sc.render_window(pc, W, H, 2, 10, 7, 20, 15, n=2), full[7:22, 10:30])
     assert np.array_equal(sc.render_window(pc, W, H, 2, 0, 0, 32, 24, n=2, sx=2, sy=2), full[::2, ::2])
+
+
+def test_oracle_matches_reference_shader_golden():
+    """tests/golden/ref_shader.npz holds outputs of the reference's OWN shader text compiled for the CPU
+    (oracle/_ref/libraytrace_comp.so, made by oracle/ref_from_glsl.py from shaders/raytrace.comp; vectors written by
+    tests/golden/make_ref_shader_golden.py). The oracle must reproduce them bit for bit — this runs everywhere, also
+    where /root/reference is absent."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_ref_shader_golden", os.path.join(GOLDEN, "make_ref_shader_golden.py"))
+    g = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(g)
+    from conftest import load_scene_fixture
+    want = np.load(os.path.join(GOLDEN, "ref_shader.npz"))
+    for name, (fix, kind, W, H, over, extra) in g.cases().items():
+        blobs = load_scene_fixture(fix)
+        got = g.run(ob.OracleScene(blobs), kind, W, H, g.push_constants(W, H, blobs, over), extra)
+        assert np.array_equal(np.ascontiguousarray(got).view(np.uint32), want[name].view(np.uint32)), name
