@@ -121,6 +121,11 @@ int b200pt_attach_accum(b200pt_ctx* ctx, void* device_ptr);
 int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const float* host_rays, uint64_t n,
                        void* host_hits48);
 
+/* The same with rays and records already in device memory (n * 32 and n * 48 bytes); asynchronous on the context's
+ * stream. The throughput form: the soup roofline case of the bench times this call. */
+int b200pt_trace_batch_device(b200pt_ctx* ctx, const void* push_constants_208, const void* device_rays, uint64_t n,
+                              void* device_hits48);
+
 /* GPU build of one object's BVH2 — replaces VulkanEngine::build_bvh(size, triIndex) with update_bvh_bounds,
  * subdivide_bvh and find_bvh_split_plane (src/vk_engine.cpp:1169-1337): 20-bin SAH, back-swapping partition,
  * depth-first node numbering. Bit-identical to the reference's sequential build for finite coordinates: same node
@@ -136,8 +141,30 @@ int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const fl
 int b200pt_build_bvh(int device, const void* tri_points, uint32_t n_points, void* triangles, uint32_t first_tri,
                      uint32_t count, uint32_t root_index, void* nodes_out, uint32_t* n_nodes_out, double* device_ms);
 
+/* ---- multi-GPU. The reference drives ONE GPU through one queue (src/vk_engine.cpp:115-117); a
+ * maintainer who wants N GPUs behind the same dispatch point (run_compute, src/vk_engine.cpp:1623-1676) creates one
+ * context per GPU (one thread or one process each, scene uploaded to every one) and joins them with a communicator.
+ * NCCL is bound at run time (libnccl.so.2); these entries fail with a message when it is absent. Collective calls
+ * (reduce_accum, render_frame_interleaved) must be made by every rank; they are asynchronous on each context's stream. */
+#define B200PT_UNIQUE_ID_BYTES 128
+int b200pt_comm_unique_id(void* out128);   /* rank 0 makes it and hands it to the other ranks (shared memory, a file, MPI ...) */
+int b200pt_comm_init_rank(b200pt_ctx* ctx, int nranks, int rank, const void* unique_id128);
+int b200pt_comm_destroy(b200pt_ctx* ctx);
+int b200pt_comm_info(b200pt_ctx* ctx, int* nranks, int* rank);      /* 1, 0 without a communicator */
+/* Sample split of draw()'s progressive loop: of the frames first_frame .. first_frame + n_frames - 1 this rank renders
+ * first_frame + rank, + nranks, ... (independent seeds: raytrace.comp:562-564) into its own accumulator. */
+int b200pt_render_frames_split(b200pt_ctx* ctx, const void* push_constants_208, uint32_t first_frame, uint32_t n_frames);
+/* Sum of all ranks' accumulators (W*H float4: rgb sums and the frame count in a) onto `root`, in place, over NVLink;
+ * zero_others != 0 clears the accumulators of the other ranks for the next batch. */
+int b200pt_reduce_accum(b200pt_ctx* ctx, int root, int zero_others);
+/* One progressive frame split by INTERLEAVED rows (rank r renders rows r, r + nranks, ...: a pixel's seed depends only
+ * on x, y, W and the frame, so any subset of pixels is exact, and interleaving balances rows of unequal cost). Every
+ * rank accumulates its rows into its own accumulator; `root` then receives the other ranks' rows into its accumulator. */
+int b200pt_render_frame_interleaved(b200pt_ctx* ctx, const void* push_constants_208, uint32_t frame, int root);
+
 /* Options: "pipeline" 0 = reference-layout per-pixel kernel, 1 = wavefront (default for
- * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1;
+ * render_frames/trace_batch); "frames_in_flight" (1..64); "profile_stages" 0/1; "count_work" 0/1: the traversal
+ * kernels count their node visits and triangle tests (counters [7..10]; a few percent slower);
  * "textures" 0/1: texture extension (albedo / metalness maps; off = the HEAD shader, which never samples);
  * "storage_rgba8" 0/1: b200pt_render stores the image at unorm8 precision, as the reference's rgba8 image does;
  * "overlap_connect" 0/1/2: the NEE (connect) kernels of a bounce run on a second stream beside the next extension —
@@ -149,7 +176,14 @@ int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
 
 /* Counters since the last b200pt_clear / b200pt_reset_counters, 16 x u64:
- * [0] kernel launches, [1] paths traced, [2] extension rays, [3] shadow/pdf rays, [4] reserved ... */
+ * [0] kernel launches, [1] paths traced;
+ * algorithmic work — what the reference's trace() does for those paths: [2] extension rays (one
+ * calculateIntersections per path per bounce), [3] connect items (diffuse bounces whose next-event query reached the
+ * connect stage; the reference traces three rays for each, raytrace.comp:443,447,453);
+ * traced work — what the kernels walked: [4] rays of the closest-hit launches (one primary ray per PIXEL when a batch
+ * shares the primary hit between its frame slots), [5] occlusion walks, [6] exact pdf rays (evaluated lazily);
+ * with option "count_work": [7] node visits and [8] triangle tests of the closest-hit kernel, [9] and [10] the same
+ * for the occlusion kernel (wide layout: 80 B per node, 64 B per triangle record); [11..15] reserved. */
 int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
 int b200pt_reset_counters(b200pt_ctx* ctx);
 /* With option "profile_stages" = 1 the wavefront records a CUDA event between consecutive launches; this

@@ -25,9 +25,10 @@ EXPORTS = (
     "b200pt_set_stream b200pt_sync b200pt_upload_scene b200pt_update_materials b200pt_update_spheres "
     "b200pt_update_objects b200pt_upload_texture b200pt_render b200pt_render_frames b200pt_render_frames_rows "
     "b200pt_clear b200pt_read_accum_f32 b200pt_read_image_f32 b200pt_write_image_f32 b200pt_read_rgba8 "
-    "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch "
+    "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch b200pt_trace_batch_device "
     "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_read_stage_times "
-    "b200pt_last_render_ms b200pt_build_bvh").split()
+    "b200pt_last_render_ms b200pt_build_bvh b200pt_comm_unique_id b200pt_comm_init_rank b200pt_comm_destroy b200pt_comm_info "
+    "b200pt_render_frames_split b200pt_reduce_accum b200pt_render_frame_interleaved").split()
 
 
 class BackendError(RuntimeError):
@@ -70,6 +71,14 @@ def load_library(path=None):
     L.b200pt_device_accum_ptr.argtypes = [vp, C.POINTER(vp)]
     L.b200pt_device_image_ptr.argtypes = [vp, C.POINTER(vp)]
     L.b200pt_trace_batch.argtypes = [vp, vp, vp, u64, vp]
+    L.b200pt_trace_batch_device.argtypes = [vp, vp, vp, u64, vp]
+    L.b200pt_comm_unique_id.argtypes = [vp]
+    L.b200pt_comm_init_rank.argtypes = [vp, i32, i32, vp]
+    L.b200pt_comm_destroy.argtypes = [vp]
+    L.b200pt_comm_info.argtypes = [vp, C.POINTER(i32), C.POINTER(i32)]
+    L.b200pt_render_frames_split.argtypes = [vp, vp, u32, u32]
+    L.b200pt_reduce_accum.argtypes = [vp, i32, i32]
+    L.b200pt_render_frame_interleaved.argtypes = [vp, vp, u32, i32]
     L.b200pt_build_bvh.argtypes = [i32, vp, u32, vp, u32, u32, u32, vp, C.POINTER(u32), C.POINTER(C.c_double)]
     L.b200pt_set_option.argtypes = [vp, C.c_char_p, i64]
     L.b200pt_get_option.argtypes = [vp, C.c_char_p, C.POINTER(i64)]
@@ -153,6 +162,32 @@ class ComputePass:
             rc = self.L.b200pt_render_frames_rows(self.h, _ptr(pc), first_frame, n_frames, frame_stride, rows[0], rows[1])
         self._check(rc, "b200pt_render_frames")
 
+    # ---- multi-GPU: one ComputePass per GPU, joined by an NCCL communicator inside the library (csrc/comm.cu)
+    def comm_init(self, nranks, rank, unique_id):
+        """unique_id: the 128 bytes rank 0 got from comm_unique_id(), handed over out of band."""
+        uid = _bytes_array(unique_id)
+        assert uid.size == 128
+        self._check(self.L.b200pt_comm_init_rank(self.h, nranks, rank, _ptr(uid)), "b200pt_comm_init_rank")
+
+    def comm_destroy(self):
+        self._check(self.L.b200pt_comm_destroy(self.h), "b200pt_comm_destroy")
+
+    def comm_info(self):
+        n, r = C.c_int(), C.c_int()
+        self._check(self.L.b200pt_comm_info(self.h, C.byref(n), C.byref(r)), "b200pt_comm_info")
+        return n.value, r.value
+
+    def render_frames_split(self, push_constants, first_frame, n_frames):
+        pc = _bytes_array(push_constants)
+        self._check(self.L.b200pt_render_frames_split(self.h, _ptr(pc), first_frame, n_frames), "b200pt_render_frames_split")
+
+    def reduce_accum(self, root=0, zero_others=True):
+        self._check(self.L.b200pt_reduce_accum(self.h, root, int(zero_others)), "b200pt_reduce_accum")
+
+    def render_frame_interleaved(self, push_constants, frame, root=0):
+        pc = _bytes_array(push_constants)
+        self._check(self.L.b200pt_render_frame_interleaved(self.h, _ptr(pc), frame, root), "b200pt_render_frame_interleaved")
+
     def clear(self):
         self._check(self.L.b200pt_clear(self.h), "b200pt_clear")
 
@@ -213,10 +248,19 @@ class ComputePass:
         self._check(self.L.b200pt_trace_batch(self.h, _ptr(pc), _ptr(r), r.shape[0], _ptr(hits)), "b200pt_trace_batch")
         return hits
 
+    def trace_batch_device(self, push_constants, device_rays, n, device_hits):
+        """b200pt_trace_batch_device: rays (n x 8 float32) and 48-byte hit records already on the device (pointers as int)."""
+        pc = _bytes_array(push_constants)
+        self._check(self.L.b200pt_trace_batch_device(self.h, _ptr(pc), C.c_void_p(device_rays), n, C.c_void_p(device_hits)),
+                    "b200pt_trace_batch_device")
+
     def counters(self):
         c = np.zeros(16, np.uint64)
         self._check(self.L.b200pt_read_counters(self.h, _ptr(c)), "b200pt_read_counters")
-        return dict(launches=int(c[0]), paths=int(c[1]), extension_rays=int(c[2]), shadow_rays=int(c[3]))
+        return dict(launches=int(c[0]), paths=int(c[1]), extension_rays=int(c[2]), connect_items=int(c[3]),
+                    extension_rays_traced=int(c[4]), occlusion_rays_traced=int(c[5]), pdf_rays_traced=int(c[6]),
+                    extend_node_visits=int(c[7]), extend_tri_tests=int(c[8]), occlude_node_visits=int(c[9]),
+                    occlude_tri_tests=int(c[10]))
 
     STAGES = ("generate", "extend", "shade", "connect_prep", "accumulate", "occlude", "connect_finish")
 
@@ -234,6 +278,15 @@ class ComputePass:
         ms = C.c_float()
         self._check(self.L.b200pt_last_render_ms(self.h, C.byref(ms)), "b200pt_last_render_ms")
         return ms.value
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id (b200pt_comm_unique_id): made by rank 0, handed to the other ranks out of band."""
+    L = load_library()
+    b = np.zeros(128, np.uint8)
+    if L.b200pt_comm_unique_id(_ptr(b)):
+        raise BackendError("b200pt_comm_unique_id: " + L.b200pt_global_error().decode())
+    return b
 
 
 def build_bvh(tri_points, triangles, first_tri, count, root_index, device=0):

@@ -11,7 +11,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libb200pt.so")
-SOURCES = ["api.cu", "megakernel.cu", "wavefront.cu", "bvh2_build.cu", "wide_build.cu"]
+SOURCES = ["api.cu", "megakernel.cu", "wavefront.cu", "bvh2_build.cu", "wide_build.cu", "comm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-O2,-fno-fast-math,-ffp-contract=off", "-shared",
               "-cudart", "static"]
@@ -81,7 +81,7 @@ def build(force=False, verbose=False, extra=(), out=None):
         return LIB
     env = dict(os.environ)
     env.pop("CXX", None)    # the image's $CXX points at a g++ without its spec files
-    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-ccbin", "/usr/bin/g++", "-o", out or LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [nvcc_path()] + NVCC_FLAGS + list(extra) + ["-ccbin", "/usr/bin/g++", "-o", out or LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-ldl"]
     if verbose:
         print(" ".join(cmd))
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)

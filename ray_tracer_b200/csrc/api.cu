@@ -140,6 +140,7 @@ int b200pt_destroy(b200pt_ctx* c) {
     if (!c) return 0;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    b200pt_comm_destroy(c);
     wavefront_destroy(c);
     dev_free(c->dSpheres); dev_free(c->dMaterials); dev_free(c->dPoints); dev_free(c->dTris);
     dev_free(c->dObjects); dev_free(c->dNodes); dev_free(c->dMinv);
@@ -426,12 +427,23 @@ int b200pt_trace_batch(b200pt_ctx* c, const void* pc208, const float* rays, uint
     return 0;
 }
 
+int b200pt_trace_batch_device(b200pt_ctx* c, const void* pc208, const void* dRays, uint64_t n, void* dHits) {
+    ptl::PushConstants pc;
+    if (int rc = check_render(c, pc208, pc)) return rc;
+    if (n && (!dRays || !dHits)) return fail(c, B200PT_ERR_ARG, "trace_batch_device: NULL buffer");
+    if (n == 0) return 0;
+    CU(c, cudaSetDevice(c->device));
+    if (c->pipeline == 0) { CU(c, launch_ref_trace_batch(c, pc, (const float*)dRays, n, (HitRecord48*)dHits)); return 0; }
+    return wavefront_trace_batch(c, pc, (const float*)dRays, n, (HitRecord48*)dHits);
+}
+
 int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (!c || !key) return B200PT_ERR_ARG;
     std::string k(key);
     if (k == "pipeline") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "pipeline must be 0 or 1"); c->pipeline = (int)v; return 0; }
     if (k == "frames_in_flight") { if (v < 1 || v > 64) return fail(c, B200PT_ERR_ARG, "frames_in_flight must be 1..64"); c->framesInFlight = (int)v; return 0; }
     if (k == "profile_stages") { c->profileStages = v != 0; return 0; }
+    if (k == "count_work") { c->countWork = v != 0; return 0; }
     if (k == "textures") { c->useTextures = v != 0; return 0; }
     if (k == "storage_rgba8") { c->storageRgba8 = v != 0; return 0; }
     if (k == "trav_tri_vote") { if (v < 1 || v > 32) return fail(c, B200PT_ERR_ARG, "trav_tri_vote must be 1..32"); c->triVote32 = (int)v; return 0; }
@@ -449,6 +461,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "pipeline") { *v = c->pipeline; return 0; }
     if (k == "frames_in_flight") { *v = c->framesInFlight; return 0; }
     if (k == "profile_stages") { *v = c->profileStages; return 0; }
+    if (k == "count_work") { *v = c->countWork; return 0; }
     if (k == "textures") { *v = c->useTextures; return 0; }
     if (k == "storage_rgba8") { *v = c->storageRgba8; return 0; }
     if (k == "trav_tri_vote") { *v = c->triVote32; return 0; }

@@ -26,6 +26,8 @@ struct DeviceBuffer {
 
 }  // namespace pt
 
+struct b200pt_comm;           // comm.cu: NCCL communicator joining the contexts of a multi-GPU job
+
 struct b200pt_ctx {
     int device = 0;
     int W = 0, H = 0;
@@ -58,6 +60,7 @@ struct b200pt_ctx {
     int pipeline = 1;
     int framesInFlight = 4;
     int profileStages = 0;
+    int countWork = 0;            // traversal kernels count their node visits / triangle tests (counters [7..10])
     int triVote32 = 12;           // see WfParams; swept on the C4 stand-in: 8 / 10 / 11 / 12 / 13 / 16 -> 300.9 / 305.2 / 305.7 / 305.6 / 304.6 / 298.3 Mpaths/s
     int fetchMinIdle = 7;         // 4 / 6 / 7 / 8 / 10 / 12 -> 298.2 / 305.5 / 306.2 / 305.6 / 303.7 / 294.2 (with triVote32 = 12)
     int triVoteOccl32 = 12, fetchMinIdleOccl = 7;     // k_occlude's own pair
@@ -71,9 +74,11 @@ struct b200pt_ctx {
     float lastMs = 0.f;
 
     pt::WavefrontState* wf = nullptr;
+    b200pt_comm* comm = nullptr;
 };
 
 namespace pt {
+void set_global_error(const char* what);      // api.cu: text behind b200pt_global_error()
 // megakernel.cu
 cudaError_t launch_ref_dispatch(b200pt_ctx* c, const ptl::PushConstants& pc);
 cudaError_t launch_ref_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,

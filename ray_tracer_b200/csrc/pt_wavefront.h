@@ -41,7 +41,8 @@ struct WfParams {
     ptl::PushConstants pc;
     CameraPlane cp;
     int W, H;
-    uint32_t row0, rows;            // row band rendered
+    uint32_t row0, rows;            // rows rendered: row0 + k * rowStride, k < rows
+    uint32_t rowStride;             // 1 = a contiguous band; N = every N-th row (interleaved split of one frame over N GPUs)
     uint32_t firstFrame, stride;    // slot k renders frameCount = firstFrame + k*stride
     uint32_t nSlots, nPaths;        // nPaths = nSlots * rows * W
     uint32_t triVote32;             // persistent kernels: run a triangle step when >= triVote32/32 of the busy lanes hold triangles
@@ -60,7 +61,7 @@ PT_HD float4 f4(v3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
 PT_HD void stage_generate(const WfParams& P, const PathArrays& A, uint32_t p) {
     uint32_t perSlot = P.rows * (uint32_t)P.W;
     uint32_t k = p / perSlot, rem = p - k * perSlot;
-    uint32_t gy = P.row0 + rem / (uint32_t)P.W, gx = rem % (uint32_t)P.W;
+    uint32_t gy = P.row0 + (rem / (uint32_t)P.W) * P.rowStride, gx = rem % (uint32_t)P.W;
     uint32_t frame = P.firstFrame + k * P.stride;
     Ray r = primary_ray(P.pc.cam, P.cp, gx, gy, P.W, P.H);
     // samples of one dispatch share the pixel's RNG stream (raytrace.comp:562-570): sample s > 0 continues from the state
@@ -418,7 +419,7 @@ PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArray
 // NaN/Inf -> magenta); accum.a counts frames.
 PT_HD void stage_accumulate(const WfParams& P, const PathArrays& A, float4* accum, uint32_t pix) {
     uint32_t perSlot = P.rows * (uint32_t)P.W;
-    uint32_t gy = P.row0 + pix / (uint32_t)P.W, gx = pix % (uint32_t)P.W;
+    uint32_t gy = P.row0 + (pix / (uint32_t)P.W) * P.rowStride, gx = pix % (uint32_t)P.W;
     size_t g = (size_t)gy * P.W + gx;
     float4 a = accum[g];
     for (uint32_t k = 0; k < P.nSlots; ++k) {

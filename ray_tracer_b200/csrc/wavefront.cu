@@ -85,6 +85,7 @@ void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool
 }
 
 #define WF_THREADS 128
+#define WF_RAY_COUNTERS 16      /* device-side u64 counters: k_fold's five, then work counters [8..11] (option count_work) */
 
 static __device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred) {
     // warp-aggregated queue append: one atomic per warp; returns this lane's slot (valid when pred)
@@ -183,9 +184,19 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
 #ifndef PT_EXTEND_MIN_BLOCKS
 #define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
 #endif
+// COUNT (option "count_work"): node visits and triangle tests of the launch are added to work[0], work[1] — the
+// kernel's own algorithmic work in the WIDE layout (80 B per node visit, 64 B per triangle test), which the bench's
+// roofline divides by the measured L2 gather bandwidth.
+static __device__ __forceinline__ void flush_work(unsigned long long* work, uint32_t nodes, uint32_t tris) {
+    nodes = __reduce_add_sync(0xffffffffu, nodes);
+    tris = __reduce_add_sync(0xffffffffu, tris);
+    if ((threadIdx.x & 31u) == 0u) { atomicAdd(work, (unsigned long long)nodes); atomicAdd(work + 1, (unsigned long long)tris); }
+}
+template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
-                                                       uint32_t* workCounter, Hit* __restrict__ hitOut) {
+                                                       uint32_t* workCounter, Hit* __restrict__ hitOut, unsigned long long* work) {
+    uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *qCount;
     const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
     PT_DECLARE_STACK(stack);
@@ -219,11 +230,12 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         }
         if (nBusy == 0u) break;                    // queue exhausted and every lane done
         if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
-            if (hasTri) trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
+            if (hasTri) { trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key); if (COUNT) cntTri++; }
         } else {
-            if (canNode) trav_node_step(sc.all, t, stack, hit.dst);
+            if (canNode) { trav_node_step(sc.all, t, stack, hit.dst); if (COUNT) cntNode++; }
         }
     }
+    if (COUNT) flush_work(work, cntNode, cntTri);
 }
 
 // Block-aggregated queue append: ONE global atomic per block per round instead of one per warp. With 16 M paths per
@@ -325,9 +337,11 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
 }
 
 // connect, part 2: bounded any-hit walks of the full BVH, same warp scheduling as k_extend
+template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
-                                                        uint32_t* workCounter) {
+                                                        uint32_t* workCounter, unsigned long long* work) {
+    uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *jobCount;
     const uint32_t objectCount = P.pc.params.objectCount;
     PT_DECLARE_STACK(stack);
@@ -356,14 +370,16 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
         }
         if (nBusy == 0u) break;
         if (nNode == 0u || 32u * nTri >= P.triVoteOccl32 * nBusy) {
+            if (COUNT && hasTri) cntTri++;
             if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
                 connect_job_occluded(A, job);
                 busy = false;
             }
         } else {
-            if (canNode) trav_node_step(sc.all, t, stack, tE);
+            if (canNode) { trav_node_step(sc.all, t, stack, tE); if (COUNT) cntNode++; }
         }
     }
+    if (COUNT) flush_work(work, cntNode, cntTri);
 }
 
 // connect, part 3: pdf, power-heuristic weight, direct light; queues the (practically never occurring) paths whose
@@ -417,34 +433,52 @@ __global__ void __launch_bounds__(WF_THREADS) k_dispatch_resolve(const __grid_co
     }
 }
 
-// ray counters: [0] += extension rays (sum of qCount), [1] += NEE/pdf queries (2 per connect item)
-__global__ void k_fold(const uint32_t* qCount, const uint32_t* sCount, uint32_t nBounce, unsigned long long* rayCounters) {
+// ray counters of one batch. Algorithmic (what the reference's trace() does for these paths): [0] += extension rays
+// (sum of qCount: one calculateIntersections per path per bounce), [1] += connect items (diffuse bounces whose NEE
+// query reached the connect stage; the reference traces three rays for each, raytrace.comp:443,447,453).
+// Traced (what the kernels really walked): [2] += rays of the k_extend launches (bounce 0 is ONE ray per pixel when
+// the batch shares the primary hit between its frame slots), [3] += occlusion walks (k_occlude jobs), [4] += exact
+// pdf rays (k_connect_mis, lazily evaluated).
+__global__ void k_fold(const uint32_t* qCount, const uint32_t* sCount, const uint32_t* oCount, const uint32_t* mCount,
+                       const uint32_t* primaryCount, uint32_t sharePrimary, uint32_t nBounce, unsigned long long* rayCounters) {
     if (blockIdx.x || threadIdx.x) return;
-    unsigned long long e = 0, s = 0;
-    for (uint32_t j = 0; j < nBounce; ++j) { e += qCount[j]; s += sCount[j]; }
+    unsigned long long e = 0, s = 0, o = 0, m = 0;
+    for (uint32_t j = 0; j < nBounce; ++j) { e += qCount[j]; s += sCount[j]; o += oCount[j]; m += mCount[j]; }
     rayCounters[0] += e;
-    rayCounters[1] += 2ull * s;
+    rayCounters[1] += s;
+    rayCounters[2] += sharePrimary ? e - qCount[0] + *primaryCount : e;
+    rayCounters[3] += o;
+    rayCounters[4] += m;
 }
 
-__global__ void k_wide_trace_batch(const __grid_constant__ WideScene sc, uint32_t sphereCount, uint32_t objectCount,
-                                   const float4* __restrict__ rays, uint64_t n, HitRecord48* out) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float4 o = rays[2 * i], d = rays[2 * i + 1];
-    Ray r; r.o = mk3(o.x, o.y, o.z); r.d = mk3(d.x, d.y, d.z);
-    Hit h = wide_closest_hit(sc, r, sphereCount, objectCount);
-    HitRecord48 rec;
-    memset(&rec, 0, sizeof(rec));
-    rec.dst = h.dst; rec.objectHitIndex = 0xffffffffu;
-    if (h.id != PT_HIT_MISS) {
-        v3 hp, nn; uint32_t mat, obj, prim; bool front;
-        hit_surface(sc, r, h, hp, nn, mat, front, obj, prim);
-        rec.kind = (h.id & PT_HIT_SPHERE) ? 1u : 2u;
-        rec.objectHitIndex = obj; rec.triHitIndex = prim; rec.materialIndex = mat; rec.frontFace = front ? 1u : 0u;
-        rec.normal[0] = nn.x; rec.normal[1] = nn.y; rec.normal[2] = nn.z;
-        rec.hitPoint[0] = hp.x; rec.hitPoint[1] = hp.y; rec.hitPoint[2] = hp.z;
+// b200pt_trace_batch: caller rays go through the SAME persistent closest-hit kernel as the renderer (k_extend) —
+// k_load_rays fills the path slots and an identity queue, k_hit_records turns the Hit of every ray into the 48-byte
+// record (surface data as calculateIntersections returns it, raytrace.comp:316-322).
+__global__ void __launch_bounds__(WF_THREADS) k_load_rays(const float4* __restrict__ rays, uint32_t n, PathArrays A, uint32_t* queue, uint32_t* qCount) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        A.rayO[i] = rays[2 * (size_t)i];
+        A.rayD[i] = rays[2 * (size_t)i + 1];
+        queue[i] = i;
     }
-    out[i] = rec;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *qCount = n;
+}
+__global__ void __launch_bounds__(WF_THREADS) k_hit_records(const __grid_constant__ WideScene sc, PathArrays A, uint32_t n, HitRecord48* out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        Ray r; r.o = xyz(A.rayO[i]); r.d = xyz(A.rayD[i]);
+        const Hit h = A.hit[i];
+        HitRecord48 rec;
+        memset(&rec, 0, sizeof(rec));
+        rec.dst = h.dst; rec.objectHitIndex = 0xffffffffu;
+        if (h.id != PT_HIT_MISS) {
+            v3 hp, nn; uint32_t mat, obj, prim; bool front;
+            hit_surface(sc, r, h, hp, nn, mat, front, obj, prim);
+            rec.kind = (h.id & PT_HIT_SPHERE) ? 1u : 2u;
+            rec.objectHitIndex = obj; rec.triHitIndex = prim; rec.materialIndex = mat; rec.frontFace = front ? 1u : 0u;
+            rec.normal[0] = nn.x; rec.normal[1] = nn.y; rec.normal[2] = nn.z;
+            rec.hitPoint[0] = hp.x; rec.hitPoint[1] = hp.y; rec.hitPoint[2] = hp.z;
+        }
+        out[i] = rec;
+    }
 }
 
 // Vulkan unorm8 store of the float image: clamp, scale, round to nearest even (f4 of SURVEY.md §8)
@@ -634,25 +668,27 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
-        WCU(wf_resize(w->dRayCounters, 16));
-        WCU(cudaMemsetAsync(w->dRayCounters.p, 0, 16, c->stream));
+        WCU(wf_resize(w->dRayCounters, WF_RAY_COUNTERS * 8));
+        WCU(cudaMemsetAsync(w->dRayCounters.p, 0, WF_RAY_COUNTERS * 8, c->stream));
     }
     return 0;
 }
 
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
-                            uint32_t row0, uint32_t row1, float4* dispatchImage) {
+                            uint32_t row0, uint32_t row1, float4* dispatchImage, uint32_t rowStride) {
     WavefrontState* w = c->wf;
     if (!w || !w->haveScene) { c->error = "wavefront: no scene (the last upload or update failed)"; return 3; }
     if (n == 0 || row1 <= row0) return 0;
     const uint32_t samples = pc.params.singleRender ? pc.params.sampleLimit : pc.params.raysPerPixel;
     if (samples == 0) {
         // no sample: outColor = 0/0 (raytrace.comp:574) — the per-pixel kernel produces exactly that
+        if (rowStride != 1) { c->error = "render: a dispatch without samples cannot be split by interleaved rows"; return 1; }
         cudaError_t e = launch_ref_frames(c, pc, first, n, stride, row0, row1);
         if (e != cudaSuccess) return wf_fail(c, 2, "launch_ref_frames", e);
         return 0;
     }
-    uint32_t rows = row1 - row0;
+    if (rowStride == 0) rowStride = 1;
+    uint32_t rows = (row1 - row0 + rowStride - 1) / rowStride;
     size_t perSlot = (size_t)rows * c->W;
     uint32_t slots = (uint32_t)std::min<uint64_t>((uint64_t)c->framesInFlight, n);
     // keep a batch below 2^31 paths and ~64M paths (10 GB of path state)
@@ -673,7 +709,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     const int grid = w->smCount * 8;
     const int gridShade = w->gridShade;
     WfParams P;
-    P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.stride = stride;
+    P.pc = pc; P.cp = camera_plane(pc.cam); P.W = c->W; P.H = c->H; P.row0 = row0; P.rows = rows; P.rowStride = rowStride; P.stride = stride;
     P.useTextures = (c->useTextures && c->dTexTable.p) ? 1u : 0u;
     P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
     P.triVoteOccl32 = (uint32_t)c->triVoteOccl32; P.fetchMinIdleOccl = (uint32_t)c->fetchMinIdleOccl;
@@ -687,12 +723,12 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* mCount = primaryCount + w->countSlots;
     if (!w->gridOcclude) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude<false>, WF_THREADS, 0));
         w->gridOcclude = std::max(1, perSm) * w->smCount;
     }
     if (!w->gridExtend) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
         w->gridExtend = std::max(1, perSm) * w->smCount;
     }
     for (uint32_t done = 0; done < n; done += slots) {
@@ -725,7 +761,9 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             }
             P.connectAfterExtend = overlap ? 0u : 1u;
             wf_mark(c, ST_EXTEND);
-            k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit);
+            unsigned long long* workCnt = (unsigned long long*)w->dRayCounters.p + 8;     // [8,9] extend, [10,11] occlude
+            if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, workCnt);
+            else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, nullptr);
             for (uint32_t j = 0; j < nB; ++j) {
                 wf_mark(c, ST_SHADE);
                 k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
@@ -738,12 +776,14 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                         cs = w->sideStream;
                     }
                     wf_mark(c, ST_EXTEND);
-                    k_extend<<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit);
+                    if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, workCnt);
+                    else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, nullptr);
                     wf_mark(c, ST_CONNECT);
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                        (uint32_t*)w->dJobQ.p, oCount + j);
                     wf_mark(c, ST_OCCLUDE);
-                    k_occlude<<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j);
+                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, workCnt + 2);
+                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, nullptr);
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                          (uint32_t*)w->dJobQ.p, mCount + j);
@@ -756,7 +796,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                 std::swap(qa, qb);
                 c->counters[0] += (j + 1 < nB) ? 6 : 1;
             }
-            k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, nB, (unsigned long long*)w->dRayCounters.p);
+            k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, oCount, mCount, primaryCount, P.sharePrimary, nB, (unsigned long long*)w->dRayCounters.p);
             c->counters[0] += 3;                                      // generate, extend(0), fold
             if (samples > 1) {
                 k_sample_sum<<<grid, WF_THREADS, 0, c->stream>>>(w->arrays, (float4*)w->dSampleSum.p, P.nPaths, smp, samples);
@@ -778,10 +818,34 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
     WavefrontState* w = c->wf;
     if (!w || !w->haveScene) { c->error = "wavefront: no scene (the last upload or update failed)"; return 3; }
     if (n == 0) return 0;
-    k_wide_trace_batch<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(w->scene, pc.params.sphereCount, pc.params.objectCount,
-                                                                         (const float4*)dRays, n, dHits);
-    c->counters[0] += 1;
+    const uint64_t chunkMax = (uint64_t)1 << 25;
+    if (int rc = wf_reserve(c, (size_t)std::min<uint64_t>(n, chunkMax), pc.params.bounceLimit)) return rc;
+    if (!w->gridExtend) {
+        int perSm = 0;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
+        w->gridExtend = std::max(1, perSm) * w->smCount;
+    }
+    WfParams P;
+    memset(&P, 0, sizeof(P));
+    P.pc = pc; P.W = c->W; P.H = c->H; P.rowStride = 1;
+    P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
+    uint32_t* qCount = (uint32_t*)w->dCounts.p;
+    uint32_t* workE = qCount + 2 * w->countSlots;
+    unsigned long long* workCnt = (unsigned long long*)w->dRayCounters.p + 8;
+    const int grid = w->smCount * 8;
+    for (uint64_t done = 0; done < n; done += chunkMax) {
+        const uint32_t m = (uint32_t)std::min<uint64_t>(chunkMax, n - done);
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
+        k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays + 2 * done, m, w->arrays, (uint32_t*)w->dQueue[0].p, qCount);
+        wf_mark(c, ST_EXTEND);
+        if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, workCnt);
+        else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, nullptr);
+        wf_mark(c, -1);
+        k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, w->arrays, m, dHits + done);
+        c->counters[0] += 3;
+    }
     c->counters[2] += n;
+    c->counters[4] += n;
     WCU(cudaGetLastError());
     return 0;
 }
@@ -790,11 +854,11 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
 void wavefront_fold_counters(b200pt_ctx* c) {
     WavefrontState* w = c->wf;
     if (!w || !w->dRayCounters.p) return;
-    unsigned long long h[2] = {0, 0};
-    if (cudaMemcpy(h, w->dRayCounters.p, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return;
-    c->counters[2] += h[0];
-    c->counters[3] += h[1];
-    cudaMemset(w->dRayCounters.p, 0, 16);
+    unsigned long long h[WF_RAY_COUNTERS] = {0};
+    if (cudaMemcpy(h, w->dRayCounters.p, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    for (int i = 0; i < 5; ++i) c->counters[2 + i] += h[i];           // [2..6]: see k_fold
+    for (int i = 0; i < 4; ++i) c->counters[7 + i] += h[8 + i];       // [7..10]: node visits / triangle tests of k_extend, k_occlude
+    cudaMemset(w->dRayCounters.p, 0, sizeof(h));
 }
 
 cudaError_t launch_image_to_rgba8(b200pt_ctx* c, const float4* image, uchar4* out, size_t n) {

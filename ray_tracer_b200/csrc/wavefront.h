@@ -12,8 +12,9 @@ void wavefront_set_textures(b200pt_ctx* c);      // texture table / sRGB table p
 void wavefront_invalidate_frame_state(b200pt_ctx* c);
 // dispatchImage != NULL (n == 1, whole image): instead of adding the frame to the accumulator, finish it as ONE literal
 // dispatch into that storage image (progressive blend etc., raytrace.comp:568-593)
+// rowStride > 1: rows row0, row0 + rowStride, ... below row1 (interleaved split of one frame over several GPUs)
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
-                            uint32_t row0, uint32_t row1, float4* dispatchImage = nullptr);
+                            uint32_t row0, uint32_t row1, float4* dispatchImage = nullptr, uint32_t rowStride = 1);
 int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits);
 void wavefront_fold_counters(b200pt_ctx* c);
 void wavefront_resolve_stage_times(b200pt_ctx* c);     // stream idle

@@ -63,7 +63,7 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
     std::memcpy(&P.pc, pc208, sizeof(P.pc));
     P.cp = camera_plane(P.pc.cam);
     P.triVote32 = 8; P.fetchMinIdle = 8; P.sharePrimary = 0; P.connectAfterExtend = 0; P.useTextures = 0; P.continueSample = 0;
-    P.W = W; P.H = H; P.row0 = 0; P.rows = (uint32_t)H; P.stride = stride ? stride : 1;
+    P.W = W; P.H = H; P.row0 = 0; P.rows = (uint32_t)H; P.rowStride = 1; P.stride = stride ? stride : 1;
     size_t cap = (size_t)slots * W * H;
     std::vector<float4> rayO(cap), rayD(cap), atten(cap), total(cap), direct(cap), qO(cap), qL(cap), qA(cap), qE(cap);
     std::vector<Hit> hit(cap);
