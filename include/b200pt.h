@@ -98,6 +98,11 @@ int b200pt_render_frames(b200pt_ctx* ctx, const void* push_constants_208, uint32
 /* Row band [row_begin, row_end) only (interactive multi-GPU tile split); other rows untouched. */
 int b200pt_render_frames_rows(b200pt_ctx* ctx, const void* push_constants_208, uint32_t first_frame,
                               uint32_t n_frames, uint32_t frame_stride, uint32_t row_begin, uint32_t row_end);
+/* Rows row_begin, row_begin + row_stride, ... below row_end (interleaved split of a frame: rows of different cost are
+ * spread evenly over the GPUs); other rows untouched. */
+int b200pt_render_frames_rows_strided(b200pt_ctx* ctx, const void* push_constants_208, uint32_t first_frame,
+                                      uint32_t n_frames, uint32_t frame_stride, uint32_t row_begin, uint32_t row_end,
+                                      uint32_t row_stride);
 int b200pt_clear(b200pt_ctx* ctx); /* zero accumulator, storage image and counters */
 
 /* Outputs. Accumulator and image are W*H float4, row 0 first (row 0 is the top of the screen). */

@@ -18,8 +18,10 @@ Every rewrite is a syntactic rule listed in RULES below; none of them changes an
   R5  GLSL array declarators `T[N] name` -> `T name[N]`
   R6  `inout T name[N]` -> `T name[N]` (a C++ array parameter is already by reference), `inout T name` -> `T& name`
   R7  floating literals without suffix get `f` (every GLSL float literal is 32-bit)
-  R8  locals and struct members declared without an initialiser are value-initialised (`T x;` -> `T x{};`):
-      GLSL leaves them undefined; SURVEY A-Q9 pins the one that matters (HitInfo.materialIndex on a miss) to 0
+  R8  scalar / vector / struct locals and struct members declared without an initialiser are value-initialised
+      (`T x;` -> `T x{};`): GLSL leaves them undefined; SURVEY A-Q9 pins the one that matters (HitInfo.materialIndex on a
+      miss) to 0. Local ARRAYS (`uint stack[64]`, the throw-away `float[2]` counters) stay uninitialised as in GLSL: the
+      shader writes stack[0] before it reads, and the throw-away counters are never consumed
   R9  `void main()` -> `void glsl_main()`
   R10 `const float` globals get `static`
 Implicit int -> float conversions of GLSL (`max(0, x)`, `vec3 * int`, `pow(x, 5)`, `smoothstep(0, 0.4, t)`) need no
@@ -101,7 +103,7 @@ def translate(src):
         m = re.match(r"^(\s*)(\w+)\s+([\w\s,\[\]]+);\s*$", line)
         if m and (m.group(2) in BASIC_TYPES or m.group(2) in STRUCT_TYPES) and depth > 0 and m.group(2) != "return":
             names = [n.strip() for n in m.group(3).split(",")]
-            line = "%s%s %s;" % (m.group(1), m.group(2), ", ".join(n + "{}" for n in names))
+            line = "%s%s %s;" % (m.group(1), m.group(2), ", ".join(n if ("[" in n and not in_struct) else n + "{}" for n in names))
         depth += line.count("{") - line.count("}")
         if in_struct and depth == 0:
             in_struct = False

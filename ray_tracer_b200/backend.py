@@ -23,7 +23,7 @@ HIT_DTYPE = np.dtype([("dst", "<f4"), ("kind", "<u4"), ("objectHitIndex", "<u4")
 EXPORTS = (
     "b200pt_version b200pt_global_error b200pt_create b200pt_destroy b200pt_resize b200pt_last_error "
     "b200pt_set_stream b200pt_sync b200pt_upload_scene b200pt_update_materials b200pt_update_spheres "
-    "b200pt_update_objects b200pt_upload_texture b200pt_render b200pt_render_frames b200pt_render_frames_rows "
+    "b200pt_update_objects b200pt_upload_texture b200pt_render b200pt_render_frames b200pt_render_frames_rows b200pt_render_frames_rows_strided "
     "b200pt_clear b200pt_read_accum_f32 b200pt_read_image_f32 b200pt_write_image_f32 b200pt_read_rgba8 "
     "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch b200pt_trace_batch_device "
     "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_read_stage_times "
@@ -64,6 +64,7 @@ def load_library(path=None):
     L.b200pt_render.argtypes = [vp, vp]
     L.b200pt_render_frames.argtypes = [vp, vp, u32, u32, u32]
     L.b200pt_render_frames_rows.argtypes = [vp, vp, u32, u32, u32, u32, u32]
+    L.b200pt_render_frames_rows_strided.argtypes = [vp, vp, u32, u32, u32, u32, u32, u32]
     L.b200pt_clear.argtypes = [vp]
     for f in ("b200pt_read_accum_f32", "b200pt_read_image_f32", "b200pt_write_image_f32", "b200pt_read_rgba8",
               "b200pt_read_stats", "b200pt_attach_accum"):
@@ -153,10 +154,13 @@ class ComputePass:
         self._check(self.L.b200pt_render(self.h, _ptr(pc)), "b200pt_render")
 
     # ---- the progressive loop of draw() (src/vk_engine.cpp:1782-1785,1812-1814), batched
-    def render_frames(self, push_constants, first_frame, n_frames, frame_stride=1, rows=None):
+    def render_frames(self, push_constants, first_frame, n_frames, frame_stride=1, rows=None, row_stride=1):
         pc = _bytes_array(push_constants)
         assert pc.size == 208
-        if rows is None:
+        if row_stride != 1:
+            r0, r1 = rows if rows is not None else (0, self.height)
+            rc = self.L.b200pt_render_frames_rows_strided(self.h, _ptr(pc), first_frame, n_frames, frame_stride, r0, r1, row_stride)
+        elif rows is None:
             rc = self.L.b200pt_render_frames(self.h, _ptr(pc), first_frame, n_frames, frame_stride)
         else:
             rc = self.L.b200pt_render_frames_rows(self.h, _ptr(pc), first_frame, n_frames, frame_stride, rows[0], rows[1])

@@ -65,7 +65,7 @@ def build_headless(force=False, verbose=False):
     if not force and os.path.exists(HEADLESS_BIN) and all(os.path.getmtime(d) <= os.path.getmtime(HEADLESS_BIN) for d in deps):
         return HEADLESS_BIN
     cmd = ["/usr/bin/g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-o", HEADLESS_BIN] + srcs + \
-          ["-L" + HERE, "-lb200pt", "-lb200pt_host", "-Wl,-rpath,$ORIGIN"]
+          ["-L" + HERE, "-lb200pt", "-lb200pt_host", "-Wl,-rpath,$ORIGIN", "-pthread"]
     if verbose:
         print(" ".join(cmd))
     r = subprocess.run(cmd, capture_output=True, text=True)

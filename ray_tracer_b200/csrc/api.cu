@@ -331,21 +331,27 @@ int b200pt_render(b200pt_ctx* c, const void* pc208) {
     return 0;
 }
 
-int b200pt_render_frames_rows(b200pt_ctx* c, const void* pc208, uint32_t first, uint32_t n, uint32_t stride,
-                              uint32_t row0, uint32_t row1) {
+int b200pt_render_frames_rows_strided(b200pt_ctx* c, const void* pc208, uint32_t first, uint32_t n, uint32_t stride,
+                                      uint32_t row0, uint32_t row1, uint32_t rowStride) {
     ptl::PushConstants pc;
     if (int rc = check_render(c, pc208, pc)) return rc;
     if (stride == 0) stride = 1;
+    if (rowStride == 0) rowStride = 1;
     if (row1 > (uint32_t)c->H || row0 > row1) return fail(c, B200PT_ERR_ARG, "render_frames: rows [%u,%u) of %d", row0, row1, c->H);
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaEventRecord(c->evStart, c->stream));
     if (c->pipeline == 0) {
+        if (rowStride != 1) return fail(c, B200PT_ERR_STATE, "render_frames: interleaved rows need the wavefront pipeline");
         CU(c, launch_ref_frames(c, pc, first, n, stride, row0, row1));
     } else {
-        if (int rc = wavefront_render_frames(c, pc, first, n, stride, row0, row1)) return rc;
+        if (int rc = wavefront_render_frames(c, pc, first, n, stride, row0, row1, nullptr, rowStride)) return rc;
     }
     CU(c, cudaEventRecord(c->evStop, c->stream));
     return 0;
+}
+int b200pt_render_frames_rows(b200pt_ctx* c, const void* pc208, uint32_t first, uint32_t n, uint32_t stride,
+                              uint32_t row0, uint32_t row1) {
+    return b200pt_render_frames_rows_strided(c, pc208, first, n, stride, row0, row1, 1);
 }
 
 int b200pt_render_frames(b200pt_ctx* c, const void* pc208, uint32_t first, uint32_t n, uint32_t stride) {

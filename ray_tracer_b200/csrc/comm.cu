@@ -158,7 +158,7 @@ int b200pt_render_frames_split(b200pt_ctx* c, const void* pc208, uint32_t first,
 
 int b200pt_reduce_accum(b200pt_ctx* c, int root, int zero_others) {
     if (!c) return B200PT_ERR_ARG;
-    if (!c->comm || c->comm->nranks == 1) return 0;
+    if (!c->comm) return 0;
     const NcclApi* api = nccl_api();
     if (!api) return cfail(c, B200PT_ERR_STATE, g_nccl.error);
     if (root < 0 || root >= c->comm->nranks) return cfail(c, B200PT_ERR_ARG, "reduce_accum: bad root");

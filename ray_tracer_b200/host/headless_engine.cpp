@@ -129,6 +129,25 @@ bool HeadlessEngine::render_batch(uint32_t firstFrame, uint32_t nFrames) {
     return true;
 }
 
+bool HeadlessEngine::comm_init(int nranks, int rank, const void* uniqueId128) {
+    if (b200pt_comm_init_rank(ctx_, nranks, rank, uniqueId128)) return fail("b200pt_comm_init_rank");
+    return true;
+}
+bool HeadlessEngine::render_batch_split(uint32_t firstFrame, uint32_t nFrames) {
+    fill_constants();
+    if (b200pt_render_frames_split(ctx_, &constants, firstFrame, nFrames)) return fail("b200pt_render_frames_split");
+    return true;
+}
+bool HeadlessEngine::reduce_accum(int root) {
+    if (b200pt_reduce_accum(ctx_, root, 1)) return fail("b200pt_reduce_accum");
+    return true;
+}
+bool HeadlessEngine::render_frame_interleaved(uint32_t frame, int root) {
+    fill_constants();
+    if (b200pt_render_frame_interleaved(ctx_, &constants, frame, root)) return fail("b200pt_render_frame_interleaved");
+    return true;
+}
+
 bool HeadlessEngine::set_option(const char* key, long long value) {
     if (b200pt_set_option(ctx_, key, (int64_t)value)) return fail("b200pt_set_option");
     return true;

@@ -46,6 +46,13 @@ class HeadlessEngine {
     bool run_compute();                                   // one dispatch with `constants.frameCount = frameNumber`
     bool draw();                                          // one iteration of the engine's loop body
     bool render_batch(uint32_t firstFrame, uint32_t nFrames);   // progressive frames firstFrame.. in flight together
+    // multi-GPU (one engine per GPU, one host thread each): the engines of a job share an NCCL communicator inside the
+    // library; render_batch_split renders this rank's frames of the batch, reduce_accum sums the accumulators onto rank 0,
+    // render_frame_interleaved splits ONE frame by interleaved rows and gathers it on rank 0
+    bool comm_init(int nranks, int rank, const void* uniqueId128);
+    bool render_batch_split(uint32_t firstFrame, uint32_t nFrames);
+    bool reduce_accum(int root);
+    bool render_frame_interleaved(uint32_t frame, int root);
     bool set_option(const char* key, long long value);
     bool read_image(std::vector<float>& rgba);            // the storage image (progressive blend), float4
     bool read_accum_mean(std::vector<float>& rgba);       // sum of outColor / frames of render_batch

@@ -2,6 +2,9 @@
 // builds or loads a scene, runs the compute pass through the C ABI and writes the image to a file.
 //   --mode loop  : the engine's own loop, one run_compute() = one b200pt_render per draw() (progressive blend)
 //   --mode batch : progressive frames in flight together (b200pt_render_frames), the throughput path
+//   --gpus N     : one engine + host thread per GPU, joined by the library's NCCL communicator. batch: the frames are
+//                  split (rank r renders f = r mod N) and the accumulators summed onto GPU 0 at the end; --mode interleaved:
+//                  every frame is split by interleaved rows and gathered on GPU 0 (1-spp latency mode)
 // Prints one JSON line with the timing. No CPU fallback: without a CUDA device the first call fails with its message.
 #include <algorithm>
 #include <chrono>
@@ -9,7 +12,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -21,7 +26,7 @@ using pth::HeadlessEngine;
 static void usage() {
     std::puts(
         "usage: b200pt_headless (--scene FILE | --default-scene ASSETDIR | --cornell ASSETDIR | --obj FILE [--mtl FILE] [--material I])\n"
-        "         [--width W] [--height H] [--frames N] [--mode loop|batch] [--in-flight K] [--bounces D] [--rays-per-pixel R]\n"
+        "         [--width W] [--height H] [--frames N] [--mode loop|batch|interleaved] [--gpus N] [--in-flight K] [--bounces D] [--rays-per-pixel R]\n"
         "         [--env 0|1] [--angles AX AY AZ] [--pos X Y Z] [--fov F] [--device I] [--gpu-bvh] [--option KEY=VALUE]...\n"
         "         [--out-ppm FILE] [--out-pfm FILE] [--dump-constants]");
 }
@@ -30,7 +35,7 @@ int main(int argc, char** argv) {
     HeadlessEngine e;
     std::string sceneFile, assetDir, objFile, mtlFile, outPpm, outPfm, mode = "batch";
     bool cornellOnly = false, dump = false, gpuBvh = false;
-    int device = 0, material = 0;
+    int device = 0, material = 0, gpus = 1;
     uint32_t frames = 16, inFlight = 8;
     std::vector<std::pair<std::string, long long>> options;
     e.width = 512; e.height = 512;
@@ -56,6 +61,7 @@ int main(int argc, char** argv) {
         else if (a == "--pos") { need(i, 3); for (int k = 0; k < 3; ++k) e.cameraInfo.pos[k] = (float)std::atof(argv[++i]); }
         else if (a == "--fov") { need(i, 1); e.cameraInfo.fov = (float)std::atof(argv[++i]); }
         else if (a == "--device") { need(i, 1); device = std::atoi(argv[++i]); }
+        else if (a == "--gpus") { need(i, 1); gpus = std::atoi(argv[++i]); }
         else if (a == "--gpu-bvh") gpuBvh = true;
         else if (a == "--option") {
             need(i, 1);
@@ -69,8 +75,10 @@ int main(int argc, char** argv) {
         else if (a == "--dump-constants") dump = true;
         else { usage(); return a == "--help" || a == "-h" ? 0 : 2; }
     }
-    if (mode != "loop" && mode != "batch") { usage(); return 2; }
-    if (e.width == 0 || e.height == 0 || inFlight == 0) { usage(); return 2; }
+    if (mode != "loop" && mode != "batch" && mode != "interleaved") { usage(); return 2; }
+    if (e.width == 0 || e.height == 0 || inFlight == 0 || gpus < 1) { usage(); return 2; }
+    if (gpus > 1 && mode == "loop") { std::fprintf(stderr, "--gpus needs --mode batch or interleaved\n"); return 2; }
+    if (mode == "interleaved" && e.rayTracerParams.raysPerPixel != 1) { std::fprintf(stderr, "--mode interleaved renders 1-spp frames\n"); return 2; }
 
     if (dump) {           // the 208-byte block run_compute() would push for frame 0, as hex (no device needed)
         e.scene.spheres.resize(10);
@@ -112,6 +120,67 @@ int main(int argc, char** argv) {
         return 1;
     }
     const double buildS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+
+    if (gpus > 1 || mode == "interleaved") {
+        // ---- one engine per GPU (devices device .. device + gpus - 1), one host thread each; GPU `device` is the root ----
+        unsigned char uid[B200PT_UNIQUE_ID_BYTES];
+        if (b200pt_comm_unique_id(uid)) { std::fprintf(stderr, "b200pt_comm_unique_id: %s\n", b200pt_global_error()); return 1; }
+        std::vector<std::unique_ptr<HeadlessEngine>> eng((size_t)gpus);
+        std::vector<std::string> errs((size_t)gpus);
+        std::vector<double> runS((size_t)gpus, 0.0), upS((size_t)gpus, 0.0);
+        std::vector<float> img;
+        auto worker = [&](int r) {
+            HeadlessEngine* g = r == 0 ? &e : eng[(size_t)r].get();
+            auto bad = [&](const std::string& w) { errs[(size_t)r] = w.empty() ? "failed" : w; };
+            const auto tu = std::chrono::steady_clock::now();
+            if (!g->init_image(device + r)) return bad(g->error());
+            for (const auto& kv : options) if (!g->set_option(kv.first.c_str(), kv.second)) return bad(g->error());
+            if (!g->prepare_storage_buffers()) return bad(g->error());
+            if (!g->comm_init(gpus, r, uid)) return bad(g->error());
+            if (b200pt_sync(g->context())) return bad("b200pt_sync");
+            upS[(size_t)r] = std::chrono::duration<double>(std::chrono::steady_clock::now() - tu).count();
+            const auto tr = std::chrono::steady_clock::now();
+            if (mode == "interleaved") {
+                for (uint32_t f = 0; f < frames; ++f) {
+                    if (!g->render_frame_interleaved(f, 0)) return bad(g->error());
+                    if (b200pt_sync(g->context())) return bad("b200pt_sync");           // one frame at a time: latency mode
+                }
+            } else {
+                const uint32_t per = inFlight * (uint32_t)gpus;
+                for (uint32_t f = 0; f < frames; f += per)
+                    if (!g->render_batch_split(f, std::min(per, frames - f))) return bad(g->error());
+                if (!g->reduce_accum(0)) return bad(g->error());
+            }
+            if (r == 0) { if (!g->read_accum_mean(img)) return bad(g->error()); }       // D2H of the finished image ends the clock
+            else if (b200pt_sync(g->context())) return bad("b200pt_sync");
+            runS[(size_t)r] = std::chrono::duration<double>(std::chrono::steady_clock::now() - tr).count();
+        };
+        for (int r = 1; r < gpus; ++r) {
+            eng[(size_t)r].reset(new HeadlessEngine());
+            HeadlessEngine& g = *eng[(size_t)r];
+            g.width = e.width; g.height = e.height; g.scene = e.scene;
+            std::memcpy(g.cameraAngles, e.cameraAngles, sizeof e.cameraAngles);
+            g.cameraInfo = e.cameraInfo; g.environment = e.environment; g.rayTracerParams = e.rayTracerParams;
+        }
+        std::vector<std::thread> th;
+        for (int r = 0; r < gpus; ++r) th.emplace_back(worker, r);
+        for (auto& t : th) t.join();
+        for (int r = 0; r < gpus; ++r) if (!errs[(size_t)r].empty()) { std::fprintf(stderr, "gpu %d: %s\n", device + r, errs[(size_t)r].c_str()); return 1; }
+        double mean = 0.0;
+        for (size_t i = 0; i < img.size(); i += 4) mean += (double)img[i] + img[i + 1] + img[i + 2];
+        mean /= 3.0 * (double)(img.size() / 4);
+        if (!outPfm.empty() && !HeadlessEngine::write_pfm(outPfm, img.data(), e.width, e.height)) { std::fprintf(stderr, "cannot write %s\n", outPfm.c_str()); return 1; }
+        const double run = *std::max_element(runS.begin(), runS.end());
+        const double paths = (double)e.width * e.height * frames;
+        std::printf("{\"mode\": \"%s\", \"gpus\": %d, \"width\": %u, \"height\": %u, \"frames\": %u, \"bounce_limit\": %u, \"triangles\": %zu, "
+                    "\"scene_build_s\": %.4f, \"scene_upload_s\": %.4f, \"run_s\": %.6f, \"ms_per_frame\": %.4f, \"mpaths_per_s\": %.3f, "
+                    "\"mean_radiance\": %.9g}\n",
+                    mode.c_str(), gpus, e.width, e.height, frames, e.rayTracerParams.bounceLimit, e.scene.triangles.size(), buildS,
+                    *std::max_element(upS.begin(), upS.end()), run, run * 1e3 / frames, paths / run / 1e6, mean);
+        for (int r = 1; r < gpus; ++r) eng[(size_t)r]->cleanup();
+        e.cleanup();
+        return 0;
+    }
 
     // ---- init(): device ----
     if (!e.init_image(device)) { std::fprintf(stderr, "%s\n", e.error().c_str()); return 1; }

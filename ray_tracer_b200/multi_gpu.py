@@ -6,9 +6,15 @@
 * row bands (1-spp interactive frames): rank r renders rows [r*H/N, (r+1)*H/N); per-pixel seeds depend
   only on (x, y, W, frame), so bands are exact; bands are gathered on rank 0.
 
-The renderer is passed in as an object with the methods of `ComputePass` (`render_frames`), so the same
-logic is exercised on CPU under gloo with a stand-in renderer (tests/test_multi_gpu_host.py) and on GPUs
-under NCCL (bench.py). Nothing here computes radiance.
+The renderer is passed in as an object with the methods of `ComputePass` (`render_frames`, `sync`), so the same
+logic is exercised on CPU under gloo with a stand-in renderer (tests/test_multi_gpu_host.py). Nothing here
+computes radiance. The product path for several GPUs is INSIDE the library (csrc/comm.cu: b200pt_comm_init_rank,
+b200pt_render_frames_split, b200pt_reduce_accum, b200pt_render_frame_interleaved — used by bench.py and by
+b200pt_headless --gpus N); these torch.distributed helpers remain for callers that already hold a process group.
+
+Stream ordering: the renderer works on its context's stream, torch's collectives on torch's current stream. Both
+helpers call `render.sync()` before the collective and synchronise torch's stream before returning, so they are
+correct whichever stream the context was given.
 """
 import torch
 import torch.distributed as dist
@@ -37,6 +43,7 @@ def render_frames_split(render, push_constants, first_frame, n_frames, accum, to
     first, count, stride = frame_share(first_frame, n_frames, rank, world)
     if count:
         render.render_frames(push_constants, first, count, frame_stride=stride)
+    _sync(render)                                   # the collective below runs on torch's stream, the renderer on its own
     if world == 1:
         if total is not None:
             total.add_(accum)
@@ -47,6 +54,7 @@ def render_frames_split(render, push_constants, first_frame, n_frames, accum, to
         total.add_(accum)
     if rank != 0 or total is not None:
         accum.zero_()
+    _sync_torch(accum)                              # zero_ / add_ must have landed before the next batch renders into accum
 
 
 def render_frame_bands(render, push_constants, frame, accum, group=None):
@@ -56,6 +64,7 @@ def render_frame_bands(render, push_constants, frame, accum, group=None):
     r0, r1 = row_band(H, rank, world)
     if r1 > r0:
         render.render_frames(push_constants, frame, 1, frame_stride=1, rows=(r0, r1))
+    _sync(render)
     if world == 1:
         return
     # bands differ in size by at most one row: gather padded bands, copy the valid rows on rank 0
@@ -68,3 +77,15 @@ def render_frame_bands(render, push_constants, frame, accum, group=None):
         for r in range(1, world):
             b0, b1 = row_band(H, r, world)
             accum[b0:b1] = parts[r][: b1 - b0]
+    _sync_torch(accum)
+
+
+def _sync(render):
+    s = getattr(render, "sync", None)
+    if s is not None:
+        s()
+
+
+def _sync_torch(t):
+    if t.is_cuda:
+        torch.cuda.current_stream(t.device).synchronize()

@@ -52,8 +52,9 @@ def _f3(v):
     return np.ascontiguousarray(np.asarray(v, np.float32).reshape(3))
 
 
-def material(albedo=(1, 1, 1), emission=(0, 0, 0), strength=0.0, reflectance=0.0, ior=-1.0):
-    """RayMaterial, 64 bytes (src/vk_engine.h:69-79)."""
+def material(albedo=(1, 1, 1), emission=(0, 0, 0), strength=0.0, reflectance=0.0, ior=-1.0, albedo_index=-1, metalness_index=-1):
+    """RayMaterial, 64 bytes (src/vk_engine.h:69-79); albedo_index / metalness_index: TextureBuffer slots (map_Kd / map_Ks
+    of read_mtl, src/vk_engine.cpp:1109-1125), -1 = none."""
     b = np.zeros(64, np.uint8)
     f = b.view(np.float32)
     f[0:3] = albedo
@@ -62,6 +63,8 @@ def material(albedo=(1, 1, 1), emission=(0, 0, 0), strength=0.0, reflectance=0.0
     f[8] = reflectance
     f[9] = ior
     b.view(np.int32)[10:14] = -1
+    b.view(np.int32)[10] = albedo_index
+    b.view(np.int32)[11] = metalness_index
     return b
 
 

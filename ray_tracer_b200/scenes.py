@@ -17,19 +17,32 @@ from . import scene as _scene
 GPU_BVH = None     # (device, min_triangles): objects at least that large get their BVH2 from b200pt_build_bvh (same bytes)
 
 
-def _builder():
+def _builder(make_builder=None):
+    """make_builder: another builder class with the same methods (bench.py's reference arm passes the oracle's, so that it
+    loads no library of the product)."""
+    if make_builder is not None:
+        return make_builder()
     b = _scene.SceneBuilder()
     if GPU_BVH is not None:
         b.use_gpu_bvh(*GPU_BVH)
     return b
 
 
-def _pack(tri_pos, tri_nrm):
-    """(n,3,3) positions + (n,3,3) normals -> (n,3,8) TrianglePoints (uv = 0)."""
+def _pack(tri_pos, tri_nrm, uv_scale=None):
+    """(n,3,3) positions + (n,3,3) normals -> (n,3,8) TrianglePoints. uv = 0, or with uv_scale a planar mapping: the two
+    world axes across the face normal's dominant axis, times uv_scale (texture repeats per world unit; sampler 0 wraps)."""
     n = tri_pos.shape[0]
     out = np.zeros((n, 3, 8), np.float32)
     out[:, :, 0:3] = tri_pos
     out[:, :, 4:7] = tri_nrm
+    if uv_scale is not None:
+        fn = np.cross(tri_pos[:, 1] - tri_pos[:, 0], tri_pos[:, 2] - tri_pos[:, 0])
+        dom = np.argmax(np.abs(fn), axis=1)
+        ua = np.where(dom == 0, 2, 0)                 # x-facing: (z, y); y-facing: (x, z); z-facing: (x, y)
+        va = np.where(dom == 1, 2, 1)
+        idx = np.arange(n)
+        out[:, :, 3] = tri_pos[idx, :, ua] * uv_scale
+        out[:, :, 7] = tri_pos[idx, :, va] * uv_scale
     return out
 
 
@@ -162,8 +175,50 @@ ATRIUM_GROUPS = ["floor", "bricks_left", "bricks_right", "wall_front", "wall_bac
                  "plant", "lion", "trim_a", "trim_b", "trim_c", "trim_d", "trim_e", "trim_f"]
 
 
-def atrium(detail=0.89, with_light=True, seed=1):
-    """Sponza stand-in: returns (blobs, info). Materials 0..24 diffuse, 25 = emissive light box at the NEE quad."""
+def procedural_texture(kind, seed, size=1024):
+    """size x size x 4 uint8, sRGB-encoded, in the role of one file of assets/sponza_textures (absent geometry, so the
+    maps are stand-ins too): brick / tile / fabric / stone patterns with per-texel noise."""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:size, 0:size].astype(np.float32) / size
+    base = rng.uniform(0.35, 0.95, 3).astype(np.float32)
+    noise = rng.uniform(0.85, 1.0, (size, size, 1)).astype(np.float32)
+    if kind == "brick":
+        row = np.floor(y * 16)
+        mortar = (np.abs((y * 16) % 1 - 0.5) > 0.44) | (np.abs(((x * 8 + 0.5 * (row % 2)) % 1) - 0.5) > 0.47)
+        shade = np.where(mortar, 0.55, 1.0)[..., None] * (0.8 + 0.2 * np.sin(row * 12.9898)[..., None] ** 2)
+    elif kind == "tile":
+        shade = np.where(((np.floor(x * 8) + np.floor(y * 8)) % 2) == 0, 1.0, 0.6)[..., None]
+    elif kind == "fabric":
+        shade = (0.75 + 0.25 * np.sin(x * 2 * np.pi * 48) * np.sin(y * 2 * np.pi * 6))[..., None]
+    else:
+        shade = (0.7 + 0.3 * np.sin(x * 37.0 + 5 * np.sin(y * 11.0)) * np.cos(y * 29.0))[..., None]
+    rgb = np.clip(base * shade * noise, 0.0, 1.0)
+    out = np.empty((size, size, 4), np.uint8)
+    out[..., :3] = np.round(rgb * 255.0)
+    out[..., 3] = 255
+    return out
+
+
+def metal_mask_texture(seed, size=512):
+    """metalness map (map_Ks): red channel >= 0.5 marks mirror texels — inlaid discs on an otherwise diffuse surface."""
+    y, x = np.mgrid[0:size, 0:size].astype(np.float32) / size
+    disc = ((x * 4 % 1 - 0.5) ** 2 + (y * 4 % 1 - 0.5) ** 2) < 0.04
+    out = np.zeros((size, size, 4), np.uint8)
+    out[..., 0] = np.where(disc, 255, 0)
+    out[..., 3] = 255
+    return out
+
+
+ATRIUM_TEXTURE_KIND = {"floor": "tile", "bricks_left": "brick", "bricks_right": "brick", "wall_front": "brick", "wall_back": "brick",
+                       "curtain_red": "fabric", "curtain_green": "fabric", "curtain_blue": "fabric"}
+
+
+def atrium(detail=0.89, with_light=True, seed=1, make_builder=None, textured=False, extra=None):
+    """Sponza stand-in: returns (blobs, info). Materials 0..24 diffuse, 25 = emissive light box at the NEE quad.
+    textured: every material group gets an albedo map (TextureBuffer slot = its material index; `vase` and `lintel_*` a
+    metalness map as well) and planar texture coordinates — the role of assets/sponza.mtl + sponza_textures; the images
+    are in info["texture_images"] {slot: (h, w, 4) uint8} for b200pt_upload_texture. extra: list of
+    (tris, normals, material64) appended as further objects (the C5 statue)."""
     rng = np.random.default_rng(seed)
     groups = {g: [] for g in ATRIUM_GROUPS}
     for name, tris, nrm in atrium_parts(detail):
@@ -174,34 +229,62 @@ def atrium(detail=0.89, with_light=True, seed=1):
             c = np.array([rng.uniform(-2.8, 2.8), rng.uniform(-4.5, 0.3), rng.uniform(-4.8, 8.8)])
             h = rng.uniform(0.03, 0.12, 3)
             groups[g].append(_box(c - h, c + h))
-    b = _builder()
+    b = _builder(make_builder)
     b.set_spheres(np.zeros(320, np.uint8))      # spheres.resize(10): ten zero spheres, always (src/vk_engine.cpp:682)
     albedo = rng.uniform(0.25, 0.9, (25, 3))
     albedo[13], albedo[14], albedo[15] = (0.8, 0.15, 0.12), (0.15, 0.7, 0.2), (0.15, 0.2, 0.8)
-    for a in albedo:
-        b.add_material(_scene.material(albedo=a))
+    images = {}
+    for gi, a in enumerate(albedo):
+        if textured:
+            g = ATRIUM_GROUPS[gi]
+            images[gi] = procedural_texture(ATRIUM_TEXTURE_KIND.get(g, "stone"), 1000 + gi)
+            metal = -1
+            if g in ("vase", "lintel_0", "lintel_1"):
+                metal = 32 + len([k for k in images if k >= 32])
+                images[metal] = metal_mask_texture(gi)
+            b.add_material(_scene.material(albedo=a, albedo_index=gi, metalness_index=metal))
+        else:
+            b.add_material(_scene.material(albedo=a))
     b.add_material(_scene.material(albedo=(0, 0, 0), emission=(1, 1, 1), strength=2.4))     # 25: the reference's light material
     counts = {}
     for gi, g in enumerate(ATRIUM_GROUPS):
         tris = np.concatenate([t for t, _ in groups[g]])
         nrm = np.concatenate([n for _, n in groups[g]])
         counts[g] = len(tris)
-        b.add_mesh(_pack(tris, nrm), material=gi)
+        b.add_mesh(_pack(tris, nrm, uv_scale=0.5 if textured else None), material=gi)
     if with_light:
         t, n = _box([-1 / 3, -1.52, -1 / 3], [1 / 3, -1.5, 1 / 3])
         b.add_mesh(_pack(t, n), material=25)
         counts["light"] = len(t)
+    for k, (t, n, mat64) in enumerate(extra or []):
+        b.add_material(mat64)
+        b.add_mesh(_pack(t, n), material=26 + k)
+        counts["extra_%d" % k] = len(t)
     blobs = b.blobs()
     info = dict(triangles=int(sum(counts.values())), objects=len(counts), groups=counts, stand_in_for="sponza.obj")
+    if textured:
+        info["texture_images"] = images
+        info["textures"] = "%d procedural albedo maps 1024x1024 + %d metalness maps (stand-ins for assets/sponza_textures), planar uv, sampler 0 (REPEAT)" % (
+            len([k for k in images if k < 32]), len([k for k in images if k >= 32]))
     return blobs, info
 
 
-def statue_room(triangles=800_000, statue_material=4, seed=7):
+def atrium_with_statue(triangles=800_000, make_builder=None, seed=7):
+    """C5 stand-in ("Sponza + dragon", BASELINE.json configs[4]): the atrium with one high-polygon mirror statue (the C3
+    stand-in's bumpy blob, ~`triangles` triangles, the reference's mirror material) standing in the nave."""
+    n = max(8, int(round((triangles / 2) ** 0.5)))
+    st, sn = _blob([0.0, -0.45, 2.2], 0.9, n, n, 0.22, seed=seed, outward=True)
+    blobs, info = atrium(make_builder=make_builder, extra=[(st, sn, _scene.material(albedo=(1, 0.84, 0.3), reflectance=1.0))])
+    info["stand_in_for"] = "sponza.obj + dragon.obj"
+    return blobs, info
+
+
+def statue_room(triangles=800_000, statue_material=4, seed=7, make_builder=None):
     """C3 stand-in (dragon.obj is not in the reference checkout): a Cornell-style room - white floor/ceiling/back,
     red and green side walls, the reference's light material on a box at the hard-wired NEE quad - around one
     high-polygon statue (bumpy blob, ~`triangles` triangles) with the reference's mirror material 4 (gold-metal
     dragon preset) or dielectric 5. Materials 0..5 are the reference's defaults (src/vk_engine.cpp:689-722)."""
-    b = _builder()
+    b = _builder(make_builder)
     b.set_spheres(np.zeros(320, np.uint8))
     b.add_material(_scene.material(albedo=(1, 1, 1)))
     b.add_material(_scene.material(albedo=(1, 0, 0)))
@@ -222,14 +305,14 @@ def statue_room(triangles=800_000, statue_material=4, seed=7):
     return b.blobs(), info
 
 
-def soup(n, seed=0x5EED, edge=0.01):
+def soup(n, seed=0x5EED, edge=0.01, make_builder=None):
     """n random triangles, centres uniform in [-1,1]^3, one object, material 0 (diffuse white)."""
     rng = np.random.default_rng(seed)
     c = rng.uniform(-1, 1, (n, 1, 3))
     p = c + rng.uniform(-edge, edge, (n, 3, 3))
     fn = np.cross(p[:, 1] - p[:, 0], p[:, 2] - p[:, 0])
     fn /= np.maximum(np.linalg.norm(fn, axis=1, keepdims=True), 1e-30)
-    b = _builder()
+    b = _builder(make_builder)
     b.add_material(_scene.material())
     b.add_mesh(_pack(p, np.repeat(fn[:, None, :], 3, 1)), material=0)
     return b.blobs(), dict(triangles=n, objects=1)
