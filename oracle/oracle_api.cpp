@@ -108,6 +108,13 @@ int orc_trace_batch(void* scene, const void* pc208, const float* rays, uint64_t 
     return 0;
 }
 
+int orc_pixel_ties(void* scene, const void* pc208, int W, int H, uint32_t frame, const uint32_t* xy, uint64_t n, uint32_t* ties) {
+    ol::PushConstants pc;
+    std::memcpy(&pc, pc208, sizeof(pc));
+    pixel_ties(*(Scene*)scene, pc, W, H, frame, xy, (size_t)n, ties);
+    return 0;
+}
+
 void orc_set_math_mode(int mode) { orc::set_math_mode(mode); }
 int orc_math_mode() { return orc::math_mode(); }
 float orc_random(uint32_t* state) { return orc::random(*state); }

@@ -60,6 +60,11 @@ struct Ctx {
     const ol::PushConstants& pc;
     Work work;      // all rays
     Work ext;       // extension rays only (the calls from trace(), raytrace.comp:493): roofline of the extend stage
+    // Tie detector (tests only, pixel_ties()): counts rays whose closest hit was met at EXACTLY the same distance on two
+    // triangles of one object — the one documented class where a traversal in another order may keep the other triangle
+    // (the reference keeps the first in its own loop order, raytrace.comp:316). Does not change any result.
+    bool detectTies = false;
+    uint32_t ties = 0;
 };
 
 vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
@@ -182,6 +187,7 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
     const ol::RayTracerData& traceData = cx.pc.rayTraceParams;
     const Work before = cx.work;
     cx.work.n_ray++;
+    float tieDst = -1.f;
 
     for (uint32_t i = 0; i < traceData.sphereCount; i++) {
         cx.work.n_sph++;
@@ -217,6 +223,9 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
                                                            sc.points[tri.v2], object.smoothShade != 0,
                                                            tri.frontOnly != 0);
                     hitInfo.materialIndex = object.materialIndex;
+                    if (cx.detectTies && hitInfo.didHit && closestHit.didHit && closestHit.kind == 2 && closestHit.objectHitIndex == i &&
+                        hitInfo.dst == closestHit.dst)
+                        tieDst = hitInfo.dst;
 
                     if (hitInfo.didHit && hitInfo.dst < closestHit.dst) {
                         closestHit = hitInfo;
@@ -253,6 +262,7 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
     }
 
     if (closestHit.didHit) cx.work.n_hit++;
+    if (cx.detectTies && closestHit.didHit && closestHit.kind == 2 && tieDst == closestHit.dst) cx.ties++;
     if (stats) {
         cx.ext.n_box += cx.work.n_box - before.n_box; cx.ext.n_tri += cx.work.n_tri - before.n_tri;
         cx.ext.n_obj += cx.work.n_obj - before.n_obj; cx.ext.n_sph += cx.work.n_sph - before.n_sph;
@@ -660,6 +670,23 @@ void render_window(const Scene& sc, const ol::PushConstants& pc_in, int W, int H
     }
     if (work) work->add(total);
     if (workExt) workExt->add(totalExt);
+}
+
+// For each listed pixel (x, y) of frame `frame`: how many rays of its path (extension, NEE and pdf rays alike) met their
+// closest hit at exactly the same distance on two triangles of one object. A pixel whose image value differs between two
+// correct traversals in different orders must have at least one (tests/test_gpu_parity.py: every differing pixel is
+// explained, none is merely budgeted).
+void pixel_ties(const Scene& sc, const ol::PushConstants& pc_in, int W, int H, uint32_t frame, const uint32_t* xy, size_t n,
+                uint32_t* ties) {
+    ol::PushConstants pc = pc_in;
+    pc.frameCount = frame;
+#pragma omp parallel for schedule(dynamic, 16)
+    for (long long i = 0; i < (long long)n; ++i) {
+        Ctx cx{sc, pc, Work(), Work()};
+        cx.detectTies = true;
+        shade_pixel(cx, xy[2 * i], xy[2 * i + 1], W, H);
+        ties[i] = cx.ties;
+    }
 }
 
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out, Work* work,

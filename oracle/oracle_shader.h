@@ -81,6 +81,10 @@ void render_frames(const Scene& sc, const ol::PushConstants& pc, int W, int H, u
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out,
                  Work* work, int threads);
 
+// tie detector: see oracle_shader.cpp
+void pixel_ties(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t frame, const uint32_t* xy, size_t n,
+                uint32_t* ties);
+
 // 0 = libm transcendentals (default), 1 = the backend's portable double-precision polynomials
 void set_math_mode(int mode);
 int math_mode();

@@ -46,6 +46,7 @@ def lib():
         L.orc_scene_use_textures.argtypes = [vp, i32]
         L.orc_render_window.argtypes = [vp, vp, i32, i32, u32, u32, i32, i32, i32, i32, i32, i32, vp, vp, i32]
         L.orc_trace_batch.argtypes = [vp, vp, vp, u64, vp, vp, i32]
+        L.orc_pixel_ties.argtypes = [vp, vp, i32, i32, u32, vp, u64, vp]
         L.orc_random.restype = f32
         L.orc_random.argtypes = [C.POINTER(u32)]
         L.orc_starting_seed.restype = u32
@@ -152,6 +153,16 @@ class OracleScene:
         if want_work:
             return accum, dict(zip(WORK_FIELDS, work[:8].tolist())), dict(zip(WORK_FIELDS, work[8:].tolist()))
         return accum
+
+    def pixel_ties(self, pc, W, H, frame, xy):
+        """For pixels xy (n, 2) of frame `frame`: number of rays on the pixel's path whose closest hit lies at exactly the
+        same distance on two triangles of one object (the documented tie class)."""
+        pcb = self._pc(pc)
+        xy = np.ascontiguousarray(xy, np.uint32).reshape(-1, 2)
+        out = np.zeros(xy.shape[0], np.uint32)
+        if xy.shape[0]:
+            lib().orc_pixel_ties(self.h, _ptr(pcb), W, H, frame, _ptr(xy), xy.shape[0], _ptr(out))
+        return out
 
     def trace_batch(self, pc, rays, threads=0):
         pcb = self._pc(pc)

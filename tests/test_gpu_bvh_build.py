@@ -1,6 +1,8 @@
-"""b200pt_build_bvh (CUDA) against the host restatement of VulkanEngine::build_bvh (src/vk_engine.cpp:1169-1337,
-ray_tracer_b200/host/scene_builder.cpp, itself byte-identical to the oracle's builder: tests/test_scene_builder.py).
-The bar is bit-exact: same node bytes, same node order, same final triangle order."""
+"""b200pt_build_bvh (CUDA) against the ORACLE's builder (oracle/oracle_scene.cpp: the restatement of
+VulkanEngine::build_bvh, src/vk_engine.cpp:1169-1337, which tests/test_ref_engine.py pins to the reference's own
+build_bvh / subdivide_bvh / find_bvh_split_plane compiled from its source). The product's host builder
+(ray_tracer_b200/host/scene_builder.cpp) only carries the meshes to the CUDA entry point here; it is itself compared
+with the oracle as a third column. The bar is bit-exact: same node bytes, same node order, same final triangle order."""
 import os
 import sys
 
@@ -22,7 +24,14 @@ def _face_vertices(tris):
 
 
 def _both(meshes, min_triangles=1):
+    """-> (oracle blobs, blobs with every BVH2 built by b200pt_build_bvh, stats)."""
+    import oracle_binding as ob
     from ray_tracer_b200 import scene
+    o = ob.OracleBuilder()
+    o.add_material(scene.material())
+    for m in meshes:
+        o.add_mesh(_face_vertices(np.asarray(m, np.float32)), material=0)
+    want = o.blobs()
     blobs = []
     for gpu in (False, True):
         b = scene.SceneBuilder()
@@ -34,7 +43,8 @@ def _both(meshes, min_triangles=1):
         blobs.append(b.blobs())
         if gpu:
             stats = b.gpu_bvh_stats()
-    return blobs[0], blobs[1], stats
+    _assert_same(want, blobs[0])          # the product's host builder, for completeness
+    return want, blobs[1], stats
 
 
 def _assert_same(host, dev):
@@ -94,9 +104,10 @@ def test_soup(n):
 
 def test_statue_and_atrium_scenes_through_the_builder_hook(monkeypatch):
     # the bench scenes, every object with >= 64 triangles built on the GPU: blobs identical to the host build
+    import oracle_binding as ob
     from ray_tracer_b200 import scene, scenes
-    host_atrium, _ = scenes.atrium()
-    host_statue, _ = scenes.statue_room(200_000)
+    host_atrium, _ = scenes.atrium(make_builder=ob.OracleBuilder)          # the oracle's builder, not the product's
+    host_statue, _ = scenes.statue_room(200_000, make_builder=ob.OracleBuilder)
     real = scene.SceneBuilder
 
     class GpuBuilder(real):

@@ -41,6 +41,34 @@ def _differing(a, b):
     return float((a.view(np.uint32) != b.view(np.uint32)).any(axis=2).mean())
 
 
+def _assert_explained(blobs, pc, W, H, frames, got, want, x0=0, y0=0, sx=1, sy=1, textures=None):
+    """got / want: images of the pixels (x0 + i*sx, y0 + j*sy) of the W x H image built from the frames in `frames`
+    (accumulated, or blended by progressive dispatches). Bit-exact is the bar; a pixel may differ only if a ray on its
+    path — in one of those frames — met its closest hit at EXACTLY the same distance on two triangles of one object (the
+    one documented tie class, DESIGN.md §4 item 5: which of the two wins depends on the order a traversal meets them).
+    Every differing pixel is re-traced by the oracle's tie detector (oracle_shader.cpp: pixel_ties) and must show such a
+    ray; and there may be no more than 1e-4 of them (two for small images)."""
+    diff = (np.ascontiguousarray(got).view(np.uint32) != np.ascontiguousarray(want).view(np.uint32)).any(axis=2)
+    nd = int(diff.sum())
+    if nd == 0:
+        return 0
+    frames = list(frames)
+    assert nd <= max(2, 1e-4 * diff.size * len(frames)), "%d of %d pixels differ" % (nd, diff.size)
+    ys, xs = np.nonzero(diff)
+    xy = np.stack([x0 + xs * sx, y0 + ys * sy], 1).astype(np.uint32)
+    sc = ob.OracleScene(blobs)
+    for slot, t in (textures or {}).items():
+        sc.set_texture(slot, t)
+    if textures:
+        sc.use_textures(True)
+    ties = np.zeros(len(xy), np.int64)
+    with ob.math_mode(1):
+        for f in frames:
+            ties += sc.pixel_ties(pc, W, H, f, xy)
+    assert (ties > 0).all(), "pixels differ with no equal-distance tie on their path: %s" % xy[ties == 0][:8].tolist()
+    return nd
+
+
 def _same_hits(got, want):
     return ((got["kind"] == want["kind"]) & (got["objectHitIndex"] == want["objectHitIndex"]) &
             (got["triHitIndex"] == want["triHitIndex"]) & (got["dst"].view(np.uint32) == want["dst"].view(np.uint32)))
@@ -100,8 +128,7 @@ def test_radiance_cornell_c1(gpu, cornell_blobs, pipeline):
     got = cp.read_accum()
     assert np.array_equal(got[..., 3], np.full((H, W), 16, np.float32))
     assert relrmse(got[..., :3], libm[..., :3]) <= 1e-3          # tolerance stated by BASELINE.json
-    diff = (got.view(np.uint32) != exact.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 1e-4, diff.mean()                      # bit-exact apart from equal-distance ties
+    _assert_explained(cornell_blobs, pc, W, H, range(16), got, exact)     # bit-exact apart from explained equal-distance ties
     assert relrmse(got[..., :3], exact[..., :3]) <= 1e-5
 
 
@@ -115,8 +142,7 @@ def test_radiance_bunny_env(gpu, bunny_blobs):
     cp = _pass(gpu, bunny_blobs, W, H)
     cp.render_frames(pc, 3, 6)
     got = cp.read_accum()
-    diff = (got.view(np.uint32) != exact.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 1e-4, diff.mean()
+    _assert_explained(bunny_blobs, pc, W, H, range(3, 9), got, exact)
     assert relrmse(got[..., :3], exact[..., :3]) <= 1e-5
 
 
@@ -163,7 +189,7 @@ def test_update_buffers_and_errors(gpu, cornell_blobs):
         want, _ = ob.OracleScene(blobs2).render_frames(pc, W, H, 0, 2)
     cp.render_frames(pc, 0, 2)
     got = cp.read_accum()
-    assert (got.view(np.uint32) != want.view(np.uint32)).any(axis=2).mean() <= 1e-3
+    _assert_explained(blobs2, pc, W, H, range(2), got, want)
     # objects: move the first cube (UI "update objects")
     objs = cornell_blobs["objects"].copy()
     objs.view(np.float32)[12] += 0.1
@@ -173,7 +199,7 @@ def test_update_buffers_and_errors(gpu, cornell_blobs):
     with ob.math_mode(1):
         want, _ = ob.OracleScene(blobs3).render_frames(pc, W, H, 0, 2)
     cp.render_frames(pc, 0, 2)
-    assert (cp.read_accum().view(np.uint32) != want.view(np.uint32)).any(axis=2).mean() <= 1e-3
+    _assert_explained(blobs3, pc, W, H, range(2), cp.read_accum(), want)
     # error behaviour: status + message, never abort
     with pytest.raises(gpu.BackendError, match="count"):
         cp.update_buffer("materials", mats[:64])
@@ -244,7 +270,7 @@ def test_full_size_properties_c4(gpu):
         for k, v in opts.items():
             cp.set_option(k, v)
         cp.render_frames(pc.buffer, 0, 4)
-        assert _differing(cp.read_accum(), whole) <= 1e-5, opts
+        assert _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole) <= 20, opts
     cp.set_option("frames_in_flight", 4)
     cp.clear()
     cp.render_frames(pc.buffer, 0, 2, frame_stride=2)
@@ -255,7 +281,10 @@ def test_full_size_properties_c4(gpu):
     cp.clear()
     cp.render_frames(pc.buffer, 0, 4, rows=(0, 377))
     cp.render_frames(pc.buffer, 0, 4, rows=(377, H))
-    assert _differing(cp.read_accum(), whole) <= 1e-5
+    assert _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole) <= 20
+    # BASELINE.json's bar for C4 ("the image within RMSE 1e-3"): the 4-frame image against the libm oracle (= the
+    # reference's shader text) on a 96 x 54 lattice of the full 1920 x 1080 image
+    _lattice_check(whole, blobs, pc.buffer, W, H, 4, 96, 54)
     # the oracle on a window of the same image: 64 x 48 pixels around the centre, 1 frame, bit-exact apart from ties
     # (a window, not a sub-sampled grid: seeds and rays depend on x, y, W and H)
     cp.clear()
@@ -264,12 +293,32 @@ def test_full_size_properties_c4(gpu):
     with ob.math_mode(1):
         want = ob.OracleScene(blobs).render_window(pc.buffer, W, H, 0, 928, 516, 64, 48)
     got = one[516:564, 928:992]
-    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 2e-3, diff.mean()
+    _assert_explained(blobs, pc.buffer, W, H, [0], got, want, x0=928, y0=516)
 
 
-def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, tie_budget):
-    """Accumulated `frames` frames of the full image on the GPU against the oracle on one window of it."""
+def _lattice_check(acc, blobs, pc, W, H, frames, nx, ny):
+    """BASELINE.json's bar on the FULL image: relative RMSE <= 1e-3 at equal spp and seeds against the libm oracle (and
+    against the reference's own shader text where oracle/_ref/libraytrace_comp.so is in the tree), on a lattice of
+    nx x ny pixels spread over the whole W x H image."""
+    sx, sy = W // nx, H // ny
+    got = acc[0:ny * sy:sy, 0:nx * sx:sx][:ny, :nx]
+    sc = ob.OracleScene(blobs)
+    libm = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
+    rel = relrmse(got[..., :3], libm[..., :3])
+    assert rel <= 1e-3, rel                                     # tolerance stated by BASELINE.json
+    import ref_shader_binding as rb
+    if rb.available():
+        ref = rb.RefShaderScene(blobs).render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
+        assert np.array_equal(ref.view(np.uint32), libm.view(np.uint32))        # the oracle IS the reference's shader text
+    with ob.math_mode(1):
+        exact = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
+    _assert_explained(blobs, pc, W, H, range(frames), got, exact, sx=sx, sy=sy)
+    return rel
+
+
+def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, lattice=(96, 54)):
+    """Accumulated `frames` frames of the full image on the GPU: bit-exact against the oracle (portable math) on one dense
+    window apart from explained ties, and within relRMSE 1e-3 of the libm oracle on a lattice over the whole image."""
     cp.clear()
     cp.render_frames(pc, 0, frames)
     acc = cp.read_accum()
@@ -277,13 +326,9 @@ def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, tie_budget):
     with ob.math_mode(1):
         want = ob.OracleScene(blobs).render_window(pc, W, H, 0, x0, y0, w, h, n=frames)
     got = acc[y0:y0 + h, x0:x0 + w]
-    if frames == 1:
-        diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
-        assert diff.mean() <= tie_budget, diff.mean()
-    else:                                                   # frame sums: equal up to fp32 summation of equal terms
-        assert relrmse(got[..., :3], want[..., :3]) <= 1e-3
-        close = np.isclose(got, want, rtol=1e-5, atol=1e-6).all(axis=2)
-        assert (~close).mean() <= tie_budget, (~close).mean()
+    _assert_explained(blobs, pc, W, H, range(frames), got, want, x0=x0, y0=y0)      # frames are summed in frame order on both sides
+    if lattice:
+        _lattice_check(acc, blobs, pc, W, H, frames, *lattice)
     return acc
 
 
@@ -292,7 +337,7 @@ def test_full_size_c2_bunny(gpu, bunny_blobs):
     W = H = 1024
     pc = ob.default_push_constants(W, H, 10, bunny_blobs["objects"].size // 80)
     cp = _pass(gpu, bunny_blobs, W, H)
-    acc = _window_check(cp, bunny_blobs, pc, W, H, 64, 480, 470, 40, 40, 5e-3)
+    acc = _window_check(cp, bunny_blobs, pc, W, H, 64, 480, 470, 40, 40, lattice=(64, 64))
     assert acc[..., :3].mean() / 64 > 0.01
     c = cp.counters()
     assert c["paths"] == 64 * W * H
@@ -307,15 +352,31 @@ def test_full_size_c3_c5_statue_stand_in(gpu):
     W, H = 1920, 1080
     pc = PushConstants(W, H, 10, info["objects"])
     cp = _pass(gpu, blobs, W, H)
-    _window_check(cp, blobs, pc.buffer, W, H, 1, 930, 500, 64, 48, 5e-3)       # the statue's silhouette
-    _window_check(cp, blobs, pc.buffer, W, H, 4, 700, 800, 48, 32, 5e-3)       # floor in front of it, 4 frames
+    _window_check(cp, blobs, pc.buffer, W, H, 1, 930, 500, 64, 48, lattice=None)   # the statue's silhouette
+    _window_check(cp, blobs, pc.buffer, W, H, 4, 700, 800, 48, 32)                 # floor in front of it, 4 frames + C3 lattice
     W, H = 3840, 2160
     blobs5, info5 = scenes.statue_room(800_000, statue_material=5)             # dielectric: longest paths
     pc = PushConstants(W, H, 10, info5["objects"])
     pc["bounceLimit"] = 16
     cp = _pass(gpu, blobs5, W, H)
     cp.set_option("frames_in_flight", 2)
-    _window_check(cp, blobs5, pc.buffer, W, H, 1, 1900, 1000, 64, 40, 5e-3)
+    _window_check(cp, blobs5, pc.buffer, W, H, 1, 1900, 1000, 64, 40, lattice=None)
+
+
+def test_full_size_c5_stand_in(gpu):
+    # configs[4] at its full size on the labelled stand-in: atrium + mirror statue (~1.06 M triangles, 27 objects),
+    # 3840 x 2160, depth 16, environment on: a dense window on the statue, and the relRMSE bar on a lattice of the image
+    from ray_tracer_b200 import PushConstants, scenes
+    blobs, info = scenes.atrium_with_statue()
+    W, H = 3840, 2160
+    pc = PushConstants(W, H, blobs["spheres"].size // 32, info["objects"])
+    scenes.atrium_camera(pc)
+    pc["bounceLimit"] = 16
+    cp = _pass(gpu, blobs, W, H)
+    cp.set_option("frames_in_flight", 2)
+    acc = _window_check(cp, blobs, pc.buffer, W, H, 2, 1900, 1100, 48, 32, lattice=(96, 54))
+    assert acc[..., :3].mean() / 2 > 0.01
+    cp.close()
 
 
 def _textured_scene():
@@ -375,13 +436,12 @@ def test_texture_extension(gpu):
     assert relrmse(want[..., :3], plain[..., :3]) > 0.05               # the maps do change the image
     cp.render_frames(pc, 0, 4)                                         # option off: uploaded textures are ignored (HEAD behaviour)
     got = cp.read_accum()
-    assert (got.view(np.uint32) != plain.view(np.uint32)).any(axis=2).mean() <= 1e-4
+    _assert_explained(blobs, pc, W, H, range(4), got, plain)
     cp.clear()
     cp.set_option("textures", 1)
     cp.render_frames(pc, 0, 4)
     got = cp.read_accum()
-    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 1e-4, diff.mean()
+    _assert_explained(blobs, pc, W, H, range(4), got, want, textures=textures)
     assert relrmse(got[..., :3], want[..., :3]) <= 1e-5
 
 
@@ -398,8 +458,7 @@ def test_depth16_and_deep_roulette(gpu, bunny_blobs):
     cp.set_option("frames_in_flight", 2)
     cp.render_frames(pc, 0, 3)
     got = cp.read_accum()
-    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 1e-4, diff.mean()
+    _assert_explained(bunny_blobs, pc, W, H, range(3), got, want)
     # bounceLimit 0: primary hit only (emission at j == 0), no connect, no second extend
     pc.view(np.uint32)[44] = 0
     with ob.math_mode(1):
@@ -422,8 +481,7 @@ def test_non_finite_emission_disables_nee_shortcut(gpu, cornell_blobs):
     cp = _pass(gpu, blobs, W, H)
     cp.render_frames(pc, 0, 3)
     got = cp.read_accum()
-    diff = (got.view(np.uint32) != want.view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 1e-3, diff.mean()
+    _assert_explained(blobs, pc, W, H, range(3), got, want)
 
 
 def test_storage_rgba8_progressive(gpu, cornell_blobs):
@@ -466,8 +524,7 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
             assert (cp.get_option("last_wide_device_us") > 0) == bool(mode)
             cp.render_frames(pc, 0, 6)
             imgs.append(cp.read_accum())
-        diff = (imgs[0].view(np.uint32) != imgs[1].view(np.uint32)).any(axis=2)
-        assert diff.mean() <= 2e-3, diff.mean()              # the documented same-object equal-distance tie class only
+        _assert_explained(blobs, pc, W, H, range(6), imgs[0], imgs[1])     # the documented same-object equal-distance tie class only
         assert np.isfinite(imgs[1]).all()
     # an object moved after upload: the tree is rebuilt on the device and agrees with a fresh upload
     blobs, pc, W, H = cases[1]
@@ -482,8 +539,7 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
     cp2 = gpu.ComputePass(W, H)
     cp2.copy_buffers(dict(blobs, objects=moved))
     cp2.render_frames(pc, 0, 3)
-    diff = (a.view(np.uint32) != cp2.read_accum().view(np.uint32)).any(axis=2)
-    assert diff.mean() <= 2e-3, diff.mean()
+    _assert_explained(dict(blobs, objects=moved), pc, W, H, range(3), a, cp2.read_accum())
 
 
 def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, bunny_blobs):
@@ -504,7 +560,8 @@ def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, b
                 fast.run_compute(pc)
                 slow.run_compute(pc)
         a, b = fast.read_image(), slow.read_image()
-        assert _differing(a, b) <= 2e-3 and _differing(a, image) <= 2e-3
+        assert np.array_equal(b.view(np.uint32), image.view(np.uint32))            # reference-order kernel: no tie class at all
+        _assert_explained(blobs, pc, W, H, range(4), a, image)
         assert fast.counters()["paths"] == 4 * W * H and fast.counters()["extension_rays"] > 4 * W * H
         assert np.array_equal(fast.read_rgba8(), np.clip(np.rint(np.clip(a, 0, 1) * 255), 0, 255).astype(np.uint8))
         # not progressive: the image is replaced; storage at 8-bit precision
@@ -513,7 +570,7 @@ def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, b
             cp.set_option("storage_rgba8", 1)
             cp.run_compute(pc)
         a, b = fast.read_image(), slow.read_image()
-        assert _differing(a, b) <= 2e-3
+        _assert_explained(blobs, pc, W, H, [3], a, b)
         assert np.array_equal(a[..., :3], np.rint(a[..., :3] * 255) / np.float32(255))
 
 
@@ -542,8 +599,8 @@ def test_multi_sample_dispatches_share_the_rng_stream(gpu, cornell_blobs):
                 fast.run_compute(pc)
                 slow.run_compute(pc)
         a, b = fast.read_image(), slow.read_image()
-        assert _differing(a, b) <= 2e-3, (rpp, single)
-        assert _differing(a, image) <= 2e-3, (rpp, single)
+        assert np.array_equal(b.view(np.uint32), image.view(np.uint32)), (rpp, single)
+        _assert_explained(cornell_blobs, pc, W, H, range(2), a, image)
         assert fast.counters()["paths"] == 2 * rpp * W * H
     # accumulated progressive frames with 2 samples each, several frames in flight
     pc = ob.default_push_constants(W, H, 10, 9)
@@ -554,7 +611,7 @@ def test_multi_sample_dispatches_share_the_rng_stream(gpu, cornell_blobs):
     slow.render_frames(pc, 0, 5)
     a, b = fast.read_accum(), slow.read_accum()
     assert np.array_equal(a[..., 3], np.full((H, W), 5, np.float32))
-    assert _differing(a, b) <= 2e-3
+    _assert_explained(cornell_blobs, pc, W, H, range(5), a, b)
 
 
 def test_material_and_sphere_updates_rebuild_only_when_needed(gpu, cornell_blobs):
@@ -569,7 +626,7 @@ def test_material_and_sphere_updates_rebuild_only_when_needed(gpu, cornell_blobs
         cp.render_frames(pc, 0, 3)
         with ob.math_mode(1):
             want, _ = ob.OracleScene(blobs).render_frames(pc, W, H, 0, 3)
-        assert _differing(cp.read_accum(), want) <= 2e-3
+        _assert_explained(blobs, pc, W, H, range(3), cp.read_accum(), want)
 
     mats = cornell_blobs["materials"].copy()
     mats.view(np.float32).reshape(-1, 16)[1, 0:3] = (0.1, 0.8, 0.3)          # recolour: nothing moves between the trees
@@ -613,7 +670,7 @@ def test_connect_chain_on_a_second_stream_gives_the_same_image(gpu, bunny_blobs)
     want = images[(0, 1)]
     assert want[..., 3].min() == 6
     for key, img in images.items():
-        assert _differing(img, want) <= 1e-4, key
+        _assert_explained(bunny_blobs, pc, W, H, range(6), img, want)
     with ob.math_mode(1):
         exact, _ = ob.OracleScene(bunny_blobs).render_frames(pc, W, H, 0, 6)
-    assert _differing(images[(1, 1)], exact) <= 1e-4
+    _assert_explained(bunny_blobs, pc, W, H, range(6), images[(1, 1)], exact)
