@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--textures", type=int, default=0, help="1: texture extension on, procedural albedo maps bound to the atrium's materials")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", default="480x270x12", help="WxHxframes of the CPU baseline sample")
+    ap.add_argument("--parity-sample", default="64x36x1024", help="WxHxframes of the parity lattice: C4's own 1024 spp on every 30th pixel")
     ap.add_argument("--strong-spp", type=int, default=1024, help="frames of the strong-scaling leg (0 = skip)")
     ap.add_argument("--c5-frames", type=int, default=24, help="frames per GPU of the C5 leg (0 = skip)")
     ap.add_argument("--only-value", action="store_true", help="skip every leg but the timed value (short runs under ncu)")
@@ -544,27 +545,31 @@ def main():
     pc["frameCount"] = 0
     cp.set_option("frames_in_flight", max(1, min(64, F)))
 
-    # ---- parity of this run's own output: frames 0..n-1 of the cpu_baseline lattice, rendered here at full size
+    # ---- CPU baseline (timing) and parity of this run's own output at the configuration's OWN sample count: the lattice
+    # pixels of the full image, frames 0 .. n-1, rendered here (whole rows, every sy-th) and by the CPU reference
     cpu = parity = None
-    r = None
-    if rank == 0:
-        if N == 1 and not args.no_cpu_baseline:
-            r = cpu_reference_sample(blobs, pc, W, H, args.cpu_sample, textures=info.get("texture_images"))
-            cpu = dict(value=r["mpaths"], unit=UNIT, cores=r["cores"], kind=r["kind"],
-                       sample="%s; %.1f s, OpenMP over rows, all host cores" % (r["lattice"], r["seconds"]),
-                       what="shaders/raytrace.comp compiled for the CPU (oracle/_ref/libraytrace_comp.so)" if r["kind"] == "reference"
-                            else "oracle/liboracle.so (hand-written restatement)")
-    if N == 1 and r is not None:
-        w, h, n, sx, sy = r["lattice_shape"]
+    if rank == 0 and N == 1 and not args.no_cpu_baseline:
+        r = cpu_reference_sample(blobs, pc, W, H, args.cpu_sample, textures=info.get("texture_images"))
+        cpu = dict(value=r["mpaths"], unit=UNIT, cores=r["cores"], kind=r["kind"],
+                   sample="%s; %.1f s, OpenMP over rows, all host cores" % (r["lattice"], r["seconds"]),
+                   what="shaders/raytrace.comp compiled for the CPU (oracle/_ref/libraytrace_comp.so)" if r["kind"] == "reference"
+                        else "oracle/liboracle.so (hand-written restatement)")
+        w, h, n, sx, sy = _lattice(W, H, args.parity_sample)
         cp.clear()
-        cp.render_frames(pcbuf, 0, n)
+        cp.render_frames(pcbuf, 0, n, rows=(0, H), row_stride=sy)
         got = cp.read_accum()[0:h * sy:sy, 0:w * sx:sx][:h, :w]
-        ref = r["image"]
+        rp = cpu_reference_sample(blobs, pc, W, H, args.parity_sample, textures=info.get("texture_images"))
+        ref = rp["image"]
         a, b = got[..., :3].astype(np.float64), ref[..., :3].astype(np.float64)
         rel = float(np.sqrt(np.mean((a - b) ** 2)) / np.mean(b))
-        parity = dict(rel_rmse=rel, tolerance=1e-3, ok=bool(rel <= 1e-3), frames=n, pixels=w * h,
-                      against="%s (libm transcendentals), %s" % (cpu["what"], r["lattice"]),
-                      pixels_bit_equal=float((got.view(np.uint32) == ref.view(np.uint32)).all(axis=2).mean()))
+        err = np.abs(a - b).max(axis=2) / n
+        parity = dict(rel_rmse=rel, tolerance=1e-3, ok=bool(rel <= 1e-3), spp=n, pixels=w * h,
+                      against="%s (host libm transcendentals), %s" % (
+                          "shaders/raytrace.comp compiled for the CPU (oracle/_ref/libraytrace_comp.so)" if rp["kind"] == "reference" else "oracle/liboracle.so", rp["lattice"]),
+                      pixels_bit_equal=float((got.view(np.uint32) == ref.view(np.uint32)).all(axis=2).mean()),
+                      max_abs_error_of_the_mean=float(err.max()), mean_radiance=float(b.mean() / n), cpu_seconds=rp["seconds"],
+                      note="GPU kernels use their own sin/cos/pow/tan (<= 1 ulp from libm); a last-bit difference in a sampled direction can send a "
+                           "path to another triangle after a few bounces on curved geometry, so individual paths differ while the estimate agrees")
 
     # ---- C5 of BASELINE.json: atrium + statue, 3840x2160, depth 16 (frames split over the ranks + reduce)
     c5 = None
