@@ -192,18 +192,18 @@ PT_HD bool nee_cannot_contribute(const WideScene& sc, const float4& qa, v3 light
 // misWeight, and misWeight is only read at the NEXT hit as emission / misWeight, which trace() uses only when
 // directLight.x == -1 (raytrace.comp:499-500; at j == 0 misWeight is still 1). After a diffuse bounce directLight is
 // the NEE result, so that pdf ray is dead unless the NEE result is EXACTLY -1.0f. It is therefore evaluated lazily:
-// stage_connect_finish reports that rare case and connect_mis_weight_exact() then runs both parts of the query.
+// connect_job_finish reports that rare case and connect_mis_weight_exact() then runs both parts of the query.
 PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p, uint32_t j) {
     const ptl::RayTracerData& td = P.pc.params;
     float4 ro = A.rayO[p], rd = A.rayD[p];
     Ray ray; ray.o = xyz(ro); ray.d = xyz(rd);
     float misWeight = ro.w;
     uint32_t state = as_uint(rd.w);
-    v3 total = xyz(A.total[p]), atten = xyz(A.atten[p]), direct = xyz(A.direct[p]);
+    v3 atten = xyz(A.atten[p]), direct = xyz(A.direct[p]);
     const Hit h = A.hit[(j == 0 && P.sharePrimary) ? p % (P.rows * (uint32_t)P.W) : p];
 
     if (h.id == PT_HIT_MISS) {                                   // raytrace.comp:531-534
-        total = total + atten * environment_light(P.pc.env, ray.d);
+        v3 total = xyz(A.total[p]) + atten * environment_light(P.pc.env, ray.d);
         A.total[p] = f4(total, 0.f);
         return 0u;
     }
@@ -213,13 +213,19 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 
     v3 emission = mk3(mat.emissionColor[0], mat.emissionColor[1], mat.emissionColor[2]) * mat.emissionStrength / misWeight;
     v3 finalLight = direct.x == -1.f ? emission : direct;        // :499-500
-    total = total + finalLight * atten;
-    if (j == 0) total = total + emission;
-    if (isnan3(total) || total.x < 0.f || total.y < 0.f || total.z < 0.f) {   // :505 — the whole path returns 0
-        A.total[p] = make_float4(0.f, 0.f, 0.f, 0.f);
-        return 0u;
+    // totalColor is read and written only when this hit changes it. Adding a zero leaves it as it is (it is never -0:
+    // it starts at +0 and only grows), and it already passed the guard of :505 at the bounce before; a NaN term is not
+    // a zero and takes the full path. Most bounces of an interior add nothing (no direct light, no emission).
+    const v3 gain = finalLight * atten;
+    if (j == 0 || !(gain.x == 0.f && gain.y == 0.f && gain.z == 0.f)) {
+        v3 total = xyz(A.total[p]) + gain;
+        if (j == 0) total = total + emission;
+        if (isnan3(total) || total.x < 0.f || total.y < 0.f || total.z < 0.f) {   // :505 — the whole path returns 0
+            A.total[p] = make_float4(0.f, 0.f, 0.f, 0.f);
+            return 0u;
+        }
+        A.total[p] = f4(total, 0.f);
     }
-    A.total[p] = f4(total, 0.f);
 
     v3 dirOut, radiance;
     float originSign = 1.f, nextMis = 1.f;
@@ -252,7 +258,9 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
             A.qO[p] = f4(origin, cosinePDF);
             A.qL[p] = f4(lightSample, realCosinePDF);
             A.qA[p] = qa;
-            direct = splat3(0.f);                                // filled in by connect
+            // what diffuseBRDF yields when the light-sample ray's closest hit is not emissive (E = 0, pdf = 0,
+            // raytrace.comp:459-460); connect overwrites it only for an unoccluded emissive hit
+            direct = splat3(0.f) * (Afac * 0.f);
             flags |= PT_SHADE_CONNECT;
         }
     }
@@ -283,8 +291,9 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 //   occlude : is there a non-emissive triangle the reference would have preferred? (bounded any-hit
 //             walk of the full BVH, the expensive part: its own persistent kernel, wavefront.cu)
 //   finish  : pdfs, MIS weights, direct light (raytrace.comp:447-460)
-// qE[p] = { tE(lightSample), tE(cosineSample), key(lightSample), key(cosineSample) }, tE < 0: no
-// emissive closest hit (none found, or occluded). qA[p].w = material of the light-sample hit.
+// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, - }, tE < 0: no emissive closest hit.
+// Paths without an emissive candidate, or whose candidate is occluded, keep the directLight shade stored (a zero: E = 0,
+// pdf = 0); only the unoccluded ones are finished — by the lane that ends the occlusion walk (connect_job_finish).
 #define PT_NO_EMISSIVE (-1.f)
 
 // Conservative slab test against the bounding box of all emissive triangles (the padded world boxes the small BVH
@@ -348,17 +357,13 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 #define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
-    float4 qa = A.qA[p];
-    v3 lightSample = xyz(A.qL[p]);
     uint32_t keyL = 0xffffffffu, matL = 0u;
     float tL = PT_NO_EMISSIVE;
     // connectAfterExtend: bounce j+1 was already extended; directLight of bounce j is dropped when it missed (:531-534)
     bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
     if (!dropped)            // (rays that cannot contribute never get here: stage_shade)
-        tL = emissive_candidate(sc, xyz(A.qO[p]), lightSample, td.sphereCount, td.objectCount, keyL, matL);  // :443-447
-    A.qE[p] = make_float4(tL, 0.f, as_float(keyL), 0.f);
-    qa.w = as_float(matL);
-    A.qA[p] = qa;
+        tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL);  // :443-447
+    if (tL >= 0.f) A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), 0.f);
     return tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u;
 }
 // the occlusion query of path p's light-sample ray
@@ -369,22 +374,17 @@ PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, u
     tE = e.x;
     keyE = as_uint(e.z);
 }
-PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p) {
-    reinterpret_cast<float*>(&A.qE[p])[0] = PT_NO_EMISSIVE;
-}
-// Returns true when misWeight is live (directLight.x == -1 exactly) and has to be computed.
-PT_HD bool stage_connect_finish(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+// The occlusion walk of path p's light-sample ray ended without an occluder: its closest hit IS the emissive one at
+// distance qE.x — pdf, power-heuristic weight and direct light of diffuseBRDF (raytrace.comp:447-460).
+// Returns true when misWeight is live (directLight.x == -1 exactly, see stage_shade) and has to be computed.
+PT_HD bool connect_job_finish(const WideScene& sc, const PathArrays& A, uint32_t p) {
     float4 qo = A.qO[p], ql = A.qL[p], qa = A.qA[p], qe = A.qE[p];
     v3 lightSample = xyz(ql);
     float cosinePDF = qo.w;
-    bool lightIsClosest = qe.x >= 0.f;
-    float realLightPDF = lightIsClosest ? light_pdf_from_dst(qe.x, lightSample) : 0.f;                      // :447
+    float realLightPDF = light_pdf_from_dst(qe.x, lightSample);                                            // :447
     float w1 = mis_weight(realLightPDF, cosinePDF);                                                        // :449-450
-    v3 E = splat3(0.f);           // a non-emissive (or missing) closest hit contributes emission * 0
-    if (lightIsClosest) {
-        const ptl::Material lm = sc.materials[as_uint(qa.w)];
-        E = mk3(lm.emissionColor[0], lm.emissionColor[1], lm.emissionColor[2]) * lm.emissionStrength;
-    }
+    const ptl::Material lm = sc.materials[as_uint(qe.y)];
+    v3 E = mk3(lm.emissionColor[0], lm.emissionColor[1], lm.emissionColor[2]) * lm.emissionStrength;
     v3 direct = E * (xyz(qa) * (realLightPDF == 0.f ? 0.f : w1 / realLightPDF));                            // :459-460
     A.direct[p] = f4(direct, 0.f);
     return direct.x == -1.f;
@@ -409,9 +409,9 @@ PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArray
     if (stage_connect_prep(P, sc, A, p)) {
         Ray r; float tE; uint32_t keyE;
         connect_job_ray(A, p, r, tE, keyE);
-        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p);
+        if (!bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE) && connect_job_finish(sc, A, p))
+            connect_mis_weight_exact(P, sc, A, p);
     }
-    if (stage_connect_finish(P, sc, A, p)) connect_mis_weight_exact(P, sc, A, p);
 }
 
 // ---- accumulate -----------------------------------------------------------------------------

@@ -36,7 +36,7 @@ struct WavefrontState {
     uint32_t countSlots = 0;
     int smCount = 148;
     int gridOcclude = 0;
-    int gridShade = 0, gridPrep = 0, gridFinish = 0;
+    int gridShade = 0, gridPrep = 0;
     int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
@@ -181,6 +181,9 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
     return __reduce_add_sync(0xffffffffu, (busy ? 1u : 0u) | (hasTri ? 0x100u : 0u) | (canNode ? 0x10000u : 0u));
 }
 
+#ifndef PT_TRI_PER_STEP
+#define PT_TRI_PER_STEP 1          /* triangles a lane tests per triangle step of the warp (A/B knob) */
+#endif
 #ifndef PT_EXTEND_MIN_BLOCKS
 #define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
 #endif
@@ -230,7 +233,13 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         }
         if (nBusy == 0u) break;                    // queue exhausted and every lane done
         if (nNode == 0u || 32u * nTri >= P.triVote32 * nBusy) {
-            if (hasTri) { trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key); if (COUNT) cntTri++; }
+            if (hasTri) {
+#pragma unroll 1
+                for (int r = 0; r < PT_TRI_PER_STEP && trav_has_tri(t); ++r) {
+                    trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
+                    if (COUNT) cntTri++;
+                }
+            }
         } else {
             if (canNode) { trav_node_step(sc.all, t, stack, hit.dst); if (COUNT) cntNode++; }
         }
@@ -340,7 +349,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
 template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
-                                                        uint32_t* workCounter, unsigned long long* work) {
+                                                        uint32_t* workCounter, uint32_t* misQueue, uint32_t* misCount, unsigned long long* work) {
     uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *jobCount;
     const uint32_t objectCount = P.pc.params.objectCount;
@@ -352,7 +361,12 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
-        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) busy = false;   // not occluded
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
+            // not occluded: the emissive candidate is the closest hit — direct light of this bounce (the former
+            // k_connect_finish, now only for the paths that need it)
+            if (connect_job_finish(sc, A, job)) misQueue[atomicAdd(misCount, 1u)] = job;
+            busy = false;
+        }
         const bool hasTri = busy && trav_has_tri(t);
         const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
         const unsigned votes = warp_votes(busy, hasTri, canNode);
@@ -371,10 +385,8 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
         if (nBusy == 0u) break;
         if (nNode == 0u || 32u * nTri >= P.triVoteOccl32 * nBusy) {
             if (COUNT && hasTri) cntTri++;
-            if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
-                connect_job_occluded(A, job);
-                busy = false;
-            }
+            if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE))
+                busy = false;          // occluded: directLight keeps the zero shade stored
         } else {
             if (canNode) { trav_node_step(sc.all, t, stack, tE); if (COUNT) cntNode++; }
         }
@@ -382,17 +394,8 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     if (COUNT) flush_work(work, cntNode, cntTri);
 }
 
-// connect, part 3: pdf, power-heuristic weight, direct light; queues the (practically never occurring) paths whose
-// misWeight is live
-__global__ void __launch_bounds__(WF_THREADS) k_connect_finish(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
-                                                               const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
-                                                               uint32_t* misQueue, uint32_t* misCount) {
-    uint32_t n = *sCount;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        uint32_t p = queue[i];
-        if (stage_connect_finish(P, sc, A, p)) misQueue[atomicAdd(misCount, 1u)] = p;
-    }
-}
+// connect, part 3 (rare): paths whose misWeight is live after all (directLight.x == -1 exactly): the exact pdf of the
+// BSDF-sampled direction
 __global__ void __launch_bounds__(WF_THREADS) k_connect_mis(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                             const uint32_t* __restrict__ misQueue, const uint32_t* __restrict__ misCount) {
     uint32_t n = *misCount;
@@ -703,8 +706,6 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         w->gridShade = std::max(1, perSm) * w->smCount;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_prep, WF_THREADS, 0));
         w->gridPrep = std::max(1, perSm) * w->smCount;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_finish, WF_THREADS, 0));
-        w->gridFinish = std::max(1, perSm) * w->smCount;
     }
     const int grid = w->smCount * 8;
     const int gridShade = w->gridShade;
@@ -782,19 +783,18 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                        (uint32_t*)w->dJobQ.p, oCount + j);
                     wf_mark(c, ST_OCCLUDE);
-                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, workCnt + 2);
-                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, nullptr);
+                    uint32_t* misQ = (uint32_t*)w->dJobQ.p + w->capacity;      // second half of the job buffer
+                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, misQ, mCount + j, workCnt + 2);
+                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, misQ, mCount + j, nullptr);
                     wf_mark(c, ST_FINISH);
-                    k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
-                                                                         (uint32_t*)w->dJobQ.p, mCount + j);
-                    k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, mCount + j);
+                    k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, misQ, mCount + j);
                     if (overlap) {
                         WCU(cudaEventRecord(w->evJoin, w->sideStream));
                         WCU(cudaStreamWaitEvent(c->stream, w->evJoin, 0));
                     }
                 }
                 std::swap(qa, qb);
-                c->counters[0] += (j + 1 < nB) ? 6 : 1;
+                c->counters[0] += (j + 1 < nB) ? 5 : 1;
             }
             k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, oCount, mCount, primaryCount, P.sharePrimary, nB, (unsigned long long*)w->dRayCounters.p);
             c->counters[0] += 3;                                      // generate, extend(0), fold

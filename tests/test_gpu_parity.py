@@ -282,9 +282,10 @@ def test_full_size_properties_c4(gpu):
     cp.render_frames(pc.buffer, 0, 4, rows=(0, 377))
     cp.render_frames(pc.buffer, 0, 4, rows=(377, H))
     assert _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole) <= 20
-    # BASELINE.json's bar for C4 ("the image within RMSE 1e-3"): the 4-frame image against the libm oracle (= the
-    # reference's shader text) on a 96 x 54 lattice of the full 1920 x 1080 image
-    _lattice_check(whole, blobs, pc.buffer, W, H, 4, 96, 54)
+    # BASELINE.json's bar for C4 ("the image within RMSE 1e-3"), at C4's own 1024 spp, on a 32 x 18 lattice of the image
+    cp.set_option("frames_in_flight", 24)
+    _config_spp_check(cp, blobs, pc.buffer, W, H, 1024, 32, 18)
+    cp.set_option("frames_in_flight", 4)
     # the oracle on a window of the same image: 64 x 48 pixels around the centre, 1 frame, bit-exact apart from ties
     # (a window, not a sub-sampled grid: seeds and rays depend on x, y, W and H)
     cp.clear()
@@ -296,29 +297,38 @@ def test_full_size_properties_c4(gpu):
     _assert_explained(blobs, pc.buffer, W, H, [0], got, want, x0=928, y0=516)
 
 
-def _lattice_check(acc, blobs, pc, W, H, frames, nx, ny):
-    """BASELINE.json's bar on the FULL image: relative RMSE <= 1e-3 at equal spp and seeds against the libm oracle (and
-    against the reference's own shader text where oracle/_ref/libraytrace_comp.so is in the tree), on a lattice of
-    nx x ny pixels spread over the whole W x H image."""
+def _config_spp_check(cp, blobs, pc, W, H, spp, nx, ny):
+    """BASELINE.json's bar, at the configuration's OWN sample count: per-pixel radiance within relative RMSE 1e-3 of the
+    reference at equal spp and seeds. Pixels: a lattice of nx x ny spread over the whole W x H image (the GPU renders the
+    lattice's rows in full — b200pt_render_frames_rows_strided — for all `spp` frames; the oracle renders the lattice).
+    Against the libm oracle, which is the reference's shader text bit for bit (asserted here too when
+    oracle/_ref/libraytrace_comp.so is in the tree). At a fraction of the spp the figure is dominated by single paths
+    that a last-bit difference in sin/cos sends to another triangle after a few bounces on curved geometry (it falls
+    as 1/sqrt(spp)), which is why the bar is checked at the full count. In portable-math mode the same pixels must be
+    bit-equal apart from explained ties."""
     sx, sy = W // nx, H // ny
+    cp.clear()
+    cp.render_frames(pc, 0, spp, rows=(0, H), row_stride=sy)
+    acc = cp.read_accum()
     got = acc[0:ny * sy:sy, 0:nx * sx:sx][:ny, :nx]
+    assert np.array_equal(got[..., 3], np.full((ny, nx), spp, np.float32)) and np.isfinite(got).all()
     sc = ob.OracleScene(blobs)
-    libm = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
+    libm = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=spp, sx=sx, sy=sy)
     rel = relrmse(got[..., :3], libm[..., :3])
     assert rel <= 1e-3, rel                                     # tolerance stated by BASELINE.json
     import ref_shader_binding as rb
     if rb.available():
-        ref = rb.RefShaderScene(blobs).render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
+        ref = rb.RefShaderScene(blobs).render_window(pc, W, H, 0, 0, 0, nx, ny, n=spp, sx=sx, sy=sy)
         assert np.array_equal(ref.view(np.uint32), libm.view(np.uint32))        # the oracle IS the reference's shader text
     with ob.math_mode(1):
-        exact = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=frames, sx=sx, sy=sy)
-    _assert_explained(blobs, pc, W, H, range(frames), got, exact, sx=sx, sy=sy)
+        exact = sc.render_window(pc, W, H, 0, 0, 0, nx, ny, n=spp, sx=sx, sy=sy)
+    _assert_explained(blobs, pc, W, H, range(spp), got, exact, sx=sx, sy=sy)
     return rel
 
 
-def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, lattice=(96, 54)):
+def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h):
     """Accumulated `frames` frames of the full image on the GPU: bit-exact against the oracle (portable math) on one dense
-    window apart from explained ties, and within relRMSE 1e-3 of the libm oracle on a lattice over the whole image."""
+    window apart from explained ties."""
     cp.clear()
     cp.render_frames(pc, 0, frames)
     acc = cp.read_accum()
@@ -327,8 +337,6 @@ def _window_check(cp, blobs, pc, W, H, frames, x0, y0, w, h, lattice=(96, 54)):
         want = ob.OracleScene(blobs).render_window(pc, W, H, 0, x0, y0, w, h, n=frames)
     got = acc[y0:y0 + h, x0:x0 + w]
     _assert_explained(blobs, pc, W, H, range(frames), got, want, x0=x0, y0=y0)      # frames are summed in frame order on both sides
-    if lattice:
-        _lattice_check(acc, blobs, pc, W, H, frames, *lattice)
     return acc
 
 
@@ -337,10 +345,11 @@ def test_full_size_c2_bunny(gpu, bunny_blobs):
     W = H = 1024
     pc = ob.default_push_constants(W, H, 10, bunny_blobs["objects"].size // 80)
     cp = _pass(gpu, bunny_blobs, W, H)
-    acc = _window_check(cp, bunny_blobs, pc, W, H, 64, 480, 470, 40, 40, lattice=(64, 64))
+    acc = _window_check(cp, bunny_blobs, pc, W, H, 64, 480, 470, 40, 40)
     assert acc[..., :3].mean() / 64 > 0.01
     c = cp.counters()
     assert c["paths"] == 64 * W * H
+    _config_spp_check(cp, bunny_blobs, pc, W, H, 64, 64, 64)                      # C2's own 64 spp
 
 
 def test_full_size_c3_c5_statue_stand_in(gpu):
@@ -352,15 +361,17 @@ def test_full_size_c3_c5_statue_stand_in(gpu):
     W, H = 1920, 1080
     pc = PushConstants(W, H, 10, info["objects"])
     cp = _pass(gpu, blobs, W, H)
-    _window_check(cp, blobs, pc.buffer, W, H, 1, 930, 500, 64, 48, lattice=None)   # the statue's silhouette
-    _window_check(cp, blobs, pc.buffer, W, H, 4, 700, 800, 48, 32)                 # floor in front of it, 4 frames + C3 lattice
+    _window_check(cp, blobs, pc.buffer, W, H, 1, 930, 500, 64, 48)                 # the statue's silhouette
+    _window_check(cp, blobs, pc.buffer, W, H, 4, 700, 800, 48, 32)                 # floor in front of it, 4 frames
+    cp.set_option("frames_in_flight", 16)
+    _config_spp_check(cp, blobs, pc.buffer, W, H, 256, 32, 18)                     # C3's own 256 spp
     W, H = 3840, 2160
     blobs5, info5 = scenes.statue_room(800_000, statue_material=5)             # dielectric: longest paths
     pc = PushConstants(W, H, 10, info5["objects"])
     pc["bounceLimit"] = 16
     cp = _pass(gpu, blobs5, W, H)
     cp.set_option("frames_in_flight", 2)
-    _window_check(cp, blobs5, pc.buffer, W, H, 1, 1900, 1000, 64, 40, lattice=None)
+    _window_check(cp, blobs5, pc.buffer, W, H, 1, 1900, 1000, 64, 40)
 
 
 def test_full_size_c5_stand_in(gpu):
@@ -374,8 +385,10 @@ def test_full_size_c5_stand_in(gpu):
     pc["bounceLimit"] = 16
     cp = _pass(gpu, blobs, W, H)
     cp.set_option("frames_in_flight", 2)
-    acc = _window_check(cp, blobs, pc.buffer, W, H, 2, 1900, 1100, 48, 32, lattice=(96, 54))
+    acc = _window_check(cp, blobs, pc.buffer, W, H, 2, 1900, 1100, 48, 32)
     assert acc[..., :3].mean() / 2 > 0.01
+    cp.set_option("frames_in_flight", 24)
+    _config_spp_check(cp, blobs, pc.buffer, W, H, 4096, 16, 9)                     # C5's own 4096 spp, depth 16
     cp.close()
 
 
