@@ -545,6 +545,22 @@ def main():
     pc["frameCount"] = 0
     cp.set_option("frames_in_flight", max(1, min(64, F)))
 
+    # ---- UI "update objects" (src/vk_engine.cpp:1594-1603): one object's transform edited; wall time until the scene is usable
+    upd = None
+    if blobs["objects"].size >= 80:
+        moved = blobs["objects"].copy()
+        moved[:64].view(np.float32)[12] += 0.25                    # object 0: translate x
+        times = []
+        for k in range(6):
+            fence()
+            tu = time.perf_counter()
+            cp.update_buffer("objects", moved if k % 2 == 0 else blobs["objects"])
+            cp.sync()
+            times.append((time.perf_counter() - tu) * 1e3)
+        upd = dict(ms=min(times), ms_all=[round(t, 3) for t in times], refit=bool(cp.get_option("last_update_was_refit")),
+                   device_ms=cp.get_option("last_wide_device_us") / 1e3,
+                   note="b200pt_update_objects of all %d objects with one matrix changed (wall clock incl. upload and sync); the scene is back to the original afterwards" % info["objects"])
+
     # ---- CPU baseline (timing) and parity of this run's own output at the configuration's OWN sample count: the lattice
     # pixels of the full image, frames 0 .. n-1, rendered here (whole rows, every sy-th) and by the CPU reference
     cpu = parity = None
@@ -622,7 +638,7 @@ def main():
                    primary_rays="traced once per pixel and shared by the %d frame slots of a batch (no jitter: raytrace.comp:541)" % F,
                    rays_per_path=dict(traced=counted["extension_rays_traced_per_path"] + counted["occlusion_rays_traced_per_path"] + counted["pdf_rays_traced_per_path"],
                                       reference=avoided["reference_rays_per_path"]))
-        out.update(roofline=roofline, cpu_baseline=cpu, parity=parity, counted_work=counted, strong_scaling=strong, c5=c5,
+        out.update(roofline=roofline, cpu_baseline=cpu, parity=parity, counted_work=counted, strong_scaling=strong, c5=c5, update_objects=upd,
                    interactive=dict(ms_per_frame=ms_inter, frames=n_inter, run_compute_ms=ms_dispatch, run_compute_pipeline0_ms=ms_dispatch_ref,
                                     split="interleaved rows over %d GPU(s), gathered on rank 0 inside the library (ncclSend/Recv)" % N,
                                     note="one 1-spp progressive frame at a time (latency), vs ms_per_frame_1spp = throughput mode / frames"))

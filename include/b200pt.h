@@ -72,7 +72,10 @@ int b200pt_upload_scene(b200pt_ctx* ctx, const void* spheres, uint32_t n_spheres
                         uint32_t n_materials, const void* tri_points, uint32_t n_points, const void* triangles,
                         uint32_t n_triangles, const void* objects, uint32_t n_objects, const void* bvh_nodes,
                         uint32_t n_nodes);
-/* In-place updates, same element counts as uploaded (the reference's update_buffer never resizes). */
+/* In-place updates, same element counts as uploaded (the reference's update_buffer never resizes).
+ * b200pt_update_objects with nothing but transform matrices changed REFITS the internal tree on the device (same
+ * topology, boxes recomputed; option "refit_on_update", default 1; "last_update_was_refit" tells); any other change, or a
+ * tree built on the host, re-lays the scene out. Images equal those of a fresh upload either way. */
 int b200pt_update_materials(b200pt_ctx* ctx, const void* materials, uint32_t n);
 int b200pt_update_spheres(b200pt_ctx* ctx, const void* spheres, uint32_t n);
 int b200pt_update_objects(b200pt_ctx* ctx, const void* objects, uint32_t n);
@@ -176,7 +179,8 @@ int b200pt_render_frame_interleaved(b200pt_ctx* ctx, const void* push_constants_
  * never / for batches of up to 8 frames (default) / always; "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32 (k_extend), "occl_tri_vote", "occl_fetch_idle" (k_occlude): scheduling of the wavefront kernels
  * (results do not depend on them); "wide_build" 1 (default) / 0: the internal wide BVH of all triangles is built on
  * the device / on the host at b200pt_upload_scene and b200pt_update_* (read before the upload; images do not depend
- * on it). Read-only: "last_scene_build_us", "last_wide_device_us". Unknown keys fail. */
+ * on it); "refit_on_update" 1 (default) / 0. Read-only: "last_scene_build_us", "last_wide_device_us",
+ * "last_update_was_refit". Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
 

@@ -249,7 +249,14 @@ int b200pt_update_objects(b200pt_ctx* c, const void* objects, uint32_t n) {
     c->hObjects.assign((const ptl::RenderObject*)objects, (const ptl::RenderObject*)objects + n);
     if (const char* why = validate_scene(c)) { c->hObjects = old; return fail(c, B200PT_ERR_ARG, "update_objects: %s", why); }
     if (int rc = upload_objects(c)) return rc;
-    return wavefront_build_scene(c);      // world-space boxes move with the transforms
+    // world-space boxes move with the transforms. When nothing but matrices changed the device-built tree is refitted
+    // (same topology, boxes recomputed bottom-up); anything else re-lays the scene out.
+    bool onlyMatrices = true;
+    for (size_t i = 0; i < old.size() && onlyMatrices; ++i) {
+        const ptl::RenderObject &a = old[i], &b = c->hObjects[i];
+        onlyMatrices = a.smoothShade == b.smoothShade && a.bvhIndex == b.bvhIndex && a.materialIndex == b.materialIndex && a.samplerIndex == b.samplerIndex;
+    }
+    return wavefront_build_scene(c, onlyMatrices ? pt::WF_CHANGED_TRANSFORMS : pt::WF_CHANGED_ALL);
 }
 
 static int upload_texture_table(b200pt_ctx* c) {
@@ -459,6 +466,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "share_primary") { c->sharePrimary = v != 0; return 0; }
     if (k == "overlap_connect") { if (v < 0 || v > 2) return fail(c, B200PT_ERR_ARG, "overlap_connect must be 0..2"); c->overlapConnect = (int)v; return 0; }
     if (k == "wide_build") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "wide_build must be 0 (host) or 1 (device)"); c->wideBuild = (int)v; return 0; }
+    if (k == "refit_on_update") { c->refitOnUpdate = v != 0; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
@@ -477,6 +485,8 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "share_primary") { *v = c->sharePrimary; return 0; }
     if (k == "overlap_connect") { *v = c->overlapConnect; return 0; }
     if (k == "wide_build") { *v = c->wideBuild; return 0; }
+    if (k == "refit_on_update") { *v = c->refitOnUpdate; return 0; }
+    if (k == "last_update_was_refit") { *v = c->lastRefit; return 0; }                               // read-only
     if (k == "last_scene_build_us") { *v = (int64_t)(c->lastSceneBuildMs * 1000.0); return 0; }      // read-only
     if (k == "last_wide_device_us") { *v = (int64_t)(c->lastWideDeviceMs * 1000.0); return 0; }      // read-only
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);

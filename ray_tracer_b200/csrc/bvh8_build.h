@@ -39,6 +39,27 @@ struct WideSceneHost {
 
 struct WideBox { float lo[3], hi[3]; };
 
+// World-space box of one triangle instance, padded: the hit the object-space test accepts lies within rounding of it.
+// Shared by the builders and by the refit after a transform edit (wide_build.cu: k_wide_refit). Returns false when a
+// world-space vertex is not finite.
+PT_HD bool wide_world_box(const ptl::RenderObject& ob, v3 pa, v3 pb, v3 pc, WideBox& bx) {
+    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] = 1e30f; bx.hi[ax] = -1e30f; }
+    v3 w[3] = {mul_point(ob.m, pa), mul_point(ob.m, pb), mul_point(ob.m, pc)};
+    bool finite = true;
+    for (int k = 0; k < 3; ++k) {
+        float q[3] = {w[k].x, w[k].y, w[k].z};
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(fabsf(q[ax]) < 1e30f)) finite = false;
+            bx.lo[ax] = fminf(bx.lo[ax], q[ax]); bx.hi[ax] = fmaxf(bx.hi[ax], q[ax]);
+        }
+    }
+    float mag = 0.f;
+    for (int ax = 0; ax < 3; ++ax) mag = fmaxf(mag, fmaxf(fabsf(bx.lo[ax]), fabsf(bx.hi[ax])));
+    float pad = 1e-5f * mag + 1e-7f;
+    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
+    return finite;
+}
+
 // Records of one (object, triangle) instance; shared by the host builder and the device build so both produce the
 // same bytes. Returns false when a world-space vertex is not finite (such a triangle can never be hit: dropped).
 PT_HD bool wide_make_records(uint32_t o, uint32_t t, const ptl::RenderObject& ob, const ptl::Triangle& tr, const ptl::TrianglePoint& a,
@@ -61,21 +82,7 @@ PT_HD bool wide_make_records(uint32_t o, uint32_t t, const ptl::RenderObject& ob
     s.n0x = a.nx; s.n0y = a.ny; s.n0z = a.nz; s.materialIndex = ob.materialIndex;
     s.n1x = b.nx; s.n1y = b.ny; s.n1z = b.nz; s.objectIndex = o;
     s.n2x = c.nx; s.n2y = c.ny; s.n2z = c.nz; s.triIndex = t;
-    // world box, padded: the hit the object-space test accepts lies within rounding of it
-    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] = 1e30f; bx.hi[ax] = -1e30f; }
-    v3 w[3] = {mul_point(ob.m, pa), mul_point(ob.m, pb), mul_point(ob.m, pc)};
-    bool finite = true;
-    for (int k = 0; k < 3; ++k) {
-        float q[3] = {w[k].x, w[k].y, w[k].z};
-        for (int ax = 0; ax < 3; ++ax) {
-            if (!(fabsf(q[ax]) < 1e30f)) finite = false;
-            bx.lo[ax] = fminf(bx.lo[ax], q[ax]); bx.hi[ax] = fmaxf(bx.hi[ax], q[ax]);
-        }
-    }
-    float mag = 0.f;
-    for (int ax = 0; ax < 3; ++ax) mag = fmaxf(mag, fmaxf(fabsf(bx.lo[ax]), fabsf(bx.hi[ax])));
-    float pad = 1e-5f * mag + 1e-7f;
-    for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] -= pad; bx.hi[ax] += pad; }
+    const bool finite = wide_world_box(ob, pa, pb, pc, bx);
     uvr.u0 = a.u; uvr.v0 = a.v; uvr.u1 = b.u; uvr.v1 = b.v; uvr.u2 = c.u; uvr.v2 = c.v;
     uvr.samplerIndex = ob.samplerIndex;
     uvr.degenerate = ((a.u == b.u && a.v == b.v) || (b.u == c.u && b.v == c.v) || (c.u == a.u && c.v == a.v)) ? 1u : 0u;
@@ -351,17 +358,9 @@ inline void wide_sphere_masks(const std::vector<ptl::Sphere>& spheres, const std
 }
 
 // Reference-layout buffers -> WideSceneHost. Returns nullptr on success or a message.
-inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials,
-                                    const std::vector<ptl::TrianglePoint>& points, const std::vector<ptl::Triangle>& tris,
-                                    const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes,
-                                    WideSceneHost& out, bool buildAll = true) {
-    using namespace b8;
-    out.xforms.clear(); out.objXform.assign(objects.size(), 0); out.anyEmissive = false;
-    out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
-    auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
-    wide_sphere_masks(spheres, materials, out);
-
-    // distinct object matrices (bit pattern): objects that share one share the transformed ray
+// distinct object matrices (bit pattern): objects that share one share the transformed ray
+inline void wide_xforms(const std::vector<ptl::RenderObject>& objects, WideSceneHost& out) {
+    out.xforms.clear(); out.objXform.assign(objects.size(), 0);
     for (size_t o = 0; o < objects.size(); ++o) {
         uint32_t id = (uint32_t)out.xforms.size();
         for (uint32_t k = 0; k < out.xforms.size(); ++k)
@@ -374,6 +373,62 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
         }
         out.objXform[o] = id;
     }
+}
+
+// After a transform edit (b200pt_update_objects): the transform table and the small tree over the triangles of EMISSIVE
+// objects only (world-space boxes move with the objects), from the triangle -> leaf map and parent links kept from the
+// last full re-layout. The tree over all triangles is refitted on the device (wide_build.cu: wide_refit_device).
+inline const char* build_emissive_scene(const std::vector<ptl::Material>& materials, const std::vector<ptl::TrianglePoint>& points,
+                                        const std::vector<ptl::Triangle>& tris, const std::vector<ptl::RenderObject>& objects,
+                                        const std::vector<ptl::BVHNode>& nodes, const std::vector<uint32_t>& leafOf, const std::vector<UpNode>& up,
+                                        WideSceneHost& out) {
+    using namespace b8;
+    wide_xforms(objects, out);
+    std::vector<Box> boxesE; std::vector<Instance> instE; std::vector<PrimRecord> primE; std::vector<ShadeRecord> shadeE; std::vector<UvRecord> uvsE;
+    std::vector<uint32_t> stack;
+    for (size_t o = 0; o < objects.size(); ++o) {
+        const ptl::RenderObject& ob = objects[o];
+        if (materials[ob.materialIndex].emissionStrength == 0.f) continue;
+        stack.clear(); stack.push_back(ob.bvhIndex);
+        size_t guard = 0;
+        while (!stack.empty()) {
+            if (++guard > 4 * nodes.size() + 8) return "BVH of an object is cyclic";
+            const ptl::BVHNode& nd = nodes[stack.back()]; stack.pop_back();
+            if (!nd.triCount) { stack.push_back(nd.index + 1); stack.push_back(nd.index); continue; }
+            for (uint32_t t = nd.index; t < nd.index + nd.triCount; ++t) {
+                const ptl::Triangle& tr = tris[t];
+                PrimRecord r; ShadeRecord s; UvRecord uvr; WideBox wb;
+                if (!wide_make_records((uint32_t)o, t, ob, tr, points[tr.v0], points[tr.v1], points[tr.v2], leafOf[t], up.data(), out.objXform[o], true,
+                                       r, s, uvr, wb)) continue;
+                Box bx;
+                for (int ax = 0; ax < 3; ++ax) { bx.lo[ax] = wb.lo[ax]; bx.hi[ax] = wb.hi[ax]; }
+                boxesE.push_back(bx); instE.push_back({(uint32_t)o, t}); primE.push_back(r); shadeE.push_back(s); uvsE.push_back(uvr);
+            }
+        }
+    }
+    b8::Box u; b8::box_reset(u);
+    for (const auto& bx : boxesE) b8::box_grow(u, bx);
+    for (int a = 0; a < 3; ++a) {
+        float mag = std::max(std::fabs(u.lo[a]), std::fabs(u.hi[a]));
+        out.emisLo[a] = u.lo[a] - (1e-4f * mag + 1e-6f); out.emisHi[a] = u.hi[a] + (1e-4f * mag + 1e-6f);
+    }
+    out.emis = Bvh8Host();
+    bvh8_build(boxesE, instE, primE, shadeE, uvsE, out.emis);
+    if (out.emis.maxDepth > PT_BVH8_MAX_DEPTH) return "wide BVH deeper than the traversal stack";
+    return nullptr;
+}
+
+inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::Material>& materials,
+                                    const std::vector<ptl::TrianglePoint>& points, const std::vector<ptl::Triangle>& tris,
+                                    const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes,
+                                    WideSceneHost& out, bool buildAll = true) {
+    using namespace b8;
+    out.anyEmissive = false;
+    out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
+    auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
+    wide_sphere_masks(spheres, materials, out);
+
+    wide_xforms(objects, out);
 
     // parent links and triangle -> leaf map of the reference BVH2
     out.up.resize(nodes.size());

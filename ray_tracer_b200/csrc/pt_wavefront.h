@@ -291,9 +291,10 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 //   occlude : is there a non-emissive triangle the reference would have preferred? (bounded any-hit
 //             walk of the full BVH, the expensive part: its own persistent kernel, wavefront.cu)
 //   finish  : pdfs, MIS weights, direct light (raytrace.comp:447-460)
-// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, - }, tE < 0: no emissive closest hit.
-// Paths without an emissive candidate, or whose candidate is occluded, keep the directLight shade stored (a zero: E = 0,
-// pdf = 0); only the unoccluded ones are finished — by the lane that ends the occlusion walk (connect_job_finish).
+// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, - }, tE < 0: no emissive closest hit
+// (none found, or occluded). Those paths keep the directLight shade stored (a zero: E = 0, pdf = 0); finish only reads
+// their qE. (Finishing the unoccluded ones inside the occlusion kernel, by the lane that ends the walk, was measured:
+// k_connect_finish 3.7 -> 0 ms but k_occlude 35.3 -> 39.7 ms per step — four dependent loads in a converged warp.)
 #define PT_NO_EMISSIVE (-1.f)
 
 // Conservative slab test against the bounding box of all emissive triangles (the padded world boxes the small BVH
@@ -363,7 +364,7 @@ PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const 
     bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
     if (!dropped)            // (rays that cannot contribute never get here: stage_shade)
         tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL);  // :443-447
-    if (tL >= 0.f) A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), 0.f);
+    A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), 0.f);
     return tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u;
 }
 // the occlusion query of path p's light-sample ray
@@ -374,11 +375,16 @@ PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, u
     tE = e.x;
     keyE = as_uint(e.z);
 }
-// The occlusion walk of path p's light-sample ray ended without an occluder: its closest hit IS the emissive one at
-// distance qE.x — pdf, power-heuristic weight and direct light of diffuseBRDF (raytrace.comp:447-460).
+PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p) {
+    reinterpret_cast<float*>(&A.qE[p])[0] = PT_NO_EMISSIVE;
+}
+// The light-sample ray of path p: when its closest hit is the emissive one at distance qE.x (found by prep, not occluded)
+// — pdf, power-heuristic weight and direct light of diffuseBRDF (raytrace.comp:447-460); otherwise nothing (see above).
 // Returns true when misWeight is live (directLight.x == -1 exactly, see stage_shade) and has to be computed.
 PT_HD bool connect_job_finish(const WideScene& sc, const PathArrays& A, uint32_t p) {
-    float4 qo = A.qO[p], ql = A.qL[p], qa = A.qA[p], qe = A.qE[p];
+    const float4 qe = A.qE[p];
+    if (!(qe.x >= 0.f)) return false;
+    float4 qo = A.qO[p], ql = A.qL[p], qa = A.qA[p];
     v3 lightSample = xyz(ql);
     float cosinePDF = qo.w;
     float realLightPDF = light_pdf_from_dst(qe.x, lightSample);                                            // :447
@@ -409,9 +415,9 @@ PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArray
     if (stage_connect_prep(P, sc, A, p)) {
         Ray r; float tE; uint32_t keyE;
         connect_job_ray(A, p, r, tE, keyE);
-        if (!bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE) && connect_job_finish(sc, A, p))
-            connect_mis_weight_exact(P, sc, A, p);
+        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p);
     }
+    if (connect_job_finish(sc, A, p)) connect_mis_weight_exact(P, sc, A, p);
 }
 
 // ---- accumulate -----------------------------------------------------------------------------

@@ -31,12 +31,14 @@ struct WavefrontState {
     WideBuildCache wideCache;
     bool wideOnDevice = false;
     std::vector<uint8_t> objEmissive;  // per object: material emits (decides which tree a triangle is in)
+    std::vector<uint32_t> hLeafOf;     // triangle -> reference BVH2 leaf, parent links: kept for the refit after a transform edit
+    std::vector<UpNode> hUp;
     bool haveScene = false, anyEmissiveTri = false;
     size_t capacity = 0;
     uint32_t countSlots = 0;
     int smCount = 148;
     int gridOcclude = 0;
-    int gridShade = 0, gridPrep = 0;
+    int gridShade = 0, gridPrep = 0, gridFinish = 0;
     int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
@@ -183,6 +185,9 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
 
 #ifndef PT_TRI_PER_STEP
 #define PT_TRI_PER_STEP 1          /* triangles a lane tests per triangle step of the warp (A/B knob) */
+#endif
+#ifndef PT_TRI_PER_STEP_OCCL
+#define PT_TRI_PER_STEP_OCCL 1     /* the same for k_occlude */
 #endif
 #ifndef PT_EXTEND_MIN_BLOCKS
 #define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
@@ -349,7 +354,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
 template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
-                                                        uint32_t* workCounter, uint32_t* misQueue, uint32_t* misCount, unsigned long long* work) {
+                                                        uint32_t* workCounter, unsigned long long* work) {
     uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *jobCount;
     const uint32_t objectCount = P.pc.params.objectCount;
@@ -361,12 +366,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
     for (;;) {
-        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
-            // not occluded: the emissive candidate is the closest hit — direct light of this bounce (the former
-            // k_connect_finish, now only for the paths that need it)
-            if (connect_job_finish(sc, A, job)) misQueue[atomicAdd(misCount, 1u)] = job;
-            busy = false;
-        }
+        if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) busy = false;   // not occluded
         const bool hasTri = busy && trav_has_tri(t);
         const bool canNode = busy && trav_has_node(t) && (!hasTri || t.sp < PT_BVH8_POSTPONE_LIMIT);
         const unsigned votes = warp_votes(busy, hasTri, canNode);
@@ -384,9 +384,17 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
         }
         if (nBusy == 0u) break;
         if (nNode == 0u || 32u * nTri >= P.triVoteOccl32 * nBusy) {
-            if (COUNT && hasTri) cntTri++;
-            if (hasTri && trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE))
-                busy = false;          // occluded: directLight keeps the zero shade stored
+            if (hasTri) {
+#pragma unroll 1
+                for (int r = 0; r < PT_TRI_PER_STEP_OCCL && trav_has_tri(t); ++r) {
+                    if (COUNT) cntTri++;
+                    if (trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
+                        connect_job_occluded(A, job);
+                        busy = false;
+                        break;
+                    }
+                }
+            }
         } else {
             if (canNode) { trav_node_step(sc.all, t, stack, tE); if (COUNT) cntNode++; }
         }
@@ -394,8 +402,18 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     if (COUNT) flush_work(work, cntNode, cntTri);
 }
 
-// connect, part 3 (rare): paths whose misWeight is live after all (directLight.x == -1 exactly): the exact pdf of the
-// BSDF-sampled direction
+// connect, part 3: pdf, power-heuristic weight, direct light of the paths whose light-sample ray reached the light (the
+// others keep the zero shade stored: one 16-byte read each); queues the (practically never occurring) paths whose
+// misWeight is live
+__global__ void __launch_bounds__(WF_THREADS) k_connect_finish(const __grid_constant__ WideScene sc, PathArrays A,
+                                                               const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
+                                                               uint32_t* misQueue, uint32_t* misCount) {
+    uint32_t n = *sCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t p = queue[i];
+        if (connect_job_finish(sc, A, p)) misQueue[atomicAdd(misCount, 1u)] = p;
+    }
+}
 __global__ void __launch_bounds__(WF_THREADS) k_connect_mis(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                             const uint32_t* __restrict__ misQueue, const uint32_t* __restrict__ misCount) {
     uint32_t n = *misCount;
@@ -527,6 +545,7 @@ static void wf_release_tree(WavefrontState* w) {
     if (r.prims) cudaFree(r.prims);
     if (r.shade) cudaFree(r.shade);
     if (r.uv) cudaFree(r.uv);
+    if (r.nodeBox) cudaFree(r.nodeBox);
     r = WideDeviceResult{};
     w->wideOnDevice = false;
 }
@@ -552,7 +571,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     std::vector<uint8_t> objEmissive(c->hObjects.size());
     for (size_t o = 0; o < c->hObjects.size(); ++o)
         objEmissive[o] = !(c->hMaterials[c->hObjects[o].materialIndex].emissionStrength == 0.f);
-    if (changed != WF_CHANGED_ALL && w->haveScene && objEmissive == w->objEmissive) {
+    if ((changed == WF_CHANGED_MATERIALS || changed == WF_CHANGED_SPHERES) && w->haveScene && objEmissive == w->objEmissive) {
         wide_sphere_masks(c->hSpheres, c->hMaterials, host);
         WideScene& s = w->scene;
         s.spheres = c->ref.spheres; s.materials = c->ref.materials;
@@ -563,6 +582,39 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
         c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
         return 0;
     }
+    // Only object matrices changed (the UI's "update objects", src/vk_engine.cpp:1594-1603): refit instead of rebuilding.
+    if (changed == WF_CHANGED_TRANSFORMS && c->refitOnUpdate && w->haveScene && w->wideOnDevice && !w->wideRes.nDropped && !w->wideRes.levelCount.empty() &&
+        objEmissive == w->objEmissive && w->hLeafOf.size() == c->hTris.size() && w->hUp.size() == c->hNodes.size()) {
+        bool finite = true;
+        for (const auto& o : c->hObjects) for (int k = 0; k < 16; ++k) finite = finite && std::fabs(o.m[k]) < 1e30f;
+        const char* err = finite ? build_emissive_scene(c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, w->hLeafOf, w->hUp, host) : "non-finite matrix";
+        if (!err) {
+            WCU(wf_upload(c, w->dNodesE, host.emis.nodes));
+            WCU(wf_upload(c, w->dPrimsE, host.emis.prims));
+            WCU(wf_upload(c, w->dShadeE, host.emis.shade));
+            WCU(wf_upload(c, w->dXforms, host.xforms));
+            WCU(wf_upload(c, w->dObjXform, host.objXform));
+            WideDeviceInputs in{(const ptl::TrianglePoint*)c->dPoints.p, (const ptl::Triangle*)c->dTris.p, (const ptl::RenderObject*)c->dObjects.p,
+                                (const ptl::Material*)c->dMaterials.p};
+            float ms = 0.f;
+            err = wide_refit_device(c->stream, in, (const uint32_t*)w->dObjXform.p, w->wideRes, &ms);      // synchronises the stream
+            if (!err) {
+                WideScene& s = w->scene;
+                s.emis = {(const Bvh8Node*)w->dNodesE.p, (const PrimRecord*)w->dPrimsE.p, (uint32_t)host.emis.nodes.size(), (uint32_t)host.emis.prims.size()};
+                s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
+                s.xforms = (const Xform*)w->dXforms.p; s.objXform = (const uint32_t*)w->dObjXform.p;
+                s.nXforms = (uint32_t)host.xforms.size();
+                for (int a = 0; a < 3; ++a) { s.emisLo[a] = host.emisLo[a]; s.emisHi[a] = host.emisHi[a]; }
+                c->lastWideDeviceMs = ms;
+                c->lastRefit = 1;
+                c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
+                return 0;
+            }
+            WCU(cudaStreamSynchronize(c->stream));
+        }
+        host = WideSceneHost();      // fall through to the full re-layout
+    }
+    c->lastRefit = 0;
     w->objEmissive = objEmissive; w->haveScene = false;
     const bool onDevice = c->wideBuild != 0;
     if (const char* err = build_wide_scene(c->hSpheres, c->hMaterials, c->hPoints, c->hTris, c->hObjects, c->hNodes, host, !onDevice)) {
@@ -620,6 +672,8 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     for (int a = 0; a < 3; ++a) {     s.emisLo[a] = host.emisLo[a];     s.emisHi[a] = host.emisHi[a]; }
     s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
     w->maxDepth = depthAll;
+    w->hLeafOf = onDevice ? host.leafOf : std::vector<uint32_t>();
+    w->hUp = host.up;
     w->haveScene = true;
     w->anyEmissiveTri = !host.emis.prims.empty();
     c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
@@ -706,6 +760,8 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         w->gridShade = std::max(1, perSm) * w->smCount;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_prep, WF_THREADS, 0));
         w->gridPrep = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_connect_finish, WF_THREADS, 0));
+        w->gridFinish = std::max(1, perSm) * w->smCount;
     }
     const int grid = w->smCount * 8;
     const int gridShade = w->gridShade;
@@ -784,9 +840,10 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                                                                        (uint32_t*)w->dJobQ.p, oCount + j);
                     wf_mark(c, ST_OCCLUDE);
                     uint32_t* misQ = (uint32_t*)w->dJobQ.p + w->capacity;      // second half of the job buffer
-                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, misQ, mCount + j, workCnt + 2);
-                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, misQ, mCount + j, nullptr);
+                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, workCnt + 2);
+                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, nullptr);
                     wf_mark(c, ST_FINISH);
+                    k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
                     k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, misQ, mCount + j);
                     if (overlap) {
                         WCU(cudaEventRecord(w->evJoin, w->sideStream));
@@ -794,7 +851,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     }
                 }
                 std::swap(qa, qb);
-                c->counters[0] += (j + 1 < nB) ? 5 : 1;
+                c->counters[0] += (j + 1 < nB) ? 6 : 1;
             }
             k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, oCount, mCount, primaryCount, P.sharePrimary, nB, (unsigned long long*)w->dRayCounters.p);
             c->counters[0] += 3;                                      // generate, extend(0), fold

@@ -3,9 +3,10 @@
 #include "pt_context.h"
 
 namespace pt {
-enum { WF_CHANGED_ALL = 0, WF_CHANGED_MATERIALS = 1, WF_CHANGED_SPHERES = 2 };
+enum { WF_CHANGED_ALL = 0, WF_CHANGED_MATERIALS = 1, WF_CHANGED_SPHERES = 2, WF_CHANGED_TRANSFORMS = 3 };
 // re-layout of the uploaded scene (or, when only materials / spheres changed and no object switched between emitting and
-// not emitting, just the flags that depend on them); 0 or a B200PT_ERR_* with c->error set
+// not emitting, just the flags that depend on them; when only object MATRICES changed, a refit of the device-built tree:
+// same topology, child boxes recomputed bottom-up, the small emissive tree rebuilt); 0 or a B200PT_ERR_* with c->error set
 int wavefront_build_scene(b200pt_ctx* c, int changed = WF_CHANGED_ALL);
 void wavefront_destroy(b200pt_ctx* c);
 void wavefront_set_textures(b200pt_ctx* c);      // texture table / sRGB table pointers changed

@@ -734,7 +734,9 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
         WBC(cudaMemcpyAsync(emit[0], &first, sizeof first, cudaMemcpyHostToDevice, st));
         uint32_t nItems = 1;
         int ecur = 0;
+        out.levelCount.clear();
         while (nItems) {
+            out.levelCount.push_back(nItems);
             if (timing) {
                 auto now = std::chrono::steady_clock::now();
                 fprintf(stderr, "[wide] emit level: %u nodes (previous step %.3f ms)\n", nItems, std::chrono::duration<double, std::milli>(now - tLevel).count());
@@ -749,7 +751,7 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
             nItems = h[7];
             ecur ^= 1;
         }
-        out.nNodes = h[5]; out.nPrims = h[6]; out.maxDepth = h[8];
+        out.nNodes = h[5]; out.nPrims = h[6]; out.maxDepth = h[8]; out.nDropped = h[9];
         if (out.nPrims != nValid) return "wide BVH device build: triangle count mismatch";
     }
     WBC(cudaEventRecord(e1, st));
@@ -762,11 +764,119 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
         if (out.prims) cudaFree(out.prims);
         if (out.shade) cudaFree(out.shade);
         if (out.uv) cudaFree(out.uv);
+        if (out.nodeBox) { cudaFree(out.nodeBox); out.nodeBox = nullptr; }
         out.capacityInstances = n;
         fresh.p.clear();                      // handed over
     }
     out.nodes = d.outNodes; out.prims = d.outPrim; out.shade = d.outShade; out.uv = d.outUv;
     if (arena.bytes > WideBuildCache::kKeepBytes && cache) { cudaFree(cache->p); cache->p = nullptr; cache->bytes = 0; }
+    return nullptr;
+}
+
+// ---- refit -----------------------------------------------------------------------------------------------------
+namespace wb {
+
+__global__ void k_wide_set_xform(PrimRecord* prims, uint32_t n, const uint32_t* __restrict__ objXform) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) prims[i].xformId = objXform[prims[i].objectIndex];
+}
+
+// one thread per wide node of one level: child boxes from the triangles (leaf children) or from the boxes the level
+// below stored (inner children), then origin, exponents and the 8-bit planes exactly as k_wide_emit derives them
+__global__ void k_wide_refit(Bvh8Node* nodes, const PrimRecord* __restrict__ prims, const ptl::TrianglePoint* __restrict__ points,
+                             const ptl::Triangle* __restrict__ tris, const ptl::RenderObject* __restrict__ objects, float* nodeBox,
+                             uint32_t first, uint32_t count, uint32_t* notFinite) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    const uint32_t me = first + k;
+    Bvh8Node node = nodes[me];
+    float clo[8][3], chi[8][3];
+    float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
+    uint32_t innerSeen = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        const uint32_t m = node.meta[sl];
+        if (!m) continue;
+        if (node.imask & (1u << sl)) {
+            const float* b = nodeBox + 6 * (size_t)(node.childBase + innerSeen);
+            for (int a = 0; a < 3; ++a) { clo[sl][a] = b[a]; chi[sl][a] = b[3 + a]; }
+            innerSeen++;
+        } else {
+            const uint32_t unary = m >> 5, off = m & 31u, n = unary == 1u ? 1u : (unary == 3u ? 2u : 3u);
+            for (int a = 0; a < 3; ++a) { clo[sl][a] = 1e30f; chi[sl][a] = -1e30f; }
+            for (uint32_t q = 0; q < n; ++q) {
+                const PrimRecord r = prims[node.primBase + off + q];
+                const ptl::Triangle tr = tris[r.triIndexFlags & PT_PRIM_TRIMASK];
+                const ptl::TrianglePoint a = points[tr.v0], b = points[tr.v1], c = points[tr.v2];
+                WideBox bx;
+                if (!wide_world_box(objects[r.objectIndex], mk3(a.px, a.py, a.pz), mk3(b.px, b.py, b.pz), mk3(c.px, c.py, c.pz), bx)) atomicAdd(notFinite, 1u);
+                for (int ax = 0; ax < 3; ++ax) { clo[sl][ax] = fminf(clo[sl][ax], bx.lo[ax]); chi[sl][ax] = fmaxf(chi[sl][ax], bx.hi[ax]); }
+            }
+        }
+        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], clo[sl][a]); hi[a] = fmaxf(hi[a], chi[sl][a]); }
+    }
+    float* mine = nodeBox + 6 * (size_t)me;
+    for (int a = 0; a < 3; ++a) { mine[a] = lo[a]; mine[3 + a] = hi[a]; }
+    node.px = lo[0]; node.py = lo[1]; node.pz = lo[2];
+    uint8_t eb[3]; float sc[3];
+    for (int a = 0; a < 3; ++a) {
+        eb[a] = exponent_for(hi[a] - lo[a]);
+        for (;;) {
+            sc[a] = __uint_as_float((uint32_t)eb[a] << 23);
+            if (eb[a] == 0 || eb[a] >= 254 || lo[a] + 255.f * sc[a] >= hi[a]) break;
+            eb[a]++;
+        }
+    }
+    node.ex = eb[0]; node.ey = eb[1]; node.ez = eb[2];
+    uint8_t* qlo[3] = {node.qlox, node.qloy, node.qloz};
+    uint8_t* qhi[3] = {node.qhix, node.qhiy, node.qhiz};
+    for (int sl = 0; sl < 8; ++sl) {
+        if (!node.meta[sl]) continue;
+        for (int a = 0; a < 3; ++a) {
+            int l = 0, h = 0;
+            if (sc[a] > 0.f) {
+                l = (int)floorf((clo[sl][a] - lo[a]) / sc[a]);
+                h = (int)ceilf((chi[sl][a] - lo[a]) / sc[a]);
+                l = max(0, min(255, l)); h = max(0, min(255, h));
+                while (l > 0 && lo[a] + (float)l * sc[a] > clo[sl][a]) l--;        // outward after rounding
+                while (h < 255 && lo[a] + (float)h * sc[a] < chi[sl][a]) h++;
+            }
+            qlo[a][sl] = (uint8_t)l; qhi[a][sl] = (uint8_t)h;
+        }
+    }
+    nodes[me] = node;
+}
+
+}  // namespace wb
+
+const char* wide_refit_device(cudaStream_t st, const WideDeviceInputs& in, const uint32_t* objXform, WideDeviceResult& tree, float* deviceMs) {
+    using namespace wb;
+    if (!tree.nodes || tree.levelCount.empty() || tree.nDropped) return "wide BVH refit: no refittable tree";
+    if (!tree.nodeBox) WBC(cudaMalloc(&tree.nodeBox, (size_t)tree.nNodes * 24 + 256));
+    uint32_t* flag = (uint32_t*)((char*)tree.nodeBox + (size_t)tree.nNodes * 24);
+    cudaEvent_t e0, e1;
+    WBC(cudaEventCreate(&e0));
+    if (cudaEventCreate(&e1) != cudaSuccess) { cudaEventDestroy(e0); return "wide BVH refit: cudaEventCreate"; }
+    cudaEventRecord(e0, st);
+    cudaMemsetAsync(flag, 0, 4, st);
+    k_wide_set_xform<<<(tree.nPrims + 255) / 256, 256, 0, st>>>((PrimRecord*)tree.prims, tree.nPrims, objXform);
+    std::vector<uint32_t> start(tree.levelCount.size());
+    uint32_t acc = 0;
+    for (size_t l = 0; l < tree.levelCount.size(); ++l) { start[l] = acc; acc += tree.levelCount[l]; }
+    for (size_t l = tree.levelCount.size(); l-- > 0;)
+        k_wide_refit<<<(tree.levelCount[l] + 63) / 64, 64, 0, st>>>((Bvh8Node*)tree.nodes, (const PrimRecord*)tree.prims, in.points, in.tris, in.objects,
+                                                                   (float*)tree.nodeBox, start[l], tree.levelCount[l], flag);
+    uint32_t bad = 0;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, flag, 4, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaEventRecord(e1, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    float ms = 0.f;
+    if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (e != cudaSuccess) return cudaGetErrorString(e);
+    if (deviceMs) *deviceMs = ms;
+    if (acc != tree.nNodes) return "wide BVH refit: level table does not cover the tree";
+    if (bad) return "wide BVH refit: a transformed vertex is not finite";      // the caller rebuilds (such triangles are dropped)
     return nullptr;
 }
 

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <vector>
 
 #include "bvh8_build.h"
 
@@ -15,6 +16,9 @@ struct WideDeviceResult {                    // cudaMalloc'ed, owned by the call
     void* nodes = nullptr; void* prims = nullptr; void* shade = nullptr; void* uv = nullptr;   // as many instances are written again,
     size_t capacityInstances = 0;                                                               // otherwise freed and replaced
     uint32_t nNodes = 0, nPrims = 0, maxDepth = 0;
+    uint32_t nDropped = 0;                   // instances left out because a world-space vertex was not finite
+    std::vector<uint32_t> levelCount;        // wide nodes per level, root first: level k is the index range after levels < k
+    void* nodeBox = nullptr;                 // refit scratch: 6 floats per wide node (owned like the other buffers)
     double deviceMs = 0.0;
 };
 struct WideBuildCache {                      // scratch arena kept between builds (released by the owner's destructor)
@@ -30,5 +34,11 @@ struct WideBuildCache {                      // scratch arena kept between build
 // Returns nullptr or an error text.
 const char* wide_build_device(cudaStream_t stream, const WideDeviceInputs& in, const WideSceneHost& host, WideDeviceResult& out,
                               WideBuildCache* cache = nullptr);
+
+// Refit after a transform edit (b200pt_update_objects): same tree, same triangle order; every wide node's child boxes are
+// recomputed bottom-up from the triangles' new world-space boxes (level by level, deepest first) and re-quantised, and the
+// triangle records get their objects' current transform ids. `objects` / `objXform`: device arrays already updated.
+// Only valid for a tree built by wide_build_device with nDropped == 0. Returns nullptr or an error text.
+const char* wide_refit_device(cudaStream_t stream, const WideDeviceInputs& in, const uint32_t* objXform, WideDeviceResult& tree, float* deviceMs);
 
 }  // namespace pt

@@ -47,13 +47,14 @@ def _assert_explained(blobs, pc, W, H, frames, got, want, x0=0, y0=0, sx=1, sy=1
     path — in one of those frames — met its closest hit at EXACTLY the same distance on two triangles of one object (the
     one documented tie class, DESIGN.md §4 item 5: which of the two wins depends on the order a traversal meets them).
     Every differing pixel is re-traced by the oracle's tie detector (oracle_shader.cpp: pixel_ties) and must show such a
-    ray; and there may be no more than 1e-4 of them (two for small images)."""
+    ray; and there may be no more than 3e-4 of them per frame (two for small images)."""
     diff = (np.ascontiguousarray(got).view(np.uint32) != np.ascontiguousarray(want).view(np.uint32)).any(axis=2)
     nd = int(diff.sum())
     if nd == 0:
         return 0
     frames = list(frames)
-    assert nd <= max(2, 1e-4 * diff.size * len(frames)), "%d of %d pixels differ" % (nd, diff.size)
+    # measured rate of such ties on the tessellated atrium: 1.2e-4 of paths (73 of 576 x 1024); the explanation below is the check
+    assert nd <= max(2, 3e-4 * diff.size * len(frames)), "%d of %d pixels differ" % (nd, diff.size)
     ys, xs = np.nonzero(diff)
     xy = np.stack([x0 + xs * sx, y0 + ys * sy], 1).astype(np.uint32)
     sc = ob.OracleScene(blobs)
@@ -553,6 +554,47 @@ def test_wide_bvh_device_build_matches_host_build(gpu, bunny_blobs):
     cp2.copy_buffers(dict(blobs, objects=moved))
     cp2.render_frames(pc, 0, 3)
     _assert_explained(dict(blobs, objects=moved), pc, W, H, range(3), a, cp2.read_accum())
+
+
+def test_update_objects_refits_the_tree(gpu):
+    # UI "update objects" (src/vk_engine.cpp:1594-1603): with only matrices changed the device-built tree is refitted
+    # (same topology, boxes recomputed bottom-up) instead of rebuilt; the next frames must equal a fresh upload's,
+    # also when objects that shared one matrix stop sharing it and when an emissive object moves
+    from ray_tracer_b200 import PushConstants, scenes
+    blobs, info = scenes.statue_room(60_000)
+    W, H = 256, 144
+    pc = PushConstants(W, H, 10, info["objects"]).buffer
+    cp = _pass(gpu, blobs, W, H)
+    objs = blobs["objects"].copy()
+    for step, (obj, dx) in enumerate(((4, 0.3), (3, 0.12), (0, -0.05), (4, -0.2))):      # statue, light box, white walls, statue again
+        objs = objs.copy()
+        objs[obj * 80: obj * 80 + 64].view(np.float32)[12] += dx                       # column-major mat4: translate x
+        cp.update_buffer("objects", objs)
+        assert cp.get_option("last_update_was_refit") == 1, step
+        cp.clear()
+        cp.render_frames(pc, 0, 3)
+        a = cp.read_accum()
+        fresh = _pass(gpu, dict(blobs, objects=objs), W, H)
+        fresh.render_frames(pc, 0, 3)
+        _assert_explained(dict(blobs, objects=objs), pc, W, H, range(3), a, fresh.read_accum())
+        with ob.math_mode(1):
+            want, _ = ob.OracleScene(dict(blobs, objects=objs)).render_frames(pc, W, H, 0, 3)
+        _assert_explained(dict(blobs, objects=objs), pc, W, H, range(3), a, want)
+        fresh.close()
+    # a change of anything but the matrix re-lays the scene out; so does refit_on_update = 0
+    objs2 = objs.copy()
+    objs2.view(np.uint32).reshape(-1, 20)[4, 18] = 5                                   # the statue becomes dielectric
+    cp.update_buffer("objects", objs2)
+    assert cp.get_option("last_update_was_refit") == 0
+    cp.set_option("refit_on_update", 0)
+    cp.update_buffer("objects", objs)
+    assert cp.get_option("last_update_was_refit") == 0
+    cp.clear()
+    cp.render_frames(pc, 0, 3)
+    with ob.math_mode(1):
+        want, _ = ob.OracleScene(dict(blobs, objects=objs)).render_frames(pc, W, H, 0, 3)
+    _assert_explained(dict(blobs, objects=objs), pc, W, H, range(3), cp.read_accum(), want)
+    cp.close()
 
 
 def test_run_compute_one_sample_goes_through_the_wavefront(gpu, cornell_blobs, bunny_blobs):
