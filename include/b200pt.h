@@ -192,7 +192,10 @@ int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
  * traced work — what the kernels walked: [4] rays of the closest-hit launches (one primary ray per PIXEL when a batch
  * shares the primary hit between its frame slots), [5] occlusion walks, [6] exact pdf rays (evaluated lazily);
  * with option "count_work": [7] node visits and [8] triangle tests of the closest-hit kernel, [9] and [10] the same
- * for the occlusion kernel (wide layout: 80 B per node, 64 B per triangle record); [11..15] reserved. */
+ * for the occlusion kernel (wide layout: 80 B per node, 64 B per triangle record); [11] extension rays and [12]
+ * light-sample queries that were CONTESTED (two candidates closer together than the rounding slack of their distances:
+ * coincident surfaces) and were re-traced in the reference's own order over the reference's own buffers, so that the
+ * result is the reference's bit for bit; [13..15] reserved. */
 int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
 int b200pt_reset_counters(b200pt_ctx* ctx);
 /* With option "profile_stages" = 1 the wavefront records a CUDA event between consecutive launches; this

@@ -115,6 +115,13 @@ int orc_pixel_ties(void* scene, const void* pc208, int W, int H, uint32_t frame,
     return 0;
 }
 
+uint64_t orc_pixel_rays(void* scene, const void* pc208, int W, int H, uint32_t frame, uint32_t x, uint32_t y, uint64_t cap, float* rays8,
+                        void* hits48) {
+    ol::PushConstants pc;
+    std::memcpy(&pc, pc208, sizeof(pc));
+    return pixel_rays(*(Scene*)scene, pc, W, H, frame, x, y, (size_t)cap, rays8, (HitOut*)hits48);
+}
+
 void orc_set_math_mode(int mode) { orc::set_math_mode(mode); }
 int orc_math_mode() { return orc::math_mode(); }
 float orc_random(uint32_t* state) { return orc::random(*state); }

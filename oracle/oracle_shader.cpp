@@ -65,6 +65,9 @@ struct Ctx {
     // (the reference keeps the first in its own loop order, raytrace.comp:316). Does not change any result.
     bool detectTies = false;
     uint32_t ties = 0;
+    // Ray recorder (tests only, pixel_rays()): every calculateIntersections call of one pixel's path with its result.
+    std::vector<float>* recRays = nullptr;      // 8 floats per ray
+    std::vector<HitOut>* recHits = nullptr;
 };
 
 vec3 v3(const float* p) { return vec3(p[0], p[1], p[2]); }
@@ -263,6 +266,19 @@ HitInfo calculateIntersections(Ctx& cx, const Ray& ray, float* stats) {
 
     if (closestHit.didHit) cx.work.n_hit++;
     if (cx.detectTies && closestHit.didHit && closestHit.kind == 2 && tieDst == closestHit.dst) cx.ties++;
+    if (cx.recRays) {
+        const float r8[8] = {ray.origin.x, ray.origin.y, ray.origin.z, 0.f, ray.dir.x, ray.dir.y, ray.dir.z, 0.f};
+        cx.recRays->insert(cx.recRays->end(), r8, r8 + 8);
+        HitOut o;
+        std::memset(&o, 0, sizeof(o));
+        o.dst = closestHit.dst;
+        o.kind = closestHit.didHit ? closestHit.kind : 0;
+        o.objectHitIndex = closestHit.didHit ? closestHit.objectHitIndex : 0xffffffffu;
+        o.triHitIndex = closestHit.didHit ? closestHit.triHitIndex : 0;
+        o.materialIndex = closestHit.materialIndex;
+        o.frontFace = closestHit.didHit ? (closestHit.frontFace ? 1u : 0u) : 0u;
+        cx.recHits->push_back(o);
+    }
     if (stats) {
         cx.ext.n_box += cx.work.n_box - before.n_box; cx.ext.n_tri += cx.work.n_tri - before.n_tri;
         cx.ext.n_obj += cx.work.n_obj - before.n_obj; cx.ext.n_sph += cx.work.n_sph - before.n_sph;
@@ -687,6 +703,22 @@ void pixel_ties(const Scene& sc, const ol::PushConstants& pc_in, int W, int H, u
         shade_pixel(cx, xy[2 * i], xy[2 * i + 1], W, H);
         ties[i] = cx.ties;
     }
+}
+
+// Every calculateIntersections call on the path of pixel (x, y) of frame `frame`, in call order (extension ray, then for
+// a diffuse bounce the NEE ray and the two pdf rays), with the hit the oracle found. Returns the number of rays; fills up
+// to `cap`. Lets a test replay the oracle's own rays through another traversal and find the first ray that differs.
+size_t pixel_rays(const Scene& sc, const ol::PushConstants& pc_in, int W, int H, uint32_t frame, uint32_t x, uint32_t y, size_t cap,
+                  float* rays8, HitOut* hits) {
+    ol::PushConstants pc = pc_in;
+    pc.frameCount = frame;
+    std::vector<float> rr; std::vector<HitOut> hh;
+    Ctx cx{sc, pc, Work(), Work()};
+    cx.recRays = &rr; cx.recHits = &hh;
+    shade_pixel(cx, x, y, W, H);
+    const size_t n = hh.size(), m = n < cap ? n : cap;
+    if (m) { std::memcpy(rays8, rr.data(), m * 32); std::memcpy(hits, hh.data(), m * sizeof(HitOut)); }
+    return n;
 }
 
 void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays, size_t n, HitOut* out, Work* work,

@@ -85,6 +85,9 @@ void trace_batch(const Scene& sc, const ol::PushConstants& pc, const float* rays
 void pixel_ties(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t frame, const uint32_t* xy, size_t n,
                 uint32_t* ties);
 
+size_t pixel_rays(const Scene& sc, const ol::PushConstants& pc, int W, int H, uint32_t frame, uint32_t x, uint32_t y, size_t cap,
+                  float* rays8, HitOut* hits);
+
 // 0 = libm transcendentals (default), 1 = the backend's portable double-precision polynomials
 void set_math_mode(int mode);
 int math_mode();

@@ -1,0 +1,12 @@
+#!/bin/bash
+set -x
+cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
+mkdir -p gpurun_out
+timeout 900 python profiles/tools/debug_mismatch.py 1024 32 18 > gpurun_out/r02e_mismatch.txt 2> gpurun_out/r02e_mismatch.err
+timeout 1800 python -m pytest tests -m gpu -q --durations=8 > gpurun_out/r02e_gputests.log 2>&1; echo "gputests rc=$?" >> gpurun_out/r02e_gputests.log
+timeout 900 python bench.py --steps 5 --warmup 3 > gpurun_out/r02e_bench_atrium.json 2> gpurun_out/r02e_bench_atrium.err
+for v in mb6 n2; do
+  B200PT_LIB=$PWD/ray_tracer_b200/libb200pt_$v.so timeout 600 python bench.py --steps 5 --warmup 3 --only-value > gpurun_out/r02e_bench_$v.json 2> gpurun_out/r02e_bench_$v.err
+done
+grep -h -o '"value": [0-9.]*' gpurun_out/r02e_bench_*.json
+head -5 gpurun_out/r02e_mismatch.txt

@@ -264,7 +264,7 @@ class ComputePass:
         return dict(launches=int(c[0]), paths=int(c[1]), extension_rays=int(c[2]), connect_items=int(c[3]),
                     extension_rays_traced=int(c[4]), occlusion_rays_traced=int(c[5]), pdf_rays_traced=int(c[6]),
                     extend_node_visits=int(c[7]), extend_tri_tests=int(c[8]), occlude_node_visits=int(c[9]),
-                    occlude_tri_tests=int(c[10]))
+                    occlude_tri_tests=int(c[10]), exact_extension_rays=int(c[11]), exact_light_queries=int(c[12]))
 
     STAGES = ("generate", "extend", "shade", "connect_prep", "accumulate", "occlude", "connect_finish")
 

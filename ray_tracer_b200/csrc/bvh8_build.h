@@ -35,7 +35,20 @@ struct WideSceneHost {
     float emisLo[3] = {0, 0, 0}, emisHi[3] = {0, 0, 0};
     // for the device build of `all` (wide_build.cu): every (object, triangle) instance and the BVH2 leaf of each triangle
     std::vector<uint32_t> instObject, instTri, leafOf;
+    // (object, triangle) -> record index in all.prims (WideScene::primOf): per object the first slot and its lowest triangle
+    // index (an object's triangles are one contiguous range of the reference's `triangles`); primOf itself is filled from
+    // the finished tree (host: fill_prim_of below; device build: k_wide_prim_of)
+    std::vector<uint32_t> instBase, triFirst, primOf;
+    uint32_t nInstSlots = 0;
 };
+
+inline void fill_prim_of(WideSceneHost& out) {
+    out.primOf.assign(out.nInstSlots, 0xffffffffu);
+    for (size_t i = 0; i < out.all.prims.size(); ++i) {
+        const PrimRecord& r = out.all.prims[i];
+        out.primOf[out.instBase[r.objectIndex] + (r.triIndexFlags & PT_PRIM_TRIMASK) - out.triFirst[r.objectIndex]] = (uint32_t)i;
+    }
+}
 
 struct WideBox { float lo[3], hi[3]; };
 
@@ -450,6 +463,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     std::vector<ShadeRecord> shade, shadeE;
     std::vector<UvRecord> uvs, uvsE;
     std::vector<uint32_t> stack, triList;
+    out.instBase.assign(objects.size(), 0); out.triFirst.assign(objects.size(), 0); out.nInstSlots = 0;
     for (size_t o = 0; o < objects.size(); ++o) {
         const ptl::RenderObject& ob = objects[o];
         // triangles of this object = leaves under its BVH root (instances share bvhIndex: src/vk_engine.cpp:802-815)
@@ -460,6 +474,12 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
             const ptl::BVHNode& nd = nodes[stack.back()]; stack.pop_back();
             if (nd.triCount) for (uint32_t t = nd.index; t < nd.index + nd.triCount; ++t) triList.push_back(t);
             else { stack.push_back(nd.index + 1); stack.push_back(nd.index); }
+        }
+        if (!triList.empty()) {
+            uint32_t lo = triList[0], hi = triList[0];
+            for (uint32_t t : triList) { lo = std::min(lo, t); hi = std::max(hi, t); }
+            out.instBase[o] = out.nInstSlots; out.triFirst[o] = lo;
+            out.nInstSlots += hi - lo + 1;
         }
         bool em = emissive(ob.materialIndex);
         if (em && !triList.empty()) out.anyEmissive = true;
@@ -485,7 +505,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
     }
     if (std::getenv("B200PT_BUILD_TIMING"))
         fprintf(stderr, "[bvh8] records of %zu triangles: %.3f s\n", boxes.size(), std::chrono::duration<double>(std::chrono::steady_clock::now() - tPrep).count());
-    if (buildAll) bvh8_build(boxes, inst, prim, shade, uvs, out.all);
+    if (buildAll) { bvh8_build(boxes, inst, prim, shade, uvs, out.all); fill_prim_of(out); }
     else out.leafOf = leafOf;      // `all` is built on the device from instObject / instTri / leafOf
     bvh8_build(boxesE, instE, primE, shadeE, uvsE, out.emis);
     if (out.all.maxDepth > PT_BVH8_MAX_DEPTH || out.emis.maxDepth > PT_BVH8_MAX_DEPTH) return "wide BVH deeper than the traversal stack";

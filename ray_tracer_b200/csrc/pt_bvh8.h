@@ -97,6 +97,9 @@ struct WideScene {
     const ptl::Sphere* spheres;
     const ptl::Material* materials;
     const uint32_t* objXform;  // object -> xformId
+    // (object, reference triangle index) -> index of its record in all.prims, for hits found by the reference-order
+    // re-trace of contested rays: primOf[instBase[object] + triangle - triFirst[object]]
+    const uint32_t* primOf; const uint32_t* instBase; const uint32_t* triFirst;
     uint32_t nXforms, nSpheres, nMaterials, nObjects;
     uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
     uint32_t emissionFinite;   // every material's emissionColor * emissionStrength is finite

@@ -23,6 +23,7 @@ struct RefScene {
 struct RefHit {
     v3 hp, n;
     float dst;
+    float u, v;                 // barycentrics of a triangle hit (raytrace.comp:239-240)
     uint32_t objectHitIndex, triHitIndex, materialIndex;
     uint32_t kind;              // 0 miss, 1 sphere, 2 triangle
     bool front;
@@ -42,6 +43,7 @@ PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerDa
     best.front = false;
     best.hp = splat3(0.f);
     best.n = splat3(0.f);
+    best.u = 0.f; best.v = 0.f;
 
     for (uint32_t i = 0; i < td.sphereCount; i++) {
         float dst; bool front;
@@ -75,7 +77,7 @@ PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerDa
                     TriEdges te = tri_edges(mk3(a.px, a.py, a.pz), mk3(b.px, b.py, b.pz), mk3(c.px, c.py, c.pz));
                     float dst, u, v; bool front;
                     if (tri_test(te, tr, tri.frontOnly != 0, dst, u, v, front) && dst < best.dst) {
-                        best.kind = 2; best.dst = dst; best.front = front;
+                        best.kind = 2; best.dst = dst; best.front = front; best.u = u; best.v = v;
                         best.triHitIndex = j; best.objectHitIndex = i; best.materialIndex = obj.materialIndex;
                         tri_surface(obj.m, tr, dst, u, v, front, mk3(a.nx, a.ny, a.nz), mk3(b.nx, b.ny, b.nz),
                                     mk3(c.nx, c.ny, c.nz), best.hp, best.n);

@@ -271,6 +271,32 @@ PT_HD TriEdges prim_edges(const PrimRecord& p) {
     return t;
 }
 
+// ---- exactness against the reference's traversal ORDER -----------------------------------------------------------
+// The reference prunes a BVH2 node when its slab distance is not below the closest hit found SO FAR in its own loop
+// order (raytrace.comp:346-347), so which triangles it tests depends on history. Taking the minimum over all reachable
+// triangles is the same answer EXCEPT when a triangle's hit distance dst_T is not above the slab distance b_T of one of
+// its enclosing boxes — possible only by rounding (triangle on a box face: b_T - dst_T is a few ulps) — and another
+// candidate lies in between: the reference then never tests T. Analysis: the two answers can
+// differ only if two reachable candidates are closer together than delta = |b_T - dst_T| <= the rounding error of the
+// Moeller-Trumbore distance (the slab distance itself is accurate to 3 ulp: lo - o is a difference of two floats).
+// tri_dst_slack() bounds that error from the condition numbers of the two dot products and of the cross product;
+// a ray on which two candidates come closer than the sum of their slacks is CONTESTED and is re-traced in the
+// reference's own order (pt_reftrace.h: ref_closest_hit — k_exact_* in wavefront.cu). That also settles hits at exactly
+// equal distance on two triangles of one object, the former "documented tie class": there is none left.
+// Nodes are culled against best + 2 slack, so a competitor within the best hit's slack is always tested.
+#ifndef PT_SLACK_K
+#define PT_SLACK_K 1e-6f      /* ~16 eps per rounding step of the bound below */
+#endif
+PT_HD float maxabs3(v3 a) { return fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fabsf(a.z)); }
+PT_HD float tri_dst_slack(const TriEdges& t, const Ray& r, float dst) {
+    const v3 rov0 = r.o - t.p0;
+    const float an = fabsf(rov0.x * t.n.x) + fabsf(rov0.y * t.n.y) + fabsf(rov0.z * t.n.z);      // |dot(rov0, n)| without cancellation
+    const float ad = fabsf(r.d.x * t.n.x) + fabsf(r.d.y * t.n.y) + fabsf(r.d.z * t.n.z);         // |dot(d, n)| without cancellation
+    const float d0 = fabsf(dot(r.d, t.n));
+    const float cr = maxabs3(t.e1) * maxabs3(t.e2) * (maxabs3(rov0) + fabsf(dst) * maxabs3(r.d)); // rounding of cross(e1, e2)
+    return PT_SLACK_K * fabsf(dst) + PT_SLACK_K * (an + fabsf(dst) * ad + 3.f * cr) / d0;
+}
+
 // ---- traversal as per-ray steps ---------------------------------------------------------------
 // The state of one ray's walk through the wide BVH. Work items are "groups": a node group
 // (base = first inner child, bits 31..24 = children still to visit in priority order, bits 7..0 =
@@ -285,11 +311,14 @@ struct Trav {
     uint32_t gBase, gBits;      // current node group
     uint32_t tBase, tBits;      // current triangle group
     int sp;
+    float bestSlack;            // distance slack of the current best hit (tri_dst_slack; 0 for a sphere or none)
+    uint32_t contested;         // two reachable candidates closer together than their slacks: the ray is re-traced in reference order
 };
 PT_HD void trav_begin(Trav& t, const Ray& ray) {
     t.ray = ray; t.br = make_box_ray(ray); t.oc.xform = 0xffffffffu;
     t.gBase = 0; t.gBits = 0x80000000u;               // the root as the only child of a virtual group
     t.tBase = 0; t.tBits = 0; t.sp = 0;
+    t.bestSlack = 0.f; t.contested = 0u;
 }
 // The per-ray stack of groups. PrivateStack: two arrays in thread-private (local) memory. The persistent kernels use
 // a SplitStack (wavefront.cu): the first PT_BVH8_SHARED_STACK entries live in shared memory, [entry][thread] so that a
@@ -373,51 +402,77 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
     if (p.objectIndex >= objectCount) return;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
     float dst, u, v; bool front;
-    if (tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
-        (dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key)) && ref_reachable(up, p, t.oc, dst)) {
+    const TriEdges te = prim_edges(p);
+    if (!tri_test(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front)) return;
+    const bool wins = dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key);
+    const float gap = fabsf(dst - hit.dst);
+    // only a hit that wins, or one that comes within the best hit's slack, can change the answer
+    if (!(wins || gap <= 2.f * t.bestSlack) || !ref_reachable(up, p, t.oc, dst)) return;
+    const float slack = tri_dst_slack(te, tr, dst);
+    if (hit.id != PT_HIT_MISS && gap <= slack + t.bestSlack && (hit.id & ~PT_HIT_FRONT) != pi) t.contested = 1u;
+    if (wins) {
         hit.dst = dst; hit.u = u; hit.v = v;
         hit.id = pi | (front ? PT_HIT_FRONT : 0u);
         key = nSpheres + p.objectIndex;
+        t.bestSlack = slack;
     }
 }
 // Occlusion form: is the next triangle a NON-emissive hit that the reference's closest-hit search
 // would have preferred to an emissive hit at (tE, keyE)? (strictly closer, or equal distance and
-// earlier in the reference's loop order)
-PT_HD bool trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                  Trav& t, float tE, uint32_t keyE) {
+// earlier in the reference's loop order) -> PT_OCCL_YES. A reachable hit within the slacks of tE on either side makes
+// the query CONTESTED (see above): PT_OCCL_CONTESTED, answered by the reference-order search.
+#define PT_OCCL_NO 0
+#define PT_OCCL_YES 1
+#define PT_OCCL_CONTESTED 2
+PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
+                                 Trav& t, float tE, uint32_t keyE, float slackE) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     const PrimRecord p = load_prim(bvh.prims, t.tBase + (uint32_t)k);
-    if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) return false;
+    if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) return PT_OCCL_NO;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
     float dst, u, v; bool front;
-    return tri_test(prim_edges(p), tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front) &&
-           (dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE)) && ref_reachable(up, p, t.oc, dst);
+    const TriEdges te = prim_edges(p);
+    if (!tri_test(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front)) return PT_OCCL_NO;
+    const bool closer = dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE);
+    const float gap = fabsf(dst - tE);
+    if (!(closer || gap <= 2.f * slackE) || !ref_reachable(up, p, t.oc, dst)) return PT_OCCL_NO;
+    if (gap <= tri_dst_slack(te, tr, dst) + slackE) return PT_OCCL_CONTESTED;
+    return closer ? PT_OCCL_YES : PT_OCCL_NO;
 }
 
-// Per-ray loops over the steps (host emulation, b200pt_trace_batch, the small emissive BVH).
+// Per-ray loops over the steps (host emulation, the small emissive BVH). `contested` is OR-ed, `slack` returns the
+// best hit's slack.
 PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, Hit& hit, uint32_t& key) {
+                                 uint32_t objectCount, Hit& hit, uint32_t& key, uint32_t& contested, float& slack) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     for (;;) {
         if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, t, hit, key);
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, hit.dst);
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, hit.dst + 2.f * t.bestSlack);
         else if (!trav_pop(t, stack)) break;
     }
+    contested |= t.contested;
+    slack = t.bestSlack;
 }
-PT_HD_NOINLINE bool bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                  uint32_t objectCount, float tE, uint32_t keyE) {
+// -> PT_OCCL_NO / PT_OCCL_YES / PT_OCCL_CONTESTED
+PT_HD_NOINLINE int bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
+                                 uint32_t objectCount, float tE, uint32_t keyE, float slackE) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
+    int contested = PT_OCCL_NO;
     for (;;) {
-        if (trav_has_tri(t)) { if (trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, t, tE, keyE)) return true; }
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, tE);
+        if (trav_has_tri(t)) {
+            const int r = trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, t, tE, keyE, slackE);
+            if (r == PT_OCCL_YES) return PT_OCCL_YES;
+            if (r == PT_OCCL_CONTESTED) contested = PT_OCCL_CONTESTED;
+        }
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, tE + 2.f * slackE);
         else if (!trav_pop(t, stack)) break;
     }
-    return false;
+    return contested;
 }
 
 }  // namespace pt

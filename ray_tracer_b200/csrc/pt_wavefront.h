@@ -16,6 +16,7 @@
 // query against the rest, instead of two more full closest-hit searches.
 #pragma once
 #include "pt_traverse.h"
+#include "pt_reftrace.h"
 
 namespace pt {
 
@@ -103,15 +104,30 @@ PT_HD void spheres_closest(const WideScene& sc, const Ray& ray, uint32_t sphereC
         }
     }
 }
-PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount) {
-    Hit h; uint32_t key;
+PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereCount, uint32_t objectCount, uint32_t& contested) {
+    Hit h; uint32_t key; float slack;
     spheres_closest(sc, ray, sphereCount, h, key);
-    bvh8_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, ray, objectCount, h, key);
+    bvh8_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, ray, objectCount, h, key, contested, slack);
     return h;
 }
-PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
+// The hit of a CONTESTED ray (pt_traverse.h): calculateIntersections in the reference's own order over the reference's own
+// buffers (pt_reftrace.h), expressed as the wavefront's Hit (record index of the triangle in the wide layout).
+PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl::RayTracerData& td, const Ray& ray) {
+    const RefHit r = ref_closest_hit(ref, td, ray, nullptr);
+    Hit h; h.dst = r.dst; h.u = 0.f; h.v = 0.f; h.id = PT_HIT_MISS;
+    if (r.kind == 1u) h.id = PT_HIT_SPHERE | (r.front ? PT_HIT_FRONT : 0u) | r.triHitIndex;
+    else if (r.kind == 2u) {
+        h.id = sc.primOf[sc.instBase[r.objectHitIndex] + r.triHitIndex - sc.triFirst[r.objectHitIndex]] | (r.front ? PT_HIT_FRONT : 0u);
+        h.u = r.u; h.v = r.v;
+    }
+    return h;
+}
+PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const RefScene& ref, const PathArrays& A, uint32_t p) {
     Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-    A.hit[p] = wide_closest_hit(sc, r, P.pc.params.sphereCount, P.pc.params.objectCount);
+    uint32_t contested = 0u;
+    Hit h = wide_closest_hit(sc, r, P.pc.params.sphereCount, P.pc.params.objectCount, contested);
+    if (contested) h = exact_closest_hit(ref, sc, P.pc.params, r);
+    A.hit[p] = h;
 }
 
 // World-space hit point, shading normal and material of a Hit (raytrace.comp:218-221 for spheres;
@@ -291,7 +307,7 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 //   occlude : is there a non-emissive triangle the reference would have preferred? (bounded any-hit
 //             walk of the full BVH, the expensive part: its own persistent kernel, wavefront.cu)
 //   finish  : pdfs, MIS weights, direct light (raytrace.comp:447-460)
-// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, - }, tE < 0: no emissive closest hit
+// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, slack of tE }, tE < 0: no emissive closest hit
 // (none found, or occluded). Those paths keep the directLight shade stored (a zero: E = 0, pdf = 0); finish only reads
 // their qE. (Finishing the unoccluded ones inside the occlusion kernel, by the lane that ends the walk, was measured:
 // k_connect_finish 3.7 -> 0 ms but k_occlude 35.3 -> 39.7 ms per step — four dependent loads in a converged warp.)
@@ -311,9 +327,11 @@ PT_HD bool ray_meets_box(const Ray& r, const float* lo, const float* hi) {
 }
 // Sphere slots are split at upload into emissive / non-emissive bit masks (WideScene), so the two
 // loops below touch only the spheres that matter; with more than 32 slots every slot is visited.
+// contested / slackE: see pt_traverse.h ("exactness against the reference's traversal order") — two emissive candidates, or
+// the emissive candidate and a sphere, closer together than the slack: the caller asks the reference-order search.
 PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
-                               uint32_t& matOut) {
-    matOut = 0u; keyE = 0xffffffffu;
+                               uint32_t& matOut, uint32_t& contested, float& slackE) {
+    matOut = 0u; keyE = 0xffffffffu; slackE = 0.f;
     if (!sc.anyEmissive) return PT_NO_EMISSIVE;
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
@@ -335,45 +353,62 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
         }
     }
     uint32_t before = e.id;
-    if (sc.emis.nPrims && ray_meets_box(r, sc.emisLo, sc.emisHi)) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE);
+    if (sc.emis.nPrims && ray_meets_box(r, sc.emisLo, sc.emisHi)) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, e, keyE, contested, slackE);
     if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
+    else slackE = 0.f;                                           // a sphere won: spheres are never pruned by the reference
     if (masks) {
         for (uint32_t mk = sc.plainSphereMask & live; mk; mk &= mk - 1u) {
             uint32_t i = (uint32_t)lowest_bit(mk);
             float dst; bool front;
-            if (sphere_test(sc.spheres[i], r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
+            if (sphere_test(sc.spheres[i], r, dst, front)) {
+                if (fabsf(dst - e.dst) <= slackE) contested = 1u;     // the reference tests spheres first: the triangle may be pruned against it
+                if (dst < e.dst || (dst == e.dst && i < keyE)) return PT_NO_EMISSIVE;
+            }
         }
     } else {
         for (uint32_t i = 0; i < sphereCount; i++) {
             const ptl::Sphere s = sc.spheres[i];
             if (!(sc.materials[s.materialIndex].emissionStrength == 0.f)) continue;
             float dst; bool front;
-            if (sphere_test(s, r, dst, front) && (dst < e.dst || (dst == e.dst && i < keyE))) return PT_NO_EMISSIVE;
+            if (sphere_test(s, r, dst, front)) {
+                if (fabsf(dst - e.dst) <= slackE) contested = 1u;
+                if (dst < e.dst || (dst == e.dst && i < keyE)) return PT_NO_EMISSIVE;
+            }
         }
     }
     return e.dst;
 }
 
 #define PT_CONNECT_JOB_LIGHT 1u     /* occlusion query pending for the light-sample ray */
+#define PT_CONNECT_JOB_EXACT 2u     /* contested: the reference-order search answers (connect_exact) */
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
-    uint32_t keyL = 0xffffffffu, matL = 0u;
-    float tL = PT_NO_EMISSIVE;
+    uint32_t keyL = 0xffffffffu, matL = 0u, contested = 0u;
+    float tL = PT_NO_EMISSIVE, slackL = 0.f;
     // connectAfterExtend: bounce j+1 was already extended; directLight of bounce j is dropped when it missed (:531-534)
     bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
     if (!dropped)            // (rays that cannot contribute never get here: stage_shade)
-        tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL);  // :443-447
-    A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), 0.f);
+        tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL, contested, slackL);  // :443-447
+    A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), slackL);
+    if (contested) return PT_CONNECT_JOB_EXACT;
     return tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u;
 }
 // the occlusion query of path p's light-sample ray
-PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, uint32_t& keyE) {
+PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, uint32_t& keyE, float& slackE) {
     float4 e = A.qE[p];
     r.o = xyz(A.qO[p]);
     r.d = xyz(A.qL[p]);
     tE = e.x;
     keyE = as_uint(e.z);
+    slackE = e.w;
+}
+// A contested light-sample ray: lightSamplePDF's closest-hit search (raytrace.comp:396-397) in the reference's own order.
+PT_HD void connect_exact(const RefScene& ref, const ptl::RayTracerData& td, const PathArrays& A, uint32_t p) {
+    Ray r; r.o = xyz(A.qO[p]); r.d = xyz(A.qL[p]);
+    const RefHit h = ref_closest_hit(ref, td, r, nullptr);
+    const bool emissive = h.kind != 0u && !(ref.materials[h.materialIndex].emissionStrength == 0.f);
+    A.qE[p] = make_float4(emissive ? h.dst : PT_NO_EMISSIVE, as_float(h.materialIndex), 0.f, 0.f);
 }
 PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p) {
     reinterpret_cast<float*>(&A.qE[p])[0] = PT_NO_EMISSIVE;
@@ -395,29 +430,26 @@ PT_HD bool connect_job_finish(const WideScene& sc, const PathArrays& A, uint32_t
     A.direct[p] = f4(direct, 0.f);
     return direct.x == -1.f;
 }
-PT_HD_NOINLINE void connect_mis_weight_exact(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
-    const ptl::RayTracerData& td = P.pc.params;
+PT_HD_NOINLINE void connect_mis_weight_exact(const RefScene& ref, const ptl::RayTracerData& td, const PathArrays& A, uint32_t p) {
     v3 origin = xyz(A.qO[p]), cosineSample = xyz(A.rayD[p]);
     float realCosinePDF = A.qL[p].w;
-    uint32_t keyC, matC;
-    float tC = emissive_candidate(sc, origin, cosineSample, td.sphereCount, td.objectCount, keyC, matC);    // :453
-    if (tC >= 0.f) {
-        Ray r; r.o = origin; r.d = cosineSample;
-        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, td.objectCount, tC, keyC)) tC = PT_NO_EMISSIVE;
-    }
-    float lightPDF = tC >= 0.f ? light_pdf_from_dst(tC, cosineSample) : 0.f;
+    float lightPDF = ref_light_pdf(ref, td, origin, cosineSample);                                          // :453, in the reference's order
     float4 ro = A.rayO[p];
     ro.w = mis_weight(realCosinePDF, lightPDF);                                                            // :455-456
     A.rayO[p] = ro;
 }
 // all parts for one path (host emulation; the kernels run them as separate launches)
-PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
-    if (stage_connect_prep(P, sc, A, p)) {
-        Ray r; float tE; uint32_t keyE;
-        connect_job_ray(A, p, r, tE, keyE);
-        if (bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE)) connect_job_occluded(A, p);
+PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const RefScene& ref, const PathArrays& A, uint32_t p) {
+    uint32_t job = stage_connect_prep(P, sc, A, p);
+    if (job == PT_CONNECT_JOB_LIGHT) {
+        Ray r; float tE, slackE; uint32_t keyE;
+        connect_job_ray(A, p, r, tE, keyE, slackE);
+        const int o = bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, tE, keyE, slackE);
+        if (o == PT_OCCL_YES) connect_job_occluded(A, p);
+        else if (o == PT_OCCL_CONTESTED) job = PT_CONNECT_JOB_EXACT;
     }
-    if (connect_job_finish(sc, A, p)) connect_mis_weight_exact(P, sc, A, p);
+    if (job == PT_CONNECT_JOB_EXACT) connect_exact(ref, P.pc.params, A, p);
+    if (connect_job_finish(sc, A, p)) connect_mis_weight_exact(ref, P.pc.params, A, p);
 }
 
 // ---- accumulate -----------------------------------------------------------------------------

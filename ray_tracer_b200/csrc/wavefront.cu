@@ -26,6 +26,8 @@ struct WavefrontState {
     // path state
     DeviceBuffer dPaths[9];
     DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters, dSampleSum;
+    DeviceBuffer dExactQ, dExactNeeQ;  // contested rays / light-sample queries: re-traced in the reference's order (pt_traverse.h)
+    DeviceBuffer dPrimOf, dInstBase, dTriFirst;
     PathArrays arrays{};
     WideDeviceResult wideRes;          // device-built tree (owned here; dNodes / dPrims / dShade / dUv alias it while wideOnDevice)
     WideBuildCache wideCache;
@@ -87,6 +89,7 @@ void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool
 }
 
 #define WF_THREADS 128
+#define WF_COUNT_ARRAYS 9        /* per-bounce device counters: qCount sCount workE workO oCount primaryCount mCount xCount xnCount */
 #define WF_RAY_COUNTERS 16      /* device-side u64 counters: k_fold's five, then work counters [8..11] (option count_work) */
 
 static __device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred) {
@@ -184,10 +187,13 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
 }
 
 #ifndef PT_TRI_PER_STEP
-#define PT_TRI_PER_STEP 1          /* triangles a lane tests per triangle step of the warp (A/B knob) */
+#define PT_TRI_PER_STEP 2          /* triangles a lane tests per triangle step of the warp: 1 / 2 / 3 -> 310.1 / 318.9 / 311.5 Mpaths/s (fewer votes per triangle) */
+#endif
+#ifndef PT_NODE_PER_STEP
+#define PT_NODE_PER_STEP 1         /* node visits per node step for lanes that came out of the first one without triangles (A/B knob) */
 #endif
 #ifndef PT_TRI_PER_STEP_OCCL
-#define PT_TRI_PER_STEP_OCCL 1     /* the same for k_occlude */
+#define PT_TRI_PER_STEP_OCCL 2     /* the same for k_occlude: 1 / 2 / 3 -> 321.2 / 326.4 / 324.8 */
 #endif
 #ifndef PT_EXTEND_MIN_BLOCKS
 #define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
@@ -203,7 +209,8 @@ static __device__ __forceinline__ void flush_work(unsigned long long* work, uint
 template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
-                                                       uint32_t* workCounter, Hit* __restrict__ hitOut, unsigned long long* work) {
+                                                       uint32_t* workCounter, Hit* __restrict__ hitOut, uint32_t* exactQueue, uint32_t* exactCount,
+                                                       unsigned long long* work) {
     uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *qCount;
     const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
@@ -219,6 +226,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         // lanes with nothing in hand take the next group from their stack, or finish
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
             hitOut[p] = hit;
+            if (t.contested) exactQueue[atomicAdd(exactCount, 1u)] = p;      // rare (coincident surfaces): k_exact_extend overwrites the hit
             busy = false;
         }
         const bool hasTri = busy && trav_has_tri(t);
@@ -246,7 +254,11 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
                 }
             }
         } else {
-            if (canNode) { trav_node_step(sc.all, t, stack, hit.dst); if (COUNT) cntNode++; }
+            if (canNode) {
+                trav_node_step(sc.all, t, stack, hit.dst + 2.f * t.bestSlack); if (COUNT) cntNode++;
+#pragma unroll 1
+                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, hit.dst + 2.f * t.bestSlack); if (COUNT) cntNode++; }
+            }
         }
     }
     if (COUNT) flush_work(work, cntNode, cntTri);
@@ -330,7 +342,7 @@ __global__ void __launch_bounds__(SHADE_THREADS, PT_SHADE_MIN_BLOCKS) k_shade(co
 #endif
 __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                              const uint32_t* __restrict__ queue, const uint32_t* __restrict__ sCount,
-                                                             uint32_t* jobQueue, uint32_t* jobCount) {
+                                                             uint32_t* jobQueue, uint32_t* jobCount, uint32_t* exactQueue, uint32_t* exactCount) {
     uint32_t n = *sCount;
     uint32_t nRound = (n + 31u) & ~31u;           // whole warps stay together for the ballot
 #if PT_STREAM_PREFETCH
@@ -345,8 +357,9 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
         if (i + 2u * stride < n) pNext = queue[i + 2u * stride];
 #endif
         if (i < n) { p = queue[i]; jobs = stage_connect_prep(P, sc, A, p); }
-        uint32_t s0 = warp_push(jobCount, jobs != 0u);
-        if (jobs) jobQueue[s0] = p;
+        uint32_t s0 = warp_push(jobCount, jobs == PT_CONNECT_JOB_LIGHT);
+        if (jobs == PT_CONNECT_JOB_LIGHT) jobQueue[s0] = p;
+        if (jobs == PT_CONNECT_JOB_EXACT) exactQueue[atomicAdd(exactCount, 1u)] = p;      // rare
     }
 }
 
@@ -354,14 +367,14 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
 template <bool COUNT>
 __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
-                                                        uint32_t* workCounter, unsigned long long* work) {
+                                                        uint32_t* workCounter, uint32_t* exactQueue, uint32_t* exactCount, unsigned long long* work) {
     uint32_t cntNode = 0, cntTri = 0;
     const uint32_t n = *jobCount;
     const uint32_t objectCount = P.pc.params.objectCount;
     PT_DECLARE_STACK(stack);
     WarpFeeder feed;
     Trav t;
-    float tE = 0.f;
+    float tE = 0.f, slackE = 0.f;
     uint32_t keyE = 0, job = 0;
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
@@ -376,7 +389,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
                 Ray r;
-                connect_job_ray(A, job, r, tE, keyE);
+                connect_job_ray(A, job, r, tE, keyE, slackE);
                 trav_begin(t, r);
                 busy = true;
             }
@@ -388,15 +401,21 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP_OCCL && trav_has_tri(t); ++r) {
                     if (COUNT) cntTri++;
-                    if (trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE)) {
-                        connect_job_occluded(A, job);
+                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE, slackE);
+                    if (o != PT_OCCL_NO) {
+                        if (o == PT_OCCL_YES) connect_job_occluded(A, job);
+                        else exactQueue[atomicAdd(exactCount, 1u)] = job;      // contested: k_exact_nee answers in the reference's order
                         busy = false;
                         break;
                     }
                 }
             }
         } else {
-            if (canNode) { trav_node_step(sc.all, t, stack, tE); if (COUNT) cntNode++; }
+            if (canNode) {
+                trav_node_step(sc.all, t, stack, tE + 2.f * slackE); if (COUNT) cntNode++;
+#pragma unroll 1
+                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, tE + 2.f * slackE); if (COUNT) cntNode++; }
+            }
         }
     }
     if (COUNT) flush_work(work, cntNode, cntTri);
@@ -414,11 +433,41 @@ __global__ void __launch_bounds__(WF_THREADS) k_connect_finish(const __grid_cons
         if (connect_job_finish(sc, A, p)) misQueue[atomicAdd(misCount, 1u)] = p;
     }
 }
-__global__ void __launch_bounds__(WF_THREADS) k_connect_mis(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+__global__ void __launch_bounds__(WF_THREADS) k_connect_mis(const __grid_constant__ WfParams P, const __grid_constant__ RefScene ref, PathArrays A,
                                                             const uint32_t* __restrict__ misQueue, const uint32_t* __restrict__ misCount) {
     uint32_t n = *misCount;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        connect_mis_weight_exact(P, sc, A, misQueue[i]);
+        connect_mis_weight_exact(ref, P.pc.params, A, misQueue[i]);
+}
+
+// Contested rays (pt_traverse.h: two reachable candidates closer together than the rounding slack of their distances,
+// coincident surfaces mostly): calculateIntersections in the reference's own order over the reference's own buffers.
+// One thread per ray; a few per thousand of the rays of a launch.
+__global__ void __launch_bounds__(WF_THREADS) k_exact_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, const __grid_constant__ RefScene ref,
+                                                             PathArrays A, const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count, Hit* hitOut,
+                                                             unsigned long long* total) {
+    const uint32_t n = *count;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = queue[i];
+        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+        hitOut[p] = exact_closest_hit(ref, sc, P.pc.params, r);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && total) atomicAdd(total, (unsigned long long)n);
+}
+__global__ void __launch_bounds__(WF_THREADS) k_exact_nee(const __grid_constant__ WfParams P, const __grid_constant__ RefScene ref, PathArrays A,
+                                                          const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count, unsigned long long* total) {
+    const uint32_t n = *count;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) connect_exact(ref, P.pc.params, A, queue[i]);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && total) atomicAdd(total, (unsigned long long)n);
+}
+
+// (object, reference triangle) -> record index in the wide layout, from the finished tree
+__global__ void k_wide_prim_of(const PrimRecord* __restrict__ prims, uint32_t n, const uint32_t* __restrict__ instBase, const uint32_t* __restrict__ triFirst,
+                               uint32_t* primOf) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t o = prims[i].objectIndex, t = prims[i].triIndexFlags & PT_PRIM_TRIMASK;
+    primOf[instBase[o] + t - triFirst[o]] = i;
 }
 
 __global__ void __launch_bounds__(WF_THREADS) k_accumulate(const __grid_constant__ WfParams P, PathArrays A, float4* accum) {
@@ -653,6 +702,13 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     WCU(wf_upload(c, w->dXforms, host.xforms));
     WCU(wf_upload(c, w->dObjXform, host.objXform));
     WCU(wf_upload(c, w->dUp, host.up));
+    // (object, triangle) -> record index, for hits found by the reference-order re-trace of contested rays
+    WCU(wf_upload(c, w->dInstBase, host.instBase));
+    WCU(wf_upload(c, w->dTriFirst, host.triFirst));
+    WCU(wf_resize(w->dPrimOf, std::max<size_t>((size_t)host.nInstSlots * 4, 16)));
+    WCU(cudaMemsetAsync(w->dPrimOf.p, 0xff, std::max<size_t>((size_t)host.nInstSlots * 4, 16), c->stream));
+    if (nPrimsAll) k_wide_prim_of<<<(nPrimsAll + 255) / 256, 256, 0, c->stream>>>((const PrimRecord*)w->dPrims.p, nPrimsAll, (const uint32_t*)w->dInstBase.p,
+                                                                                (const uint32_t*)w->dTriFirst.p, (uint32_t*)w->dPrimOf.p);
     WCU(cudaStreamSynchronize(c->stream));        // `host` is a local
     WideScene& s = w->scene;
     s.all = {(const Bvh8Node*)w->dNodes.p, (const PrimRecord*)w->dPrims.p, nNodesAll, nPrimsAll};
@@ -664,6 +720,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     s.xforms = (const Xform*)w->dXforms.p;
     s.objXform = (const uint32_t*)w->dObjXform.p;
     s.up = (const UpNode*)w->dUp.p;
+    s.primOf = (const uint32_t*)w->dPrimOf.p; s.instBase = (const uint32_t*)w->dInstBase.p; s.triFirst = (const uint32_t*)w->dTriFirst.p;
     s.spheres = c->ref.spheres; s.materials = c->ref.materials;
     s.nXforms = (uint32_t)host.xforms.size(); s.nSpheres = (uint32_t)c->hSpheres.size();
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
@@ -693,7 +750,8 @@ void wavefront_destroy(b200pt_ctx* c) {
     if (!w) return;
     wf_release_tree(w);
     DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dUv, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
-                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters, &w->dSampleSum};
+                           &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters, &w->dSampleSum,
+                           &w->dExactQ, &w->dExactNeeQ, &w->dPrimOf, &w->dInstBase, &w->dTriFirst};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
@@ -713,6 +771,8 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
         WCU(wf_resize(w->dQueue[1], paths * 4));
         WCU(wf_resize(w->dShadowQ, paths * 4));
         WCU(wf_resize(w->dJobQ, paths * 8));
+        WCU(wf_resize(w->dExactQ, paths * 4));
+        WCU(wf_resize(w->dExactNeeQ, paths * 4));
         w->capacity = paths;
         PathArrays& A = w->arrays;
         A.rayO = (float4*)w->dPaths[0].p; A.rayD = (float4*)w->dPaths[1].p; A.atten = (float4*)w->dPaths[2].p;
@@ -721,7 +781,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
     }
     uint32_t need = bounces + 3;
     if (need > w->countSlots) {
-        WCU(wf_resize(w->dCounts, (size_t)need * 7 * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
+        WCU(wf_resize(w->dCounts, (size_t)need * WF_COUNT_ARRAYS * 4));      // qCount | sCount | extend work counters | occlusion work counters | job counts
         w->countSlots = need;
     }
     if (!w->dRayCounters.p) {
@@ -778,6 +838,10 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* oCount = workO + w->countSlots;
     uint32_t* primaryCount = oCount + w->countSlots;
     uint32_t* mCount = primaryCount + w->countSlots;
+    uint32_t* xCount = mCount + w->countSlots;          // contested extension rays per bounce
+    uint32_t* xnCount = xCount + w->countSlots;         // contested light-sample queries per bounce
+    unsigned long long* exactTotals = (unsigned long long*)w->dRayCounters.p + 12;      // [12] extension rays, [13] light-sample queries re-traced exactly
+    const int gridExact = w->smCount * 4;
     if (!w->gridOcclude) {
         int perSm = 0;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude<false>, WF_THREADS, 0));
@@ -795,7 +859,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
         if (samples > 1) WCU(wf_resize(w->dSampleSum, (size_t)P.nPaths * 16));
         for (uint32_t smp = 0; smp < samples; ++smp) {            // samples of one dispatch run one after the other: they share the RNG stream
             P.continueSample = smp ? 1u : 0u;
-            WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
+            WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * WF_COUNT_ARRAYS * 4, c->stream));
             uint32_t* qa = (uint32_t*)w->dQueue[0].p;
             uint32_t* qb = (uint32_t*)w->dQueue[1].p;
             if (w->eventsUsed > 4096) { WCU(cudaStreamSynchronize(c->stream)); wavefront_resolve_stage_times(c); }
@@ -819,8 +883,11 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             P.connectAfterExtend = overlap ? 0u : 1u;
             wf_mark(c, ST_EXTEND);
             unsigned long long* workCnt = (unsigned long long*)w->dRayCounters.p + 8;     // [8,9] extend, [10,11] occlude
-            if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, workCnt);
-            else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, nullptr);
+            uint32_t* exactQ = (uint32_t*)w->dExactQ.p;
+            uint32_t* exactNeeQ = (uint32_t*)w->dExactNeeQ.p;
+            if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, workCnt);
+            else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, nullptr);
+            k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
             for (uint32_t j = 0; j < nB; ++j) {
                 wf_mark(c, ST_SHADE);
                 k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
@@ -833,28 +900,30 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                         cs = w->sideStream;
                     }
                     wf_mark(c, ST_EXTEND);
-                    if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, workCnt);
-                    else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, nullptr);
+                    if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, workCnt);
+                    else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, nullptr);
+                    k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
                     wf_mark(c, ST_CONNECT);
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
-                                                                       (uint32_t*)w->dJobQ.p, oCount + j);
+                                                                       (uint32_t*)w->dJobQ.p, oCount + j, exactNeeQ, xnCount + j);
                     wf_mark(c, ST_OCCLUDE);
                     uint32_t* misQ = (uint32_t*)w->dJobQ.p + w->capacity;      // second half of the job buffer
-                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, workCnt + 2);
-                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, nullptr);
+                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
+                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
+                    k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
-                    k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, misQ, mCount + j);
+                    k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, misQ, mCount + j);
                     if (overlap) {
                         WCU(cudaEventRecord(w->evJoin, w->sideStream));
                         WCU(cudaStreamWaitEvent(c->stream, w->evJoin, 0));
                     }
                 }
                 std::swap(qa, qb);
-                c->counters[0] += (j + 1 < nB) ? 6 : 1;
+                c->counters[0] += (j + 1 < nB) ? 8 : 1;
             }
             k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, oCount, mCount, primaryCount, P.sharePrimary, nB, (unsigned long long*)w->dRayCounters.p);
-            c->counters[0] += 3;                                      // generate, extend(0), fold
+            c->counters[0] += 4;                                      // generate, extend(0) + its exact re-trace, fold
             if (samples > 1) {
                 k_sample_sum<<<grid, WF_THREADS, 0, c->stream>>>(w->arrays, (float4*)w->dSampleSum.p, P.nPaths, smp, samples);
                 c->counters[0] += 1;
@@ -892,14 +961,17 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
     const int grid = w->smCount * 8;
     for (uint64_t done = 0; done < n; done += chunkMax) {
         const uint32_t m = (uint32_t)std::min<uint64_t>(chunkMax, n - done);
-        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * 7 * 4, c->stream));
+        WCU(cudaMemsetAsync(w->dCounts.p, 0, (size_t)w->countSlots * WF_COUNT_ARRAYS * 4, c->stream));
         k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays + 2 * done, m, w->arrays, (uint32_t*)w->dQueue[0].p, qCount);
         wf_mark(c, ST_EXTEND);
-        if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, workCnt);
-        else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, nullptr);
+        uint32_t* xCount = qCount + 7 * w->countSlots;
+        if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, (uint32_t*)w->dExactQ.p, xCount, workCnt);
+        else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, (uint32_t*)w->dExactQ.p, xCount, nullptr);
         wf_mark(c, -1);
+        k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, (const uint32_t*)w->dExactQ.p, xCount, w->arrays.hit,
+                                                                   (unsigned long long*)w->dRayCounters.p + 12);
         k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, w->arrays, m, dHits + done);
-        c->counters[0] += 3;
+        c->counters[0] += 4;
     }
     c->counters[2] += n;
     c->counters[4] += n;
@@ -915,6 +987,7 @@ void wavefront_fold_counters(b200pt_ctx* c) {
     if (cudaMemcpy(h, w->dRayCounters.p, sizeof(h), cudaMemcpyDeviceToHost) != cudaSuccess) return;
     for (int i = 0; i < 5; ++i) c->counters[2 + i] += h[i];           // [2..6]: see k_fold
     for (int i = 0; i < 4; ++i) c->counters[7 + i] += h[8 + i];       // [7..10]: node visits / triangle tests of k_extend, k_occlude
+    for (int i = 0; i < 2; ++i) c->counters[11 + i] += h[12 + i];     // [11, 12]: extension rays / light-sample queries re-traced in reference order
     cudaMemset(w->dRayCounters.p, 0, sizeof(h));
 }
 

@@ -83,10 +83,11 @@ class EmuScene:
         assert rc == 0
         return accum, rays
 
-    def trace_batch(self, pc, rays):
+    def trace_batch(self, pc, rays, want_contested=False):
         pcb = np.frombuffer(bytes(pc), np.uint8).copy()
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
         hits = np.zeros(rays.shape[0], HIT_DTYPE)
-        rc = lib().emu_wf_trace_batch(C.c_void_p(self.h), _ptr(pcb), _ptr(rays), C.c_uint64(rays.shape[0]), _ptr(hits))
+        nc = np.zeros(1, np.uint64)
+        rc = lib().emu_wf_trace_batch2(C.c_void_p(self.h), _ptr(pcb), _ptr(rays), C.c_uint64(rays.shape[0]), _ptr(hits), _ptr(nc))
         assert rc == 0
-        return hits
+        return (hits, int(nc[0])) if want_contested else hits

@@ -15,6 +15,8 @@ struct EmuScene {
     std::vector<ptl::Triangle> tris; std::vector<ptl::RenderObject> objects; std::vector<ptl::BVHNode> nodes;
     WideSceneHost wide;
     WideScene view;
+    std::vector<float> minv;      // inverse(transformMatrix) per object, for the reference-order re-trace of contested rays
+    RefScene ref;
 };
 }  // namespace
 
@@ -44,6 +46,11 @@ void* emu_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     v.emissionFinite = s->wide.emissionFinite ? 1u : 0u;
     for (int a = 0; a < 3; ++a) {     v.emisLo[a] = s->wide.emisLo[a];     v.emisHi[a] = s->wide.emisHi[a]; }
     v.uniqSphereMask = s->wide.uniqSphereMask; v.emisSphereMask = s->wide.emisSphereMask; v.plainSphereMask = s->wide.plainSphereMask;
+    v.primOf = s->wide.primOf.data(); v.instBase = s->wide.instBase.data(); v.triFirst = s->wide.triFirst.data();
+    s->minv.resize(16 * (size_t)nO);
+    for (uint32_t o = 0; o < nO; ++o) inverse4(s->objects[o].m, &s->minv[16 * (size_t)o]);
+    s->ref = RefScene{s->spheres.data(), s->materials.data(), s->points.data(), s->tris.data(), s->objects.data(), s->nodes.data(), s->minv.data(),
+                      nS, nM, nP, nT, nO, nN};
     return s;
 }
 void emu_scene_destroy(void* s) { delete (EmuScene*)s; }
@@ -79,7 +86,7 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
         uint32_t* cur = q0.data(); uint32_t* nxt = q1.data();
         for (uint32_t j = 0; j <= P.pc.params.bounceLimit && count; ++j) {
 #pragma omp parallel for schedule(dynamic, 256)
-            for (long long i = 0; i < (long long)count; ++i) stage_extend(P, sc, A, cur[i]);
+            for (long long i = 0; i < (long long)count; ++i) stage_extend(P, sc, s->ref, A, cur[i]);
             if (rays2) rays2[0] += count;
             uint32_t nNext = 0, nShadow = 0;
             std::vector<uint32_t> flags(count);
@@ -90,7 +97,7 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
                 if ((flags[i] & PT_SHADE_CONTINUE) && (flags[i] & PT_SHADE_CONNECT)) qs[nShadow++] = cur[i];
             }
 #pragma omp parallel for schedule(dynamic, 256)
-            for (long long i = 0; i < (long long)nShadow; ++i) stage_connect(P, sc, A, qs[i]);
+            for (long long i = 0; i < (long long)nShadow; ++i) stage_connect(P, sc, s->ref, A, qs[i]);
             if (rays2) rays2[1] += 2ull * nShadow;
             std::swap(cur, nxt);
             count = nNext;
@@ -102,7 +109,10 @@ int emu_wf_render_frames(void* sp, const void* pc208, int W, int H, uint32_t fir
 }
 
 // closest hits of a ray batch through the wide scene; 48-byte records as b200pt_trace_batch
-int emu_wf_trace_batch(void* sp, const void* pc208, const float* rays, uint64_t n, void* hits48) {
+int emu_wf_trace_batch2(void* sp, const void* pc208, const float* rays, uint64_t n, void* hits48, uint64_t* nContested);
+int emu_wf_trace_batch(void* sp, const void* pc208, const float* rays, uint64_t n, void* hits48) { return emu_wf_trace_batch2(sp, pc208, rays, n, hits48, nullptr); }
+// nContested: optional counter of rays that took the reference-order re-trace
+int emu_wf_trace_batch2(void* sp, const void* pc208, const float* rays, uint64_t n, void* hits48, uint64_t* nContested) {
     EmuScene* s = (EmuScene*)sp;
     const WideScene& sc = s->view;
     ptl::PushConstants pc;
@@ -112,7 +122,11 @@ int emu_wf_trace_batch(void* sp, const void* pc208, const float* rays, uint64_t 
 #pragma omp parallel for schedule(dynamic, 256)
     for (long long i = 0; i < (long long)n; ++i) {
         Ray r; r.o = mk3(rays[8 * i], rays[8 * i + 1], rays[8 * i + 2]); r.d = mk3(rays[8 * i + 4], rays[8 * i + 5], rays[8 * i + 6]);
-        Hit h = wide_closest_hit(sc, r, pc.params.sphereCount, pc.params.objectCount);
+        uint32_t contested = 0u;
+        Hit h = wide_closest_hit(sc, r, pc.params.sphereCount, pc.params.objectCount, contested);
+        if (contested) { h = exact_closest_hit(s->ref, sc, pc.params, r); if (nContested) {
+#pragma omp atomic
+            nContested[0]++; } }
         Rec o; std::memset(&o, 0, sizeof(o));
         o.dst = h.dst; o.obj = 0xffffffffu;
         if (h.id != PT_HIT_MISS) {

@@ -47,6 +47,8 @@ def lib():
         L.orc_render_window.argtypes = [vp, vp, i32, i32, u32, u32, i32, i32, i32, i32, i32, i32, vp, vp, i32]
         L.orc_trace_batch.argtypes = [vp, vp, vp, u64, vp, vp, i32]
         L.orc_pixel_ties.argtypes = [vp, vp, i32, i32, u32, vp, u64, vp]
+        L.orc_pixel_rays.restype = u64
+        L.orc_pixel_rays.argtypes = [vp, vp, i32, i32, u32, u32, u32, u64, vp, vp]
         L.orc_random.restype = f32
         L.orc_random.argtypes = [C.POINTER(u32)]
         L.orc_starting_seed.restype = u32
@@ -163,6 +165,15 @@ class OracleScene:
         if xy.shape[0]:
             lib().orc_pixel_ties(self.h, _ptr(pcb), W, H, frame, _ptr(xy), xy.shape[0], _ptr(out))
         return out
+
+    def pixel_rays(self, pc, W, H, frame, x, y, cap=512):
+        """Every ray the oracle traces for pixel (x, y) of `frame`, in call order -> (rays (n, 8), hits (n,) HIT_DTYPE)."""
+        pcb = self._pc(pc)
+        rays = np.zeros((cap, 8), np.float32)
+        hits = np.zeros(cap, HIT_DTYPE)
+        n = lib().orc_pixel_rays(self.h, _ptr(pcb), W, H, frame, x, y, cap, _ptr(rays), _ptr(hits))
+        n = min(int(n), cap)
+        return rays[:n], hits[:n]
 
     def trace_batch(self, pc, rays, threads=0):
         pcb = self._pc(pc)

@@ -43,18 +43,16 @@ def _differing(a, b):
 
 def _assert_explained(blobs, pc, W, H, frames, got, want, x0=0, y0=0, sx=1, sy=1, textures=None):
     """got / want: images of the pixels (x0 + i*sx, y0 + j*sy) of the W x H image built from the frames in `frames`
-    (accumulated, or blended by progressive dispatches). Bit-exact is the bar; a pixel may differ only if a ray on its
-    path — in one of those frames — met its closest hit at EXACTLY the same distance on two triangles of one object (the
-    one documented tie class, DESIGN.md §4 item 5: which of the two wins depends on the order a traversal meets them).
-    Every differing pixel is re-traced by the oracle's tie detector (oracle_shader.cpp: pixel_ties) and must show such a
-    ray; and there may be no more than 3e-4 of them per frame (two for small images)."""
+    (accumulated, or blended by progressive dispatches). The bar is BIT-EXACT, with no tie class: rays on which two
+    candidates come closer together than the rounding slack of their hit distances (coincident surfaces, equal-distance
+    hits on two triangles of one object) are re-traced by the kernels in the reference's own order (pt_traverse.h,
+    k_exact_*), so the traversal order of the wide BVH cannot show. On a failure the message says, per differing pixel,
+    whether the oracle's tie detector (oracle_shader.cpp: pixel_ties) sees an equal-distance hit on its path."""
     diff = (np.ascontiguousarray(got).view(np.uint32) != np.ascontiguousarray(want).view(np.uint32)).any(axis=2)
     nd = int(diff.sum())
     if nd == 0:
         return 0
     frames = list(frames)
-    # measured rate of such ties on the tessellated atrium: 1.2e-4 of paths (73 of 576 x 1024); the explanation below is the check
-    assert nd <= max(2, 3e-4 * diff.size * len(frames)), "%d of %d pixels differ" % (nd, diff.size)
     ys, xs = np.nonzero(diff)
     xy = np.stack([x0 + xs * sx, y0 + ys * sy], 1).astype(np.uint32)
     sc = ob.OracleScene(blobs)
@@ -64,10 +62,10 @@ def _assert_explained(blobs, pc, W, H, frames, got, want, x0=0, y0=0, sx=1, sy=1
         sc.use_textures(True)
     ties = np.zeros(len(xy), np.int64)
     with ob.math_mode(1):
-        for f in frames:
-            ties += sc.pixel_ties(pc, W, H, f, xy)
-    assert (ties > 0).all(), "pixels differ with no equal-distance tie on their path: %s" % xy[ties == 0][:8].tolist()
-    return nd
+        for f in frames[:64]:
+            ties += sc.pixel_ties(pc, W, H, f, xy[:32])[: len(xy)] if len(xy) <= 32 else np.pad(sc.pixel_ties(pc, W, H, f, xy[:32]), (0, len(xy) - 32))
+    raise AssertionError("%d of %d pixels differ; first (x, y, ties on the oracle's path): %s" % (
+        nd, diff.size, [(int(a), int(b), int(t)) for (a, b), t in zip(xy[:12], ties[:12])]))
 
 
 def _same_hits(got, want):
@@ -87,12 +85,7 @@ def test_first_hit_ids(gpu, name, pipeline, request):
     cp.set_option("pipeline", pipeline)
     got = cp.trace_batch(pc, rays)
     same = _same_hits(got, want)
-    if pipeline == 0:
-        assert same.all()                       # same traversal order as the reference: no tie class
-    else:
-        ties = ~same & (got["dst"] == want["dst"]) & (got["kind"] == want["kind"])
-        assert (same | ties).all()
-        assert ties.mean() < 1e-3
+    assert same.all()        # pipeline 0: the reference's own order; pipeline 1: contested rays are re-traced in that order
     hit = same & (want["kind"] != 0)
     for f in ("normal", "hitPoint"):
         assert np.array_equal(got[f][hit].view(np.uint32), want[f][hit].view(np.uint32)), f
@@ -107,10 +100,38 @@ def test_first_hit_ids_soup_200k(gpu):
     want, _ = ob.OracleScene(blobs).trace_batch(pc, rays)
     cp = _pass(gpu, blobs, 64, 64)
     got = cp.trace_batch(pc, rays)
-    same = _same_hits(got, want)
-    assert same.mean() > 0.9999, same.mean()
+    assert _same_hits(got, want).all()
     cp.set_option("pipeline", 0)
     assert _same_hits(cp.trace_batch(pc, rays), want).all()
+
+
+@pytest.mark.parametrize("pipeline", [0, 1])
+def test_first_hit_ids_on_coincident_surfaces_atrium(gpu):
+    # The C4 stand-in has coincident surfaces (lintels lying in the plane of the gallery floor, boxes flush with walls):
+    # two objects hit at distances a rounding error apart. Which one the reference returns depends on its traversal ORDER
+    # (a BVH2 node is pruned against the closest hit found so far, raytrace.comp:346-347). Replays the rays of 3000 random
+    # (pixel, frame) paths of the full-size image — the oracle's own extension, NEE and pdf rays — through
+    # b200pt_trace_batch: every hit must be the oracle's, bit for bit; about 3 per thousand of them are contested and go
+    # through the reference-order re-trace (k_exact_extend), which the counters must show.
+    from ray_tracer_b200 import PushConstants, scenes
+    W, H = 1920, 1080
+    blobs, info = scenes.atrium()
+    pc = PushConstants(W, H, blobs["spheres"].size // 32, info["objects"])
+    scenes.atrium_camera(pc)
+    sc = ob.OracleScene(blobs)
+    rng = np.random.default_rng(11)
+    rays, want = [], []
+    with ob.math_mode(1):
+        for _ in range(3000):
+            r, h = sc.pixel_rays(pc.buffer, W, H, int(rng.integers(0, 1024)), int(rng.integers(0, W)), int(rng.integers(0, H)))
+            rays.append(r); want.append(h)
+    rays, want = np.concatenate(rays), np.concatenate(want)
+    cp = _pass(gpu, blobs, 64, 64)
+    cp.reset_counters()
+    got = cp.trace_batch(pc.buffer, rays)
+    assert _same_hits(got, want).all()
+    n_exact = cp.counters()["exact_extension_rays"]
+    assert 0 < n_exact < 0.02 * len(rays), n_exact
 
 
 @pytest.mark.parametrize("pipeline", [0, 1])
@@ -271,7 +292,7 @@ def test_full_size_properties_c4(gpu):
         for k, v in opts.items():
             cp.set_option(k, v)
         cp.render_frames(pc.buffer, 0, 4)
-        assert _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole) <= 20, opts
+        _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole)
     cp.set_option("frames_in_flight", 4)
     cp.clear()
     cp.render_frames(pc.buffer, 0, 2, frame_stride=2)
@@ -282,7 +303,7 @@ def test_full_size_properties_c4(gpu):
     cp.clear()
     cp.render_frames(pc.buffer, 0, 4, rows=(0, 377))
     cp.render_frames(pc.buffer, 0, 4, rows=(377, H))
-    assert _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole) <= 20
+    _assert_explained(blobs, pc.buffer, W, H, range(4), cp.read_accum(), whole)
     # BASELINE.json's bar for C4 ("the image within RMSE 1e-3"), at C4's own 1024 spp, on a 32 x 18 lattice of the image
     cp.set_option("frames_in_flight", 24)
     _config_spp_check(cp, blobs, pc.buffer, W, H, 1024, 32, 18)
