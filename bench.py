@@ -452,20 +452,28 @@ def main():
         step()
     fence()
     cp.reset_counters()
-    cp.set_option("profile_stages", 1)
-    cp.stage_times(reset=True)
     sampler = ClockSampler(local) if rank == 0 else None
-    ms, t0, t1 = device_ms(lambda: [step() for _ in range(args.steps)])
+    ms, t0, t1 = device_ms(lambda: [step() for _ in range(args.steps)])       # the library's default path (no per-stage events)
     clocks = sampler.stop(t0, t1) if sampler else None
     counters = cp.counters()
-    stages = cp.stage_times(reset=True)
+    # per-stage device times: a second, shorter pass with an event between consecutive launches (serialises the streams)
+    cp.set_option("profile_stages", 1)
+    cp.stage_times(reset=True)
+    stage_steps = max(1, min(3, args.steps))
+    ms_staged, _, _ = device_ms(lambda: [step() for _ in range(stage_steps)])
+    stages = {k: (v[0] * args.steps / stage_steps, v[1] * args.steps // stage_steps) for k, v in cp.stage_times(reset=True).items()}
     cp.set_option("profile_stages", 0)
     paths_per_step = W * H * F * N
     value = paths_per_step * args.steps / (ms * 1e-3) / 1e6
     out = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=N, steps=args.steps, warmup=args.warmup, ms_per_step=ms / args.steps,
                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic", config=cfg, clocks=clocks,
-               gpu_launches=counters["launches"], ms_per_frame_1spp=ms / args.steps / F)
+               gpu_launches=counters["launches"], ms_per_frame_1spp=ms / args.steps / F, ms_per_step_with_stage_events=ms_staged / stage_steps)
+    out["exact_retrace"] = dict(extension_rays_per_path=counters["exact_extension_rays"] / max(counters["paths"], 1),
+                                light_queries_per_path=counters["exact_light_queries"] / max(counters["paths"], 1),
+                                note="contested rays (two candidates closer together than the rounding slack of their distances: coincident "
+                                     "surfaces) re-traced in the reference's own order so that results equal the reference's bit for bit")
     if args.only_value:
+        out["stage_ms_per_step"] = {k: v[0] / args.steps for k, v in stages.items()}
         if rank == 0:
             print(json.dumps(out), flush=True)
         cp.close()

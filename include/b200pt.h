@@ -200,7 +200,8 @@ int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
 int b200pt_reset_counters(b200pt_ctx* ctx);
 /* With option "profile_stages" = 1 the wavefront records a CUDA event between consecutive launches; this
  * returns the accumulated device milliseconds and launch counts per stage, 8 entries each
- * (0 generate, 1 extend, 2 shade, 3 connect-prep, 4 accumulate, 5 occlude, 6 connect-finish, 7 reserved)
+ * (0 generate, 1 extend, 2 shade, 3 connect-prep, 4 accumulate, 5 occlude, 6 connect-finish, 7 reference-order re-trace of
+ * contested rays)
  * and optionally resets them. */
 int b200pt_read_stage_times(b200pt_ctx* ctx, double* ms8, uint64_t* launches8, int reset);
 /* Device time of the last render call in milliseconds (CUDA events on the context's stream). */

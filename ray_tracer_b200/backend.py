@@ -266,7 +266,7 @@ class ComputePass:
                     extend_node_visits=int(c[7]), extend_tri_tests=int(c[8]), occlude_node_visits=int(c[9]),
                     occlude_tri_tests=int(c[10]), exact_extension_rays=int(c[11]), exact_light_queries=int(c[12]))
 
-    STAGES = ("generate", "extend", "shade", "connect_prep", "accumulate", "occlude", "connect_finish")
+    STAGES = ("generate", "extend", "shade", "connect_prep", "accumulate", "occlude", "connect_finish", "exact_retrace")
 
     def stage_times(self, reset=False):
         """{stage: (device ms, launches)} accumulated while option profile_stages = 1."""

@@ -40,7 +40,25 @@ struct WideSceneHost {
     // the finished tree (host: fill_prim_of below; device build: k_wide_prim_of)
     std::vector<uint32_t> instBase, triFirst, primOf;
     uint32_t nInstSlots = 0;
+    float extent = 0.f;        // WideScene::extent
 };
+
+// Largest |coordinate| the scene reaches in world space: the corners of every object's BVH2 root box through its matrix,
+// and the spheres. Scale of the contest window (pt_traverse.h); non-finite values are skipped.
+inline float wide_extent(const std::vector<ptl::Sphere>& spheres, const std::vector<ptl::RenderObject>& objects, const std::vector<ptl::BVHNode>& nodes) {
+    float m = 0.f;
+    auto grow = [&](float v) { v = std::fabs(v); if (v < 1e30f && v > m) m = v; };
+    for (const auto& s : spheres) { grow(std::fabs(s.px) + std::fabs(s.radius)); grow(std::fabs(s.py) + std::fabs(s.radius)); grow(std::fabs(s.pz) + std::fabs(s.radius)); }
+    for (const auto& ob : objects) {
+        if (ob.bvhIndex >= nodes.size()) continue;
+        const ptl::BVHNode& r = nodes[ob.bvhIndex];
+        for (int c = 0; c < 8; ++c) {
+            v3 p = mul_point(ob.m, mk3((c & 1) ? r.maxX : r.minX, (c & 2) ? r.maxY : r.minY, (c & 4) ? r.maxZ : r.minZ));
+            grow(p.x); grow(p.y); grow(p.z);
+        }
+    }
+    return m;
+}
 
 inline void fill_prim_of(WideSceneHost& out) {
     out.primOf.assign(out.nInstSlots, 0xffffffffu);
@@ -437,6 +455,7 @@ inline const char* build_wide_scene(const std::vector<ptl::Sphere>& spheres, con
                                     WideSceneHost& out, bool buildAll = true) {
     using namespace b8;
     out.anyEmissive = false;
+    out.extent = wide_extent(spheres, objects, nodes);
     out.instObject.clear(); out.instTri.clear(); out.leafOf.clear();
     auto emissive = [&](uint32_t m) { return !(materials[m].emissionStrength == 0.f); };
     wide_sphere_masks(spheres, materials, out);

@@ -103,6 +103,7 @@ struct WideScene {
     uint32_t nXforms, nSpheres, nMaterials, nObjects;
     uint32_t anyEmissive;      // any emissive sphere or triangle in the scene
     uint32_t emissionFinite;   // every material's emissionColor * emissionStrength is finite
+    float extent;              // largest |coordinate| of the scene's world-space boxes and spheres (contest window, pt_traverse.h)
     float emisLo[3], emisHi[3];   // bounding box of all emissive triangles (grown; see ray_meets_box)
     // Sphere slot masks (valid when nSpheres <= 32). Slots with bit-identical (position, radius) give identical
     // test results, and every loop of the reference keeps the FIRST of equal candidates, so only the lowest

@@ -95,17 +95,22 @@ PT_HD TriEdges tri_edges(v3 p0, v3 p1, v3 p2) {
 }
 // triangleIntersection(), raytrace.comp:227-248 (the ray is in object space). u, v, dst are the
 // shader's values; didHit as at :246.
-PT_HD bool tri_test(const TriEdges& t, const Ray& ray, bool frontOnly, float& dst, float& u, float& v, bool& front) {
+PT_HD bool tri_test_r(const TriEdges& t, const Ray& ray, bool frontOnly, float& dst, float& u, float& v, bool& front, float& invD0) {
     v3 rov0 = ray.o - t.p0;
     v3 q = cross(rov0, ray.d);
     float d0 = -dot(ray.d, t.n);
     float d = 1.f / d0;
+    invD0 = d;                  // for the distance slack of an accepted hit (pt_traverse.h: tri_dst_slack)
     dst = dot(rov0, t.n) * d;
     u = dot(t.e2, q) * d;
     v = -dot(t.e1, q) * d;
     float w = 1.f - u - v;
     front = d0 >= 0.00000001f;
     return dst >= 0.f && u >= 0.f && v >= 0.f && w >= 0.f && !(!front && frontOnly);
+}
+PT_HD bool tri_test(const TriEdges& t, const Ray& ray, bool frontOnly, float& dst, float& u, float& v, bool& front) {
+    float invD0;
+    return tri_test_r(t, ray, frontOnly, dst, u, v, front, invD0);
 }
 // raytrace.comp:247,259 then :318-319 — object-space hit point / interpolated normal, moved to
 // world space with the object's matrix (normal by M, not inverse-transpose: A-Q13).

@@ -241,7 +241,10 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
         const bool inZ = flatZ || (h.z >= lz + m && h.z <= hz - m);
         const int nOut = (inX ? 0 : 1) + (inY ? 0 : 1) + (inZ ? 0 : 1);
         if (nOut == 0) return true;
-        if (nOut == 1) {
+        // (b) needs real margins on the other two axes: not when the leaf is flat on one of them (its slab interval there
+        // is the single value of the plane distance, and a hit point m/16 outside the triangle's box on axis a means the
+        // ray has left the zero-thickness box: found on the C4 stand-in, frame 402 pixel (1740, 780), a trim-box face)
+        if (nOut == 1 && !(flatX || flatY || flatZ)) {
             const float m16 = m * 0.0625f;
             const float ax = fabsf(c.r.d.x), ay = fabsf(c.r.d.y), az = fabsf(c.r.d.z);
             bool ok;
@@ -277,25 +280,29 @@ PT_HD TriEdges prim_edges(const PrimRecord& p) {
 // triangles is the same answer EXCEPT when a triangle's hit distance dst_T is not above the slab distance b_T of one of
 // its enclosing boxes — possible only by rounding (triangle on a box face: b_T - dst_T is a few ulps) — and another
 // candidate lies in between: the reference then never tests T. Analysis: the two answers can
-// differ only if two reachable candidates are closer together than delta = |b_T - dst_T| <= the rounding error of the
-// Moeller-Trumbore distance (the slab distance itself is accurate to 3 ulp: lo - o is a difference of two floats).
-// tri_dst_slack() bounds that error from the condition numbers of the two dot products and of the cross product;
-// a ray on which two candidates come closer than the sum of their slacks is CONTESTED and is re-traced in the
-// reference's own order (pt_reftrace.h: ref_closest_hit — k_exact_* in wavefront.cu). That also settles hits at exactly
-// equal distance on two triangles of one object, the former "documented tie class": there is none left.
-// Nodes are culled against best + 2 slack, so a competitor within the best hit's slack is always tested.
-#ifndef PT_SLACK_K
-#define PT_SLACK_K 1e-6f      /* ~16 eps per rounding step of the bound below */
+// differ only if two reachable candidates are closer together than delta = b_T - dst_T <= the rounding error of the
+// Moeller-Trumbore distance, about 4 eps * (scene extent) / cos(incidence) in ray-parameter units (the slab distance
+// itself is accurate to 3 ulp: lo - o is a difference of two floats).
+// Rule: a ray is CONTESTED when (i) two reachable candidates lie within PT_TAU * (distance + scene extent) of each other
+// — 60 times that error at normal incidence — or (ii) its best hit is grazing (1 / cos above PT_GRAZE: the error bound
+// then approaches (i)'s window). Contested rays are re-traced in the reference's own order (pt_reftrace.h:
+// ref_closest_hit — k_exact_* in wavefront.cu). That also settles hits at exactly equal distance on two triangles of one
+// object, the former "documented tie class": there is none left. Nodes are culled against best + window, so a competitor
+// inside the window beyond the best hit is always tested. State: two bits of br.octinv4 (bits 5..7 of its bytes are free:
+// the node test masks with 0x1f) — separate registers for it cost 17 % of k_extend at its 72-register cap.
+#ifndef PT_CONTEST
+#define PT_CONTEST 1          /* 0: measurement only — no contest detection (results then depend on the traversal order) */
 #endif
+#define PT_TAU 1.52587890625e-5f       /* 2^-16 */
+#define PT_GRAZE 64.f
+#define PT_TRAV_CONTESTED 0x80000000u
+#define PT_TRAV_GRAZING 0x40000000u   /* the current best hit is grazing */
 PT_HD float maxabs3(v3 a) { return fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fabsf(a.z)); }
-PT_HD float tri_dst_slack(const TriEdges& t, const Ray& r, float dst) {
-    const v3 rov0 = r.o - t.p0;
-    const float an = fabsf(rov0.x * t.n.x) + fabsf(rov0.y * t.n.y) + fabsf(rov0.z * t.n.z);      // |dot(rov0, n)| without cancellation
-    const float ad = fabsf(r.d.x * t.n.x) + fabsf(r.d.y * t.n.y) + fabsf(r.d.z * t.n.z);         // |dot(d, n)| without cancellation
-    const float d0 = fabsf(dot(r.d, t.n));
-    const float cr = maxabs3(t.e1) * maxabs3(t.e2) * (maxabs3(rov0) + fabsf(dst) * maxabs3(r.d)); // rounding of cross(e1, e2)
-    return PT_SLACK_K * fabsf(dst) + PT_SLACK_K * (an + fabsf(dst) * ad + 3.f * cr) / d0;
-}
+PT_HD float contest_window(float dst, float extent) { return PT_TAU * (dst + extent); }
+PT_HD float cull_dst(float best, float extent) { return best + contest_window(best, extent); }
+// 1 / cos(incidence) from what tri_test already formed: invD0 = 1 / -dot(d, n) (n = cross(e1, e2), not normalised)
+PT_HD float inv_cos_incidence(const TriEdges& t, const Ray& r, float invD0) { return fabsf(invD0) * maxabs3(t.n) * maxabs3(r.d); }
+PT_HD bool hit_is_grazing(const TriEdges& t, const Ray& r, float invD0) { return inv_cos_incidence(t, r, invD0) > PT_GRAZE; }
 
 // ---- traversal as per-ray steps ---------------------------------------------------------------
 // The state of one ray's walk through the wide BVH. Work items are "groups": a node group
@@ -311,14 +318,12 @@ struct Trav {
     uint32_t gBase, gBits;      // current node group
     uint32_t tBase, tBits;      // current triangle group
     int sp;
-    float bestSlack;            // distance slack of the current best hit (tri_dst_slack; 0 for a sphere or none)
-    uint32_t contested;         // two reachable candidates closer together than their slacks: the ray is re-traced in reference order
 };
+PT_HD bool trav_contested(const Trav& t) { return (t.br.octinv4 & 0xc0000000u) != 0u; }      // contested, or the best hit is grazing (see below)
 PT_HD void trav_begin(Trav& t, const Ray& ray) {
     t.ray = ray; t.br = make_box_ray(ray); t.oc.xform = 0xffffffffu;
     t.gBase = 0; t.gBits = 0x80000000u;               // the root as the only child of a virtual group
     t.tBase = 0; t.tBits = 0; t.sp = 0;
-    t.bestSlack = 0.f; t.contested = 0u;
 }
 // The per-ray stack of groups. PrivateStack: two arrays in thread-private (local) memory. The persistent kernels use
 // a SplitStack (wavefront.cu): the first PT_BVH8_SHARED_STACK entries live in shared memory, [entry][thread] so that a
@@ -393,7 +398,7 @@ PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, Stack& stack, float tmax
 // reference's loop order (sphere i -> i, object o -> nSpheres + o; 0xffffffff for none): the
 // reference keeps the FIRST of equal-distance hits.
 PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                 Trav& t, Hit& hit, uint32_t& key) {
+                                 float extent, Trav& t, Hit& hit, uint32_t& key) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     uint32_t pi = t.tBase + (uint32_t)k;
@@ -401,20 +406,23 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
     const PrimRecord p = load_prim(bvh.prims, pi);
     if (p.objectIndex >= objectCount) return;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
-    float dst, u, v; bool front;
+    float dst, u, v, invD0; bool front;
     const TriEdges te = prim_edges(p);
-    if (!tri_test(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front)) return;
+    if (!tri_test_r(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front, invD0)) return;
     const bool wins = dst < hit.dst || (dst == hit.dst && nSpheres + p.objectIndex < key);
-    const float gap = fabsf(dst - hit.dst);
-    // only a hit that wins, or one that comes within the best hit's slack, can change the answer
-    if (!(wins || gap <= 2.f * t.bestSlack) || !ref_reachable(up, p, t.oc, dst)) return;
-    const float slack = tri_dst_slack(te, tr, dst);
-    if (hit.id != PT_HIT_MISS && gap <= slack + t.bestSlack && (hit.id & ~PT_HIT_FRONT) != pi) t.contested = 1u;
+#if PT_CONTEST
+    // only a hit that wins, or one that comes within tau of the best, can change the answer
+    const bool near = fabsf(dst - hit.dst) <= contest_window(fmaxf(dst, hit.dst), extent) && hit.id != PT_HIT_MISS;
+    if (!(wins || near) || !ref_reachable(up, p, t.oc, dst)) return;
+    if (near && (hit.id & ~PT_HIT_FRONT) != pi) t.br.octinv4 |= PT_TRAV_CONTESTED;
+    if (wins) t.br.octinv4 = (t.br.octinv4 & ~PT_TRAV_GRAZING) | (hit_is_grazing(te, tr, invD0) ? PT_TRAV_GRAZING : 0u);
+#else
+    if (!wins || !ref_reachable(up, p, t.oc, dst)) return;
+#endif
     if (wins) {
         hit.dst = dst; hit.u = u; hit.v = v;
         hit.id = pi | (front ? PT_HIT_FRONT : 0u);
         key = nSpheres + p.objectIndex;
-        t.bestSlack = slack;
     }
 }
 // Occlusion form: is the next triangle a NON-emissive hit that the reference's closest-hit search
@@ -425,51 +433,54 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
 #define PT_OCCL_YES 1
 #define PT_OCCL_CONTESTED 2
 PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                 Trav& t, float tE, uint32_t keyE, float slackE) {
+                                 float extent, Trav& t, float tE, uint32_t keyE) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     const PrimRecord p = load_prim(bvh.prims, t.tBase + (uint32_t)k);
     if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) return PT_OCCL_NO;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
-    float dst, u, v; bool front;
+    float dst, u, v, invD0; bool front;
     const TriEdges te = prim_edges(p);
-    if (!tri_test(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front)) return PT_OCCL_NO;
+    if (!tri_test_r(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front, invD0)) return PT_OCCL_NO;
     const bool closer = dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE);
-    const float gap = fabsf(dst - tE);
-    if (!(closer || gap <= 2.f * slackE) || !ref_reachable(up, p, t.oc, dst)) return PT_OCCL_NO;
-    if (gap <= tri_dst_slack(te, tr, dst) + slackE) return PT_OCCL_CONTESTED;
+    const float gap = fabsf(dst - tE), window = contest_window(fmaxf(dst, tE), extent);
+    const bool near = gap <= window;
+    if (!(closer || near) || !ref_reachable(up, p, t.oc, dst)) return PT_OCCL_NO;
+#if PT_CONTEST
+    // an occluder far in front of tE decides unless its own distance error (which grows with 1 / cos) reaches back to tE
+    if (near || gap <= window * inv_cos_incidence(te, tr, invD0) * (1.f / 16.f)) return PT_OCCL_CONTESTED;
+#endif
     return closer ? PT_OCCL_YES : PT_OCCL_NO;
 }
 
 // Per-ray loops over the steps (host emulation, the small emissive BVH). `contested` is OR-ed, `slack` returns the
 // best hit's slack.
 PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, Hit& hit, uint32_t& key, uint32_t& contested, float& slack) {
+                                 uint32_t objectCount, float extent, Hit& hit, uint32_t& key, uint32_t& contested) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     for (;;) {
-        if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, t, hit, key);
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, hit.dst + 2.f * t.bestSlack);
+        if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, extent, t, hit, key);
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, cull_dst(hit.dst, extent));
         else if (!trav_pop(t, stack)) break;
     }
-    contested |= t.contested;
-    slack = t.bestSlack;
+    contested |= trav_contested(t) ? 1u : 0u;
 }
 // -> PT_OCCL_NO / PT_OCCL_YES / PT_OCCL_CONTESTED
 PT_HD_NOINLINE int bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, float tE, uint32_t keyE, float slackE) {
+                                 uint32_t objectCount, float extent, float tE, uint32_t keyE) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     int contested = PT_OCCL_NO;
     for (;;) {
         if (trav_has_tri(t)) {
-            const int r = trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, t, tE, keyE, slackE);
+            const int r = trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, extent, t, tE, keyE);
             if (r == PT_OCCL_YES) return PT_OCCL_YES;
             if (r == PT_OCCL_CONTESTED) contested = PT_OCCL_CONTESTED;
         }
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, tE + 2.f * slackE);
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, cull_dst(tE, extent));
         else if (!trav_pop(t, stack)) break;
     }
     return contested;

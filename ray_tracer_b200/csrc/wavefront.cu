@@ -51,9 +51,12 @@ struct WavefrontState {
     // second stream for the connect chain of a bounce (option overlap_connect)
     cudaStream_t sideStream = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    // third stream: the reference-order re-trace of bounce j+1's contested rays runs beside the connect chain of bounce j
+    cudaStream_t exactStream = nullptr;
+    cudaEvent_t evX0 = nullptr, evX1 = nullptr;
 };
 
-enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4, ST_OCCLUDE = 5, ST_FINISH = 6 };
+enum { ST_GENERATE = 0, ST_EXTEND = 1, ST_SHADE = 2, ST_CONNECT = 3, ST_ACCUMULATE = 4, ST_OCCLUDE = 5, ST_FINISH = 6, ST_EXACT = 7 };
 
 static void wf_mark(b200pt_ctx* c, int stage) {
     WavefrontState* w = c->wf;
@@ -226,7 +229,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         // lanes with nothing in hand take the next group from their stack, or finish
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
             hitOut[p] = hit;
-            if (t.contested) exactQueue[atomicAdd(exactCount, 1u)] = p;      // rare (coincident surfaces): k_exact_extend overwrites the hit
+            if (trav_contested(t)) exactQueue[atomicAdd(exactCount, 1u)] = p;      // rare (coincident surfaces): k_exact_extend overwrites the hit
             busy = false;
         }
         const bool hasTri = busy && trav_has_tri(t);
@@ -249,15 +252,15 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
             if (hasTri) {
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP && trav_has_tri(t); ++r) {
-                    trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, hit, key);
+                    trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, t, hit, key);
                     if (COUNT) cntTri++;
                 }
             }
         } else {
             if (canNode) {
-                trav_node_step(sc.all, t, stack, hit.dst + 2.f * t.bestSlack); if (COUNT) cntNode++;
+                trav_node_step(sc.all, t, stack, cull_dst(hit.dst, sc.extent)); if (COUNT) cntNode++;
 #pragma unroll 1
-                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, hit.dst + 2.f * t.bestSlack); if (COUNT) cntNode++; }
+                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, cull_dst(hit.dst, sc.extent)); if (COUNT) cntNode++; }
             }
         }
     }
@@ -374,7 +377,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     PT_DECLARE_STACK(stack);
     WarpFeeder feed;
     Trav t;
-    float tE = 0.f, slackE = 0.f;
+    float tE = 0.f;
     uint32_t keyE = 0, job = 0;
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
@@ -389,7 +392,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
                 Ray r;
-                connect_job_ray(A, job, r, tE, keyE, slackE);
+                connect_job_ray(A, job, r, tE, keyE);
                 trav_begin(t, r);
                 busy = true;
             }
@@ -401,7 +404,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP_OCCL && trav_has_tri(t); ++r) {
                     if (COUNT) cntTri++;
-                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, t, tE, keyE, slackE);
+                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, t, tE, keyE);
                     if (o != PT_OCCL_NO) {
                         if (o == PT_OCCL_YES) connect_job_occluded(A, job);
                         else exactQueue[atomicAdd(exactCount, 1u)] = job;      // contested: k_exact_nee answers in the reference's order
@@ -412,9 +415,9 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             }
         } else {
             if (canNode) {
-                trav_node_step(sc.all, t, stack, tE + 2.f * slackE); if (COUNT) cntNode++;
+                trav_node_step(sc.all, t, stack, cull_dst(tE, sc.extent)); if (COUNT) cntNode++;
 #pragma unroll 1
-                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, tE + 2.f * slackE); if (COUNT) cntNode++; }
+                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, cull_dst(tE, sc.extent)); if (COUNT) cntNode++; }
             }
         }
     }
@@ -627,6 +630,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
         s.anyEmissive = (host.anyEmissive || w->anyEmissiveTri) ? 1u : 0u;
         s.emissionFinite = host.emissionFinite ? 1u : 0u;
         s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
+        s.extent = wide_extent(c->hSpheres, c->hObjects, c->hNodes);
         c->lastWideDeviceMs = 0.0;
         c->lastSceneBuildMs = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tBuild).count();
         return 0;
@@ -653,6 +657,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
                 s.shadeEmis = (const ShadeRecord*)w->dShadeE.p;
                 s.xforms = (const Xform*)w->dXforms.p; s.objXform = (const uint32_t*)w->dObjXform.p;
                 s.nXforms = (uint32_t)host.xforms.size();
+                s.extent = wide_extent(c->hSpheres, c->hObjects, c->hNodes);
                 for (int a = 0; a < 3; ++a) { s.emisLo[a] = host.emisLo[a]; s.emisHi[a] = host.emisHi[a]; }
                 c->lastWideDeviceMs = ms;
                 c->lastRefit = 1;
@@ -726,6 +731,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     s.nMaterials = (uint32_t)c->hMaterials.size(); s.nObjects = (uint32_t)c->hObjects.size();
     s.anyEmissive = host.anyEmissive ? 1u : 0u;
     s.emissionFinite = host.emissionFinite ? 1u : 0u;
+    s.extent = host.extent;
     for (int a = 0; a < 3; ++a) {     s.emisLo[a] = host.emisLo[a];     s.emisHi[a] = host.emisHi[a]; }
     s.uniqSphereMask = host.uniqSphereMask; s.emisSphereMask = host.emisSphereMask; s.plainSphereMask = host.plainSphereMask;
     w->maxDepth = depthAll;
@@ -758,6 +764,9 @@ void wavefront_destroy(b200pt_ctx* c) {
     if (w->evFork) cudaEventDestroy(w->evFork);
     if (w->evJoin) cudaEventDestroy(w->evJoin);
     if (w->sideStream) cudaStreamDestroy(w->sideStream);
+    if (w->evX0) cudaEventDestroy(w->evX0);
+    if (w->evX1) cudaEventDestroy(w->evX1);
+    if (w->exactStream) cudaStreamDestroy(w->exactStream);
     delete w;
     c->wf = nullptr;
 }
@@ -881,12 +890,22 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                 WCU(cudaEventCreateWithFlags(&w->evJoin, cudaEventDisableTiming));
             }
             P.connectAfterExtend = overlap ? 0u : 1u;
+            // k_exact_extend of bounce j+1 (a few rays per thousand, one thread each: latency bound) is only needed by
+            // shade(j+1): it runs on its own stream beside the connect chain of bounce j. (prep reads hit.id of those paths
+            // meanwhile, only to see whether the ray escaped: a contested ray has candidates, so both values say "hit".)
+            const bool exactAside = !c->profileStages && !overlap;
+            if (exactAside && !w->exactStream) {
+                WCU(cudaStreamCreateWithFlags(&w->exactStream, cudaStreamNonBlocking));
+                WCU(cudaEventCreateWithFlags(&w->evX0, cudaEventDisableTiming));
+                WCU(cudaEventCreateWithFlags(&w->evX1, cudaEventDisableTiming));
+            }
             wf_mark(c, ST_EXTEND);
             unsigned long long* workCnt = (unsigned long long*)w->dRayCounters.p + 8;     // [8,9] extend, [10,11] occlude
             uint32_t* exactQ = (uint32_t*)w->dExactQ.p;
             uint32_t* exactNeeQ = (uint32_t*)w->dExactNeeQ.p;
             if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, workCnt);
             else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, nullptr);
+            wf_mark(c, ST_EXACT);
             k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
             for (uint32_t j = 0; j < nB; ++j) {
                 wf_mark(c, ST_SHADE);
@@ -902,7 +921,13 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     wf_mark(c, ST_EXTEND);
                     if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, workCnt);
                     else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, nullptr);
-                    k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
+                    wf_mark(c, ST_EXACT);
+                    if (exactAside) {
+                        WCU(cudaEventRecord(w->evX0, c->stream));
+                        WCU(cudaStreamWaitEvent(w->exactStream, w->evX0, 0));
+                    }
+                    k_exact_extend<<<gridExact, WF_THREADS, 0, exactAside ? w->exactStream : c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
+                    if (exactAside) WCU(cudaEventRecord(w->evX1, w->exactStream));
                     wf_mark(c, ST_CONNECT);
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                        (uint32_t*)w->dJobQ.p, oCount + j, exactNeeQ, xnCount + j);
@@ -910,6 +935,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     uint32_t* misQ = (uint32_t*)w->dJobQ.p + w->capacity;      // second half of the job buffer
                     if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
                     else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
+                    wf_mark(c, ST_EXACT);
                     k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
@@ -918,6 +944,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                         WCU(cudaEventRecord(w->evJoin, w->sideStream));
                         WCU(cudaStreamWaitEvent(c->stream, w->evJoin, 0));
                     }
+                    if (exactAside) WCU(cudaStreamWaitEvent(c->stream, w->evX1, 0));
                 }
                 std::swap(qa, qb);
                 c->counters[0] += (j + 1 < nB) ? 8 : 1;

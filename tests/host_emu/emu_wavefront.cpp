@@ -44,6 +44,7 @@ void* emu_scene_create(const void* spheres, uint32_t nS, const void* materials, 
     v.nXforms = (uint32_t)s->wide.xforms.size(); v.nSpheres = nS; v.nMaterials = nM; v.nObjects = nO;
     v.anyEmissive = s->wide.anyEmissive ? 1u : 0u;
     v.emissionFinite = s->wide.emissionFinite ? 1u : 0u;
+    v.extent = s->wide.extent;
     for (int a = 0; a < 3; ++a) {     v.emisLo[a] = s->wide.emisLo[a];     v.emisHi[a] = s->wide.emisHi[a]; }
     v.uniqSphereMask = s->wide.uniqSphereMask; v.emisSphereMask = s->wide.emisSphereMask; v.plainSphereMask = s->wide.plainSphereMask;
     v.primOf = s->wide.primOf.data(); v.instBase = s->wide.instBase.data(); v.triFirst = s->wide.triFirst.data();
