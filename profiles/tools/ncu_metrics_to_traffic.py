@@ -6,7 +6,8 @@ gpu__time_duration.sum,... --clock-control none -k regex:'k_extend|k_occlude|k_s
         --csv --log-file metrics.csv python bench.py --steps 1 --warmup 1 --only-value
     python profiles/tools/ncu_metrics_to_traffic.py metrics.csv atrium 49766400 width=1920 height=1080 frames_in_flight=24 bounce_limit=8
 
-The capture holds the warm-up step and the timed step; the second half of the launches is the timed step. Sums per
+The capture of `bench.py --steps 1 --warmup 1 --only-value` holds three identical steps (warm-up, timed, the pass with
+stage events): the launches of every kernel are split in three and the last third is taken (parts=N overrides). Sums per
 kernel over the step: DRAM bytes, warp instructions, thread instructions, ncu's (serialised, cold-cache) time."""
 import collections
 import csv
@@ -28,9 +29,15 @@ def load(fn):
 def main():
     fn, workload, units = sys.argv[1], sys.argv[2], int(sys.argv[3])
     cfg = {k: int(v) for k, v in (a.split("=") for a in sys.argv[4:] if not a.startswith("--"))}
-    whole = "--whole" in sys.argv
+    parts = cfg.pop("parts", 3)
     L = load(fn)
-    step = L if whole else L[len(L) // 2:]
+    per = collections.OrderedDict()
+    for l in L:
+        per.setdefault(l["name"], []).append(l)
+    step = []
+    for name, ls in per.items():                      # last 1/parts of each kernel's launches = one step
+        n = len(ls) // parts
+        step += ls[len(ls) - n:] if n else []
     agg = collections.OrderedDict()
     for l in step:
         a = agg.setdefault(l["name"], dict(launches=0, dram_bytes=0.0, warp_inst=0.0, thread_inst=0.0, time_ms_ncu=0.0))

@@ -398,7 +398,7 @@ PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, Stack& stack, float tmax
 // reference's loop order (sphere i -> i, object o -> nSpheres + o; 0xffffffff for none): the
 // reference keeps the FIRST of equal-distance hits.
 PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                 float extent, Trav& t, Hit& hit, uint32_t& key) {
+                                 float extent, Trav& t, Hit& hit, uint32_t& key, float* bestInvCos = nullptr) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     uint32_t pi = t.tBase + (uint32_t)k;
@@ -415,7 +415,11 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
     const bool near = fabsf(dst - hit.dst) <= contest_window(fmaxf(dst, hit.dst), extent) && hit.id != PT_HIT_MISS;
     if (!(wins || near) || !ref_reachable(up, p, t.oc, dst)) return;
     if (near && (hit.id & ~PT_HIT_FRONT) != pi) t.br.octinv4 |= PT_TRAV_CONTESTED;
-    if (wins) t.br.octinv4 = (t.br.octinv4 & ~PT_TRAV_GRAZING) | (hit_is_grazing(te, tr, invD0) ? PT_TRAV_GRAZING : 0u);
+    if (wins) {
+        const float g = inv_cos_incidence(te, tr, invD0);
+        t.br.octinv4 = (t.br.octinv4 & ~PT_TRAV_GRAZING) | (g > PT_GRAZE ? PT_TRAV_GRAZING : 0u);
+        if (bestInvCos) *bestInvCos = g;
+    }
 #else
     if (!wins || !ref_reachable(up, p, t.oc, dst)) return;
 #endif
@@ -433,7 +437,7 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
 #define PT_OCCL_YES 1
 #define PT_OCCL_CONTESTED 2
 PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                 float extent, Trav& t, float tE, uint32_t keyE) {
+                                 float extent, float windowScale, Trav& t, float tE, uint32_t keyE) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
     const PrimRecord p = load_prim(bvh.prims, t.tBase + (uint32_t)k);
@@ -444,7 +448,7 @@ PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const
     if (!tri_test_r(te, tr, (p.triIndexFlags & PT_PRIM_FRONTONLY) != 0, dst, u, v, front, invD0)) return PT_OCCL_NO;
     const bool closer = dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE);
     const float gap = fabsf(dst - tE), window = contest_window(fmaxf(dst, tE), extent);
-    const bool near = gap <= window;
+    const bool near = gap <= window * windowScale;          // windowScale >= 1: the emissive hit's own error grows with its 1 / cos
     if (!(closer || near) || !ref_reachable(up, p, t.oc, dst)) return PT_OCCL_NO;
 #if PT_CONTEST
     // an occluder far in front of tE decides unless its own distance error (which grows with 1 / cos) reaches back to tE
@@ -453,34 +457,34 @@ PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const
     return closer ? PT_OCCL_YES : PT_OCCL_NO;
 }
 
-// Per-ray loops over the steps (host emulation, the small emissive BVH). `contested` is OR-ed, `slack` returns the
-// best hit's slack.
+// Per-ray loops over the steps (host emulation, the small emissive BVH). `contested` is OR-ed: with bestInvCos == NULL
+// it includes "the best hit is grazing"; otherwise 1 / cos(incidence) of the best triangle hit is returned instead.
 PT_HD_NOINLINE void bvh8_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, float extent, Hit& hit, uint32_t& key, uint32_t& contested) {
+                                 uint32_t objectCount, float extent, Hit& hit, uint32_t& key, uint32_t& contested, float* bestInvCos = nullptr) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     for (;;) {
-        if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, extent, t, hit, key);
+        if (trav_has_tri(t)) trav_tri_step_closest(bvh, xforms, up, nSpheres, objectCount, extent, t, hit, key, bestInvCos);
         else if (trav_has_node(t)) trav_node_step(bvh, t, stack, cull_dst(hit.dst, extent));
         else if (!trav_pop(t, stack)) break;
     }
-    contested |= trav_contested(t) ? 1u : 0u;
+    contested |= (bestInvCos ? (t.br.octinv4 & PT_TRAV_CONTESTED) != 0u : trav_contested(t)) ? 1u : 0u;
 }
 // -> PT_OCCL_NO / PT_OCCL_YES / PT_OCCL_CONTESTED
 PT_HD_NOINLINE int bvh8_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, const Ray& ray,
-                                 uint32_t objectCount, float extent, float tE, uint32_t keyE) {
+                                 uint32_t objectCount, float extent, float windowScale, float tE, uint32_t keyE) {
     PrivateStack stack;
     Trav t;
     trav_begin(t, ray);
     int contested = PT_OCCL_NO;
     for (;;) {
         if (trav_has_tri(t)) {
-            const int r = trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, extent, t, tE, keyE);
+            const int r = trav_tri_step_occluded(bvh, xforms, up, nSpheres, objectCount, extent, windowScale, t, tE, keyE);
             if (r == PT_OCCL_YES) return PT_OCCL_YES;
             if (r == PT_OCCL_CONTESTED) contested = PT_OCCL_CONTESTED;
         }
-        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, cull_dst(tE, extent));
+        else if (trav_has_node(t)) trav_node_step(bvh, t, stack, tE + contest_window(tE, extent) * windowScale);
         else if (!trav_pop(t, stack)) break;
     }
     return contested;

@@ -307,7 +307,7 @@ PT_HD uint32_t stage_shade(const WfParams& P, const WideScene& sc, const PathArr
 //   occlude : is there a non-emissive triangle the reference would have preferred? (bounded any-hit
 //             walk of the full BVH, the expensive part: its own persistent kernel, wavefront.cu)
 //   finish  : pdfs, MIS weights, direct light (raytrace.comp:447-460)
-// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, - }, tE < 0: no emissive closest hit
+// qE[p] = { tE(lightSample), material of that emissive hit, loop-order key of it, scale of the contest window }, tE < 0: no emissive closest hit
 // (none found, or occluded). Those paths keep the directLight shade stored (a zero: E = 0, pdf = 0); finish only reads
 // their qE. (Finishing the unoccluded ones inside the occlusion kernel, by the lane that ends the walk, was measured:
 // k_connect_finish 3.7 -> 0 ms but k_occlude 35.3 -> 39.7 ms per step — four dependent loads in a converged warp.)
@@ -330,8 +330,8 @@ PT_HD bool ray_meets_box(const Ray& r, const float* lo, const float* hi) {
 // contested: see pt_traverse.h ("exactness against the reference's traversal order") — two emissive candidates, or
 // the emissive candidate and a sphere, closer together than the slack: the caller asks the reference-order search.
 PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t sphereCount, uint32_t objectCount, uint32_t& keyE,
-                               uint32_t& matOut, uint32_t& contested) {
-    matOut = 0u; keyE = 0xffffffffu;
+                               uint32_t& matOut, uint32_t& contested, float& windowScale) {
+    matOut = 0u; keyE = 0xffffffffu; windowScale = 1.f;
     if (!sc.anyEmissive) return PT_NO_EMISSIVE;
     Ray r; r.o = origin; r.d = dir;
     Hit e; e.dst = PT_FAR; e.id = PT_HIT_MISS; e.u = 0.f; e.v = 0.f;
@@ -353,10 +353,14 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
         }
     }
     uint32_t before = e.id;
-    if (sc.emis.nPrims && ray_meets_box(r, sc.emisLo, sc.emisHi)) bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, sc.extent, e, keyE, contested);
+    if (sc.emis.nPrims && ray_meets_box(r, sc.emisLo, sc.emisHi)) {
+        float g = 0.f;
+        bvh8_closest(sc.emis, sc.xforms, sc.up, sc.nSpheres, r, objectCount, sc.extent, e, keyE, contested, &g);
+        if (e.id != before) windowScale = fmaxf(1.f, g * (1.f / 16.f));     // the window grows with 1 / cos of the emissive hit
+    }
     if (e.id == PT_HIT_MISS) return PT_NO_EMISSIVE;
     if (e.id != before) matOut = sc.shadeEmis[e.id & PT_HIT_IDMASK].materialIndex;
-    const float slackE = (e.id & PT_HIT_SPHERE) ? -1.f : contest_window(e.dst, sc.extent);      // a sphere is never pruned by the reference
+    const float slackE = (e.id & PT_HIT_SPHERE) ? -1.f : contest_window(e.dst, sc.extent) * windowScale;      // a sphere is never pruned by the reference
     if (masks) {
         for (uint32_t mk = sc.plainSphereMask & live; mk; mk &= mk - 1u) {
             uint32_t i = (uint32_t)lowest_bit(mk);
@@ -385,22 +389,23 @@ PT_HD float emissive_candidate(const WideScene& sc, v3 origin, v3 dir, uint32_t 
 PT_HD uint32_t stage_connect_prep(const WfParams& P, const WideScene& sc, const PathArrays& A, uint32_t p) {
     const ptl::RayTracerData& td = P.pc.params;
     uint32_t keyL = 0xffffffffu, matL = 0u, contested = 0u;
-    float tL = PT_NO_EMISSIVE;
+    float tL = PT_NO_EMISSIVE, scaleL = 1.f;
     // connectAfterExtend: bounce j+1 was already extended; directLight of bounce j is dropped when it missed (:531-534)
     bool dropped = P.connectAfterExtend && A.hit[p].id == PT_HIT_MISS;
     if (!dropped)            // (rays that cannot contribute never get here: stage_shade)
-        tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL, contested);  // :443-447
-    A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), 0.f);
+        tL = emissive_candidate(sc, xyz(A.qO[p]), xyz(A.qL[p]), td.sphereCount, td.objectCount, keyL, matL, contested, scaleL);  // :443-447
+    A.qE[p] = make_float4(tL, as_float(matL), as_float(keyL), scaleL);
     if (contested) return PT_CONNECT_JOB_EXACT;
     return tL >= 0.f ? PT_CONNECT_JOB_LIGHT : 0u;
 }
 // the occlusion query of path p's light-sample ray
-PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, uint32_t& keyE) {
+PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, uint32_t& keyE, float& windowScale) {
     float4 e = A.qE[p];
     r.o = xyz(A.qO[p]);
     r.d = xyz(A.qL[p]);
     tE = e.x;
     keyE = as_uint(e.z);
+    windowScale = e.w;
 }
 // A contested light-sample ray: lightSamplePDF's closest-hit search (raytrace.comp:396-397) in the reference's own order.
 PT_HD void connect_exact(const RefScene& ref, const ptl::RayTracerData& td, const PathArrays& A, uint32_t p) {
@@ -441,9 +446,9 @@ PT_HD_NOINLINE void connect_mis_weight_exact(const RefScene& ref, const ptl::Ray
 PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const RefScene& ref, const PathArrays& A, uint32_t p) {
     uint32_t job = stage_connect_prep(P, sc, A, p);
     if (job == PT_CONNECT_JOB_LIGHT) {
-        Ray r; float tE; uint32_t keyE;
-        connect_job_ray(A, p, r, tE, keyE);
-        const int o = bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, sc.extent, tE, keyE);
+        Ray r; float tE, ws; uint32_t keyE;
+        connect_job_ray(A, p, r, tE, keyE, ws);
+        const int o = bvh8_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, r, P.pc.params.objectCount, sc.extent, ws, tE, keyE);
         if (o == PT_OCCL_YES) connect_job_occluded(A, p);
         else if (o == PT_OCCL_CONTESTED) job = PT_CONNECT_JOB_EXACT;
     }

@@ -377,7 +377,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
     PT_DECLARE_STACK(stack);
     WarpFeeder feed;
     Trav t;
-    float tE = 0.f;
+    float tE = 0.f, ws = 1.f;
     uint32_t keyE = 0, job = 0;
     bool busy = false;
     t.gBits = 0; t.tBits = 0; t.sp = 0;
@@ -392,7 +392,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             if (feeder_take(feed, workCounter, n, __ballot_sync(0xffffffffu, !busy), qi)) {
                 job = jobQueue[qi];
                 Ray r;
-                connect_job_ray(A, job, r, tE, keyE);
+                connect_job_ray(A, job, r, tE, keyE, ws);
                 trav_begin(t, r);
                 busy = true;
             }
@@ -404,7 +404,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP_OCCL && trav_has_tri(t); ++r) {
                     if (COUNT) cntTri++;
-                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, t, tE, keyE);
+                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, ws, t, tE, keyE);
                     if (o != PT_OCCL_NO) {
                         if (o == PT_OCCL_YES) connect_job_occluded(A, job);
                         else exactQueue[atomicAdd(exactCount, 1u)] = job;      // contested: k_exact_nee answers in the reference's order
@@ -415,9 +415,9 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
             }
         } else {
             if (canNode) {
-                trav_node_step(sc.all, t, stack, cull_dst(tE, sc.extent)); if (COUNT) cntNode++;
+                trav_node_step(sc.all, t, stack, tE + contest_window(tE, sc.extent) * ws); if (COUNT) cntNode++;
 #pragma unroll 1
-                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, cull_dst(tE, sc.extent)); if (COUNT) cntNode++; }
+                for (int r = 1; r < PT_NODE_PER_STEP && trav_has_node(t) && !trav_has_tri(t); ++r) { trav_node_step(sc.all, t, stack, tE + contest_window(tE, sc.extent) * ws); if (COUNT) cntNode++; }
             }
         }
     }
@@ -893,7 +893,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             // k_exact_extend of bounce j+1 (a few rays per thousand, one thread each: latency bound) is only needed by
             // shade(j+1): it runs on its own stream beside the connect chain of bounce j. (prep reads hit.id of those paths
             // meanwhile, only to see whether the ray escaped: a contested ray has candidates, so both values say "hit".)
-            const bool exactAside = !c->profileStages && !overlap;
+            const bool exactAside = !c->profileStages;
             if (exactAside && !w->exactStream) {
                 WCU(cudaStreamCreateWithFlags(&w->exactStream, cudaStreamNonBlocking));
                 WCU(cudaEventCreateWithFlags(&w->evX0, cudaEventDisableTiming));
