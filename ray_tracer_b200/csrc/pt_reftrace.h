@@ -33,10 +33,17 @@ PT_HD v3 ld3(const float* p) { return mk3(p[0], p[1], p[2]); }
 
 // calculateIntersections(), raytrace.comp:276-353. stats may be null (NEE / pdf rays use
 // throw-away arrays in the shader, :391,:442).
-PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerData& td, const Ray& ray, float* stats) {
+// bound0 (default: none): a PHANTOM upper bound for the re-trace of contested rays (pt_traverse.h). The wide traversal
+// already knows the smallest candidate distance m; every candidate that can win lies within the contest window w of m and
+// its enclosing boxes start before m + 2w. Starting the search with closestHit.dst = m + 3w instead of 99999999 prunes, from
+// the first node on, only subtrees whose boxes start beyond it: their triangles cannot win, and the only other thing they
+// could do — lower closestHit.dst to some value still above m + 2w — changes no pruning decision for a candidate that can
+// win (its boxes start before that value either way). Same winner, a tenth of the node visits. A search that ends without a
+// hit is repeated without the bound.
+PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerData& td, const Ray& ray, float* stats, float bound0 = PT_FAR) {
     RefHit best;
     best.kind = 0;
-    best.dst = PT_FAR;
+    best.dst = bound0;
     best.materialIndex = 0;                     // uninitialised in the shader on a miss; pinned (A-Q9)
     best.objectHitIndex = 0xffffffffu;
     best.triHitIndex = 0;
@@ -96,6 +103,10 @@ PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerDa
                 if (dNear < best.dst && sp < 72) stack[sp++] = iNear;
             }
         }
+    }
+    if (best.kind == 0u) {
+        if (bound0 < PT_FAR) return ref_closest_hit(sc, td, ray, stats, PT_FAR);
+        best.dst = PT_FAR;
     }
     return best;
 }

@@ -112,8 +112,9 @@ PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereC
 }
 // The hit of a CONTESTED ray (pt_traverse.h): calculateIntersections in the reference's own order over the reference's own
 // buffers (pt_reftrace.h), expressed as the wavefront's Hit (record index of the triangle in the wide layout).
-PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl::RayTracerData& td, const Ray& ray) {
-    const RefHit r = ref_closest_hit(ref, td, ray, nullptr);
+PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl::RayTracerData& td, const Ray& ray, float wideDst) {
+    // wideDst: the distance the wide traversal found (the smallest candidate): phantom bound of the re-trace (pt_reftrace.h)
+    const RefHit r = ref_closest_hit(ref, td, ray, nullptr, wideDst + 3.f * contest_window(wideDst, sc.extent));
     Hit h; h.dst = r.dst; h.u = 0.f; h.v = 0.f; h.id = PT_HIT_MISS;
     if (r.kind == 1u) h.id = PT_HIT_SPHERE | (r.front ? PT_HIT_FRONT : 0u) | r.triHitIndex;
     else if (r.kind == 2u) {
@@ -126,7 +127,7 @@ PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const RefScene& 
     Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
     uint32_t contested = 0u;
     Hit h = wide_closest_hit(sc, r, P.pc.params.sphereCount, P.pc.params.objectCount, contested);
-    if (contested) h = exact_closest_hit(ref, sc, P.pc.params, r);
+    if (contested) h = exact_closest_hit(ref, sc, P.pc.params, r, h.dst);
     A.hit[p] = h;
 }
 
@@ -408,9 +409,12 @@ PT_HD void connect_job_ray(const PathArrays& A, uint32_t p, Ray& r, float& tE, u
     windowScale = e.w;
 }
 // A contested light-sample ray: lightSamplePDF's closest-hit search (raytrace.comp:396-397) in the reference's own order.
-PT_HD void connect_exact(const RefScene& ref, const ptl::RayTracerData& td, const PathArrays& A, uint32_t p) {
+PT_HD void connect_exact(const RefScene& ref, const WideScene& sc, const ptl::RayTracerData& td, const PathArrays& A, uint32_t p) {
     Ray r; r.o = xyz(A.qO[p]); r.d = xyz(A.qL[p]);
-    const RefHit h = ref_closest_hit(ref, td, r, nullptr);
+    // phantom bound (pt_reftrace.h): nothing beyond the emissive candidate's window can be the closest hit of this ray
+    const float4 qe = A.qE[p];
+    const float bound = qe.x >= 0.f ? qe.x + 3.f * contest_window(qe.x, sc.extent) * fmaxf(qe.w, 1.f) : PT_FAR;
+    const RefHit h = ref_closest_hit(ref, td, r, nullptr, bound);
     const bool emissive = h.kind != 0u && !(ref.materials[h.materialIndex].emissionStrength == 0.f);
     A.qE[p] = make_float4(emissive ? h.dst : PT_NO_EMISSIVE, as_float(h.materialIndex), 0.f, 0.f);
 }
@@ -452,7 +456,7 @@ PT_HD void stage_connect(const WfParams& P, const WideScene& sc, const RefScene&
         if (o == PT_OCCL_YES) connect_job_occluded(A, p);
         else if (o == PT_OCCL_CONTESTED) job = PT_CONNECT_JOB_EXACT;
     }
-    if (job == PT_CONNECT_JOB_EXACT) connect_exact(ref, P.pc.params, A, p);
+    if (job == PT_CONNECT_JOB_EXACT) connect_exact(ref, sc, P.pc.params, A, p);
     if (connect_job_finish(sc, A, p)) connect_mis_weight_exact(ref, P.pc.params, A, p);
 }
 

@@ -453,14 +453,14 @@ __global__ void __launch_bounds__(WF_THREADS) k_exact_extend(const __grid_consta
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t p = queue[i];
         Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-        hitOut[p] = exact_closest_hit(ref, sc, P.pc.params, r);
+        hitOut[p] = exact_closest_hit(ref, sc, P.pc.params, r, hitOut[p].dst);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && total) atomicAdd(total, (unsigned long long)n);
 }
-__global__ void __launch_bounds__(WF_THREADS) k_exact_nee(const __grid_constant__ WfParams P, const __grid_constant__ RefScene ref, PathArrays A,
+__global__ void __launch_bounds__(WF_THREADS) k_exact_nee(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, const __grid_constant__ RefScene ref, PathArrays A,
                                                           const uint32_t* __restrict__ queue, const uint32_t* __restrict__ count, unsigned long long* total) {
     const uint32_t n = *count;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) connect_exact(ref, P.pc.params, A, queue[i]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) connect_exact(ref, sc, P.pc.params, A, queue[i]);
     if (blockIdx.x == 0 && threadIdx.x == 0 && total) atomicAdd(total, (unsigned long long)n);
 }
 
@@ -936,7 +936,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
                     else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
                     wf_mark(c, ST_EXACT);
-                    k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
+                    k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, w->scene, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
                     k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, misQ, mCount + j);

@@ -125,7 +125,7 @@ int emu_wf_trace_batch2(void* sp, const void* pc208, const float* rays, uint64_t
         Ray r; r.o = mk3(rays[8 * i], rays[8 * i + 1], rays[8 * i + 2]); r.d = mk3(rays[8 * i + 4], rays[8 * i + 5], rays[8 * i + 6]);
         uint32_t contested = 0u;
         Hit h = wide_closest_hit(sc, r, pc.params.sphereCount, pc.params.objectCount, contested);
-        if (contested) { h = exact_closest_hit(s->ref, sc, pc.params, r); if (nContested) {
+        if (contested) { h = exact_closest_hit(s->ref, sc, pc.params, r, h.dst); if (nContested) {
 #pragma omp atomic
             nContested[0]++; } }
         Rec o; std::memset(&o, 0, sizeof(o));
