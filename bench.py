@@ -360,6 +360,8 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the backend has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"          # NCCL would print its version banner on stdout, in front of the JSON line
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -536,6 +538,10 @@ def main():
     interactive(3)
     ms_inter, _, _ = device_ms(lambda: interactive(n_inter))
     ms_inter /= n_inter
+    cp.set_option("exact_order", 0)         # without the reference-order re-trace of contested rays (not bit-exact: see exact_retrace)
+    interactive(2)
+    ms_inter_fast = device_ms(lambda: interactive(n_inter))[0] / n_inter
+    cp.set_option("exact_order", 1)
 
     # the engine's own per-frame call: b200pt_render = one literal dispatch (progressive blend into the storage image)
     def dispatches(k, first):
@@ -609,6 +615,7 @@ def main():
             cp5.clear()
             cp5.render_frames_split(pc5.buffer, first, F5 * N)
         c5_run(0)
+        cp5.reduce_accum(0, zero_others=True)          # first collective of this communicator: NCCL sets its channels up here
         ms_c5, _, _ = device_ms(lambda: c5_run(F5 * N))
         ms_red, _, _ = device_ms(lambda: cp5.reduce_accum(0, zero_others=True))
         t_d2h = time.perf_counter()
@@ -647,7 +654,7 @@ def main():
                    rays_per_path=dict(traced=counted["extension_rays_traced_per_path"] + counted["occlusion_rays_traced_per_path"] + counted["pdf_rays_traced_per_path"],
                                       reference=avoided["reference_rays_per_path"]))
         out.update(roofline=roofline, cpu_baseline=cpu, parity=parity, counted_work=counted, strong_scaling=strong, c5=c5, update_objects=upd,
-                   interactive=dict(ms_per_frame=ms_inter, frames=n_inter, run_compute_ms=ms_dispatch, run_compute_pipeline0_ms=ms_dispatch_ref,
+                   interactive=dict(ms_per_frame=ms_inter, ms_per_frame_without_exact_retrace=ms_inter_fast, frames=n_inter, run_compute_ms=ms_dispatch, run_compute_pipeline0_ms=ms_dispatch_ref,
                                     split="interleaved rows over %d GPU(s), gathered on rank 0 inside the library (ncclSend/Recv)" % N,
                                     note="one 1-spp progressive frame at a time (latency), vs ms_per_frame_1spp = throughput mode / frames"))
         if args.dump:

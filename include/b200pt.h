@@ -179,7 +179,10 @@ int b200pt_render_frame_interleaved(b200pt_ctx* ctx, const void* push_constants_
  * never / for batches of up to 8 frames (default) / always; "share_primary" 0/1, "trav_tri_vote" 1..32, "trav_fetch_idle" 1..32 (k_extend), "occl_tri_vote", "occl_fetch_idle" (k_occlude): scheduling of the wavefront kernels
  * (results do not depend on them); "wide_build" 1 (default) / 0: the internal wide BVH of all triangles is built on
  * the device / on the host at b200pt_upload_scene and b200pt_update_* (read before the upload; images do not depend
- * on it); "refit_on_update" 1 (default) / 0. Read-only: "last_scene_build_us", "last_wide_device_us",
+ * on it); "refit_on_update" 1 (default) / 0; "exact_order" 1 (default) / 0: rays on which two candidates lie
+ * closer together than the rounding error of their distances (coincident surfaces; about 5 per thousand in the C4 stand-in)
+ * are re-traced in the reference's own traversal order, which makes every result the reference's bit for bit; 0 skips the
+ * re-trace (2 ms less latency per 1-spp frame, about 1e-4 of the paths then depend on the traversal order). Read-only: "last_scene_build_us", "last_wide_device_us",
  * "last_update_was_refit". Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);

@@ -467,6 +467,7 @@ int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (k == "overlap_connect") { if (v < 0 || v > 2) return fail(c, B200PT_ERR_ARG, "overlap_connect must be 0..2"); c->overlapConnect = (int)v; return 0; }
     if (k == "wide_build") { if (v < 0 || v > 1) return fail(c, B200PT_ERR_ARG, "wide_build must be 0 (host) or 1 (device)"); c->wideBuild = (int)v; return 0; }
     if (k == "refit_on_update") { c->refitOnUpdate = v != 0; return 0; }
+    if (k == "exact_order") { c->exactOrder = v != 0; return 0; }
     return fail(c, B200PT_ERR_ARG, "unknown option '%s'", key);
 }
 int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
@@ -486,6 +487,7 @@ int b200pt_get_option(b200pt_ctx* c, const char* key, int64_t* v) {
     if (k == "overlap_connect") { *v = c->overlapConnect; return 0; }
     if (k == "wide_build") { *v = c->wideBuild; return 0; }
     if (k == "refit_on_update") { *v = c->refitOnUpdate; return 0; }
+    if (k == "exact_order") { *v = c->exactOrder; return 0; }
     if (k == "last_update_was_refit") { *v = c->lastRefit; return 0; }                               // read-only
     if (k == "last_scene_build_us") { *v = (int64_t)(c->lastSceneBuildMs * 1000.0); return 0; }      // read-only
     if (k == "last_wide_device_us") { *v = (int64_t)(c->lastWideDeviceMs * 1000.0); return 0; }      // read-only

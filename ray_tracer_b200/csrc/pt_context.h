@@ -67,6 +67,7 @@ struct b200pt_ctx {
     int overlapConnect = 1;       // connect chain of bounce j beside extend(j+1) on a second stream: 0 never, 1 for batches of up to 8 frames, 2 always
     int sharePrimary = 1;         // trace the primary ray once per pixel and share the hit between frame slots (A-Q4)
     int wideBuild = 1;            // 1: the wide BVH of all triangles is built on the device (wide_build.cu), 0: on the host
+    int exactOrder = 1;           // contested rays are re-traced in the reference's order (k_exact_*); 0 skips that (results then depend on the traversal order for ~1e-4 of paths)
     int refitOnUpdate = 1;        // b200pt_update_objects with only matrices changed refits the device-built tree instead of rebuilding it
     int lastRefit = 0;            // the last re-layout was such a refit
     double lastSceneBuildMs = 0.0, lastWideDeviceMs = 0.0;   // wall time of the last re-layout; device part of it

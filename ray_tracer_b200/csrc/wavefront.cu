@@ -893,7 +893,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             // k_exact_extend of bounce j+1 (a few rays per thousand, one thread each: latency bound) is only needed by
             // shade(j+1): it runs on its own stream beside the connect chain of bounce j. (prep reads hit.id of those paths
             // meanwhile, only to see whether the ray escaped: a contested ray has candidates, so both values say "hit".)
-            const bool exactAside = !c->profileStages;
+            const bool exactAside = !c->profileStages && c->exactOrder;
             if (exactAside && !w->exactStream) {
                 WCU(cudaStreamCreateWithFlags(&w->exactStream, cudaStreamNonBlocking));
                 WCU(cudaEventCreateWithFlags(&w->evX0, cudaEventDisableTiming));
@@ -906,7 +906,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, workCnt);
             else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, nullptr);
             wf_mark(c, ST_EXACT);
-            k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
+            if (c->exactOrder) k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
             for (uint32_t j = 0; j < nB; ++j) {
                 wf_mark(c, ST_SHADE);
                 k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
@@ -926,7 +926,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                         WCU(cudaEventRecord(w->evX0, c->stream));
                         WCU(cudaStreamWaitEvent(w->exactStream, w->evX0, 0));
                     }
-                    k_exact_extend<<<gridExact, WF_THREADS, 0, exactAside ? w->exactStream : c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
+                    if (c->exactOrder) k_exact_extend<<<gridExact, WF_THREADS, 0, exactAside ? w->exactStream : c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
                     if (exactAside) WCU(cudaEventRecord(w->evX1, w->exactStream));
                     wf_mark(c, ST_CONNECT);
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
@@ -936,7 +936,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
                     else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
                     wf_mark(c, ST_EXACT);
-                    k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, w->scene, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
+                    if (c->exactOrder) k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, w->scene, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
                     k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, misQ, mCount + j);
