@@ -134,6 +134,18 @@ int b200pt_trace_batch(b200pt_ctx* ctx, const void* push_constants_208, const fl
 int b200pt_trace_batch_device(b200pt_ctx* ctx, const void* push_constants_208, const void* device_rays, uint64_t n,
                               void* device_hits48);
 
+/* b200pt_trace_batch_device for callers that cannot allocate. No counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same inputs, same records, same kernels; the scratch memory (ray slots, hits, queues, counters) is a file-scope
+ * static device array of B200PT_STATIC_MAX_RAYS * 56 + 256 bytes (3.5 MiB, held by every GPU that loads the library
+ * until exit) instead of buffers grown with cudaMalloc. The call makes no cudaMalloc / cudaFree and calls no allocating
+ * library routine; the scene must have been uploaded before (that is where allocation happens). n above
+ * B200PT_STATIC_MAX_RAYS is rejected with B200PT_ERR_ARG and a message. Asynchronous on the context's stream.
+ * All calls on one GPU share the array: calls that overlap on the GPU (two streams, two contexts, two threads) race. */
+#define B200PT_STATIC_MAX_RAYS 65536u
+int b200pt_trace_batch_device_static(b200pt_ctx* ctx, const void* push_constants_208, const void* device_rays, uint64_t n,
+                                     void* device_hits48);
+
 /* GPU build of one object's BVH2 — replaces VulkanEngine::build_bvh(size, triIndex) with update_bvh_bounds,
  * subdivide_bvh and find_bvh_split_plane (src/vk_engine.cpp:1169-1337): 20-bin SAH, back-swapping partition,
  * depth-first node numbering. Bit-identical to the reference's sequential build for finite coordinates: same node

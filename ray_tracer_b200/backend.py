@@ -25,7 +25,7 @@ EXPORTS = (
     "b200pt_set_stream b200pt_sync b200pt_upload_scene b200pt_update_materials b200pt_update_spheres "
     "b200pt_update_objects b200pt_upload_texture b200pt_render b200pt_render_frames b200pt_render_frames_rows b200pt_render_frames_rows_strided "
     "b200pt_clear b200pt_read_accum_f32 b200pt_read_image_f32 b200pt_write_image_f32 b200pt_read_rgba8 "
-    "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch b200pt_trace_batch_device "
+    "b200pt_read_stats b200pt_device_accum_ptr b200pt_device_image_ptr b200pt_attach_accum b200pt_trace_batch b200pt_trace_batch_device b200pt_trace_batch_device_static "
     "b200pt_set_option b200pt_get_option b200pt_read_counters b200pt_reset_counters b200pt_read_stage_times "
     "b200pt_last_render_ms b200pt_build_bvh b200pt_comm_unique_id b200pt_comm_init_rank b200pt_comm_destroy b200pt_comm_info "
     "b200pt_render_frames_split b200pt_reduce_accum b200pt_render_frame_interleaved").split()
@@ -73,6 +73,7 @@ def load_library(path=None):
     L.b200pt_device_image_ptr.argtypes = [vp, C.POINTER(vp)]
     L.b200pt_trace_batch.argtypes = [vp, vp, vp, u64, vp]
     L.b200pt_trace_batch_device.argtypes = [vp, vp, vp, u64, vp]
+    L.b200pt_trace_batch_device_static.argtypes = [vp, vp, vp, u64, vp]
     L.b200pt_comm_unique_id.argtypes = [vp]
     L.b200pt_comm_init_rank.argtypes = [vp, i32, i32, vp]
     L.b200pt_comm_destroy.argtypes = [vp]
@@ -257,6 +258,15 @@ class ComputePass:
         pc = _bytes_array(push_constants)
         self._check(self.L.b200pt_trace_batch_device(self.h, _ptr(pc), C.c_void_p(device_rays), n, C.c_void_p(device_hits)),
                     "b200pt_trace_batch_device")
+
+    STATIC_MAX_RAYS = 65536      # B200PT_STATIC_MAX_RAYS
+
+    def trace_batch_device_static(self, push_constants, device_rays, n, device_hits):
+        """b200pt_trace_batch_device_static: the same call with its scratch in a static device array — allocates nothing,
+        n <= STATIC_MAX_RAYS, calls that overlap on one GPU race on the shared scratch."""
+        pc = _bytes_array(push_constants)
+        self._check(self.L.b200pt_trace_batch_device_static(self.h, _ptr(pc), C.c_void_p(device_rays), n, C.c_void_p(device_hits)),
+                    "b200pt_trace_batch_device_static")
 
     def counters(self):
         c = np.zeros(16, np.uint64)

@@ -450,6 +450,18 @@ int b200pt_trace_batch_device(b200pt_ctx* c, const void* pc208, const void* dRay
     return wavefront_trace_batch(c, pc, (const float*)dRays, n, (HitRecord48*)dHits);
 }
 
+int b200pt_trace_batch_device_static(b200pt_ctx* c, const void* pc208, const void* dRays, uint64_t n, void* dHits) {
+    ptl::PushConstants pc;
+    if (int rc = check_render(c, pc208, pc)) return rc;
+    if (n && (!dRays || !dHits)) return fail(c, B200PT_ERR_ARG, "trace_batch_device_static: NULL buffer");
+    if (n > B200PT_STATIC_MAX_RAYS)
+        return fail(c, B200PT_ERR_ARG, "trace_batch_device_static: %llu rays exceed the static scratch (B200PT_STATIC_MAX_RAYS = %u); split the batch or use b200pt_trace_batch_device",
+                    (unsigned long long)n, (unsigned)B200PT_STATIC_MAX_RAYS);
+    if (n == 0) return 0;
+    CU(c, cudaSetDevice(c->device));
+    return wavefront_trace_batch_static(c, pc, (const float*)dRays, n, (HitRecord48*)dHits);
+}
+
 int b200pt_set_option(b200pt_ctx* c, const char* key, int64_t v) {
     if (!c || !key) return B200PT_ERR_ARG;
     std::string k(key);

@@ -8,6 +8,10 @@
 // accumulate, fold.  Queue sizes live in device memory (qCount[j], sCount[j]); every kernel is a
 // grid-stride loop over its queue sized to the SM count, so an empty queue costs one idle launch.
 #include <algorithm>
+#include <cstdio>
+#include <mutex>
+
+#include "../../include/b200pt.h"
 
 #include "bvh8_build.h"
 #include "pt_wavefront.h"
@@ -1002,6 +1006,79 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
     }
     c->counters[2] += n;
     c->counters[4] += n;
+    WCU(cudaGetLastError());
+    return 0;
+}
+
+// ---- b200pt_trace_batch_device_static: the same launches with NO allocation ------------------------------------
+// wavefront_trace_batch keeps its scratch (ray slots, hits, queues, counters) in buffers that wf_reserve grows with
+// cudaMalloc. Callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid it) get a variant
+// whose scratch is this file-scope device array: a fixed size, held by every GPU that loads the library until exit.
+// Layout: 256-byte header {qCount, k_extend's work counter, contested count, pad, u64 re-trace total}, then per-ray
+// arrays origin (16 B) | direction (16 B) | Hit (16 B) | queue (4 B) | contested queue (4 B).
+// The NAME below is a host-side stand-in in host code, not a device address: its device address is looked up once per
+// device (cudaGetSymbolAddress with that device current) and only that pointer is handed to kernels.
+// Every call shares the array and finds the previous call's contents in it: the header is cleared at the start of each
+// call, the per-ray arrays are written before they are read. Calls that overlap on one GPU (two streams, two contexts,
+// two threads) race on it.
+#define WF_STATIC_HEADER 256
+#define WF_STATIC_PER_RAY 56
+static __device__ __align__(256) unsigned char g_staticScratch[WF_STATIC_HEADER + (size_t)B200PT_STATIC_MAX_RAYS * WF_STATIC_PER_RAY];
+static_assert(sizeof(Hit) == 16, "scratch layout");
+static unsigned char* g_staticScratchAddr[64] = {nullptr};      // per device ordinal
+static std::mutex g_staticScratchMutex;
+
+int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits) {
+    WavefrontState* w = c->wf;
+    if (!w || !w->haveScene) { c->error = "wavefront: no scene (the last upload or update failed)"; return 3; }
+    if (n > (uint64_t)B200PT_STATIC_MAX_RAYS) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "trace_batch_device_static: %llu rays exceed the static scratch (B200PT_STATIC_MAX_RAYS = %u); split the batch or use b200pt_trace_batch_device",
+                 (unsigned long long)n, (unsigned)B200PT_STATIC_MAX_RAYS);
+        c->error = msg;
+        return 1;
+    }
+    if (n == 0) return 0;
+    if (c->device < 0 || c->device >= 64) { c->error = "trace_batch_device_static: device ordinal above 63"; return 1; }
+    unsigned char* base;
+    {
+        std::lock_guard<std::mutex> lock(g_staticScratchMutex);
+        if (!g_staticScratchAddr[c->device]) {                   // once per device; the caller made c->device current
+            void* q = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&q, g_staticScratch);
+            if (e != cudaSuccess || !q) return wf_fail(c, 2, "cudaGetSymbolAddress(g_staticScratch)", e);
+            g_staticScratchAddr[c->device] = (unsigned char*)q;
+        }
+        base = g_staticScratchAddr[c->device];
+    }
+    if (!w->gridExtend) {
+        int perSm = 0;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
+        w->gridExtend = std::max(1, perSm) * w->smCount;
+    }
+    const size_t cap = B200PT_STATIC_MAX_RAYS;
+    uint32_t* header = (uint32_t*)base;
+    PathArrays A;
+    memset(&A, 0, sizeof(A));
+    A.rayO = (float4*)(base + WF_STATIC_HEADER);
+    A.rayD = A.rayO + cap;
+    A.hit = (Hit*)(A.rayD + cap);
+    uint32_t* queue = (uint32_t*)(A.hit + cap);
+    uint32_t* exactQ = queue + cap;
+    uint32_t* qCount = header, *workE = header + 1, *xCount = header + 2;
+    unsigned long long* total = (unsigned long long*)(header + 4);
+    WfParams P;
+    memset(&P, 0, sizeof(P));
+    P.pc = pc; P.W = c->W; P.H = c->H; P.rowStride = 1;
+    P.triVote32 = (uint32_t)c->triVote32; P.fetchMinIdle = (uint32_t)c->fetchMinIdle;
+    const uint32_t m = (uint32_t)n;
+    const int grid = std::min<int>(w->smCount * 8, (int)((m + WF_THREADS - 1) / WF_THREADS));
+    WCU(cudaMemsetAsync(header, 0, WF_STATIC_HEADER, c->stream));
+    k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays, m, A, queue, qCount);
+    k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, A, queue, qCount, workE, A.hit, exactQ, xCount, nullptr);
+    if (c->exactOrder) k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, A, exactQ, xCount, A.hit, total);
+    k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, A, m, dHits);
+    c->counters[0] += 4;
     WCU(cudaGetLastError());
     return 0;
 }

@@ -17,6 +17,8 @@ void wavefront_invalidate_frame_state(b200pt_ctx* c);
 int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_t first, uint32_t n, uint32_t stride,
                             uint32_t row0, uint32_t row1, float4* dispatchImage = nullptr, uint32_t rowStride = 1);
 int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits);
+// the same launches with the scratch in a static device array (no allocation; n <= B200PT_STATIC_MAX_RAYS)
+int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, const float* dRays, uint64_t n, HitRecord48* dHits);
 void wavefront_fold_counters(b200pt_ctx* c);
 void wavefront_resolve_stage_times(b200pt_ctx* c);     // stream idle
 void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool reset);
