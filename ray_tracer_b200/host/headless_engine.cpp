@@ -9,7 +9,7 @@
 
 extern "C" {   // on-disk scene cache, host_api.cpp
 int b200host_scene_probe(const char* path, uint64_t* counts6);
-int b200host_scene_read(const char* path, void* const* blobs6);
+int b200host_scene_read_checked(const char* path, void* const* blobs6, const uint64_t* counts6);
 }
 
 namespace pth {
@@ -64,7 +64,7 @@ bool HeadlessEngine::load_scene_file(const std::string& path) {
     scene.spheres.resize(n[0]); scene.materials.resize(n[1]); scene.points.resize(n[2]);
     scene.triangles.resize(n[3]); scene.objects.resize(n[4]); scene.nodes.resize(n[5]);
     void* blobs[6] = {scene.spheres.data(), scene.materials.data(), scene.points.data(), scene.triangles.data(), scene.objects.data(), scene.nodes.data()};
-    if (int rc = b200host_scene_read(path.c_str(), blobs)) { error_ = path + ": scene file unreadable (code " + std::to_string(rc) + ")"; return false; }
+    if (int rc = b200host_scene_read_checked(path.c_str(), blobs, n)) { error_ = path + ": scene file unreadable (code " + std::to_string(rc) + ")"; return false; }
     return true;
 }
 

@@ -137,22 +137,29 @@ int b200host_scene_probe(const char* path, uint64_t* counts6) {
     }
     if (!rc) {
         std::memcpy(counts6, head + 16, 48);
-        size_t need = 128;
-        for (int i = 0; i < 6; ++i) need += pad64((size_t)counts6[i] * kRecord[i]);
-        std::fseek(f, 0, SEEK_END);
-        if ((size_t)std::ftell(f) < need) rc = 3;
+        uint64_t need = 128;
+        for (int i = 0; i < 6 && !rc; ++i) {
+            if (counts6[i] > ((uint64_t)1 << 40) / kRecord[i]) rc = 2;         // a byte size that cannot be a real scene (and cannot wrap below)
+            else need += pad64((size_t)counts6[i] * kRecord[i]);
+        }
+        long end = -1;
+        if (!rc && (std::fseek(f, 0, SEEK_END) != 0 || (end = std::ftell(f)) < 0 || (uint64_t)end < need)) rc = 3;
     }
     std::fclose(f);
     return rc;
 }
-// Fills six caller-allocated arrays (sizes from b200host_scene_probe): 0 ok, 1 cannot open, 3 truncated, 4 checksum mismatch
-int b200host_scene_read(const char* path, void* const* blobs6) {
+// Fills six caller-allocated arrays whose capacities (records) are `counts6` as b200host_scene_probe returned them; the
+// file's header is read again and must still say the same — a file replaced between the two calls is refused before
+// anything is written: 0 ok, 1 cannot open, 2 not a scene file, 3 truncated, 4 checksum mismatch, 5 counts changed
+int b200host_scene_read_checked(const char* path, void* const* blobs6, const uint64_t* counts6) {
     uint64_t counts[6];
     if (int rc = b200host_scene_probe(path, counts)) return rc;
+    if (counts6 && std::memcmp(counts, counts6, sizeof(counts)) != 0) return 5;
     FILE* f = std::fopen(path, "rb");
     if (!f) return 1;
     unsigned char head[128];
     int rc = std::fread(head, 1, 128, f) == 128 ? 0 : 3;
+    if (!rc && std::memcmp(head + 16, counts, 48) != 0) rc = 5;      // this open sees another file than the probe did
     uint64_t h = 14695981039346656037ull, want = 0;
     std::memcpy(&want, head + 88, 8);
     for (int i = 0; i < 6 && !rc; ++i) {
@@ -165,5 +172,6 @@ int b200host_scene_read(const char* path, void* const* blobs6) {
     if (!rc && h != want) rc = 4;
     return rc;
 }
+int b200host_scene_read(const char* path, void* const* blobs6) { return b200host_scene_read_checked(path, blobs6, nullptr); }
 
 }  // extern "C"

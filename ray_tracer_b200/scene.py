@@ -38,6 +38,7 @@ def _host():
         L.b200host_scene_write.argtypes = [C.c_char_p, vp, vp]
         L.b200host_scene_probe.argtypes = [C.c_char_p, vp]
         L.b200host_scene_read.argtypes = [C.c_char_p, vp]
+        L.b200host_scene_read_checked.argtypes = [C.c_char_p, vp, vp]
         L.b200host_set_bvh_builder.argtypes = [vp, vp, i32, u32]
         L.b200host_bvh_builder_stats.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
         _lib = L
@@ -177,14 +178,15 @@ def save_scene(path, blobs):
 
 def load_scene(path):
     """Reads a file written by save_scene -> blobs dict; raises SceneFileError on a foreign, truncated or corrupt file."""
-    why = {1: "cannot open", 2: "not a scene file of this version", 3: "truncated", 4: "checksum mismatch"}
+    why = {1: "cannot open", 2: "not a scene file of this version", 3: "truncated", 4: "checksum mismatch",
+           5: "replaced while it was being read"}
     counts = (C.c_uint64 * 6)()
     rc = _host().b200host_scene_probe(str(path).encode(), counts)
     if rc:
         raise SceneFileError("%s: %s" % (path, why[rc]))
     arrs = [np.zeros(int(c) * sz, np.uint8) for c, sz in zip(counts, BLOB_ITEMSIZE)]
     ptrs = (C.c_void_p * 6)(*[a.ctypes.data for a in arrs])
-    rc = _host().b200host_scene_read(str(path).encode(), ptrs)
+    rc = _host().b200host_scene_read_checked(str(path).encode(), ptrs, counts)
     if rc:
         raise SceneFileError("%s: %s" % (path, why[rc]))
     return dict(zip(BLOB_NAMES, arrs))

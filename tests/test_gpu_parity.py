@@ -479,6 +479,41 @@ def test_texture_extension(gpu):
     assert relrmse(got[..., :3], want[..., :3]) <= 1e-5
 
 
+def test_real_asset_with_its_texture_maps(gpu):
+    # A textured asset of the reference checkout — assets/bobadog/bobadog.obj + .mtl (map_Ka -> albedoIndex) + its PNG, and
+    # assets/test_plane.obj + .mtl (map_Kd, sampler 1) — built by the reference's own read_obj / read_mtl / build_bvh
+    # (tests/golden/make_textured_fixture.py). Texture semantics are this project's (the HEAD shader never samples).
+    import os
+    from conftest import GOLDEN
+    z = np.load(os.path.join(GOLDEN, "scene_bobadog_textured.npz"))
+    blobs = {k: np.ascontiguousarray(z[k]) for k in ob.BLOB_NAMES}
+    textures = {int(k.split("_")[1]): np.ascontiguousarray(z[k]) for k in z.files if k.startswith("texture_")}
+    mats = blobs["materials"].view(np.int32).reshape(-1, 16)
+    assert sorted(int(m[10]) for m in mats if m[10] >= 0) == sorted(textures)         # every map of the .mtl files has its texels
+    W, H = 160, 128
+    nobj = blobs["objects"].size // 80
+    pc = ob.default_push_constants(W, H, 0, nobj)
+    pc.view(np.float32)[39] = 1.0          # environment on (the asset brings no light)
+    sc = ob.OracleScene(blobs)
+    cp = _pass(gpu, blobs, W, H)
+    for slot, t in textures.items():
+        sc.set_texture(slot, t)
+        cp.upload_texture(slot, t)
+    with ob.math_mode(1):
+        plain, _ = sc.render_frames(pc, W, H, 0, 8)
+        sc.use_textures(True)
+        want, _ = sc.render_frames(pc, W, H, 0, 8)
+    assert relrmse(want[..., :3], plain[..., :3]) > 0.05
+    cp.set_option("textures", 1)
+    cp.render_frames(pc, 0, 8)
+    got = cp.read_accum()
+    _assert_explained(blobs, pc, W, H, range(8), got, want, textures=textures)
+    cp.clear()
+    cp.set_option("textures", 0)
+    cp.render_frames(pc, 0, 8)
+    _assert_explained(blobs, pc, W, H, range(8), cp.read_accum(), plain)
+
+
 def test_depth16_and_deep_roulette(gpu, bunny_blobs):
     # C5's bounce limit (16): Russian roulette is live for j > 5 (raytrace.comp:519-524), the queues run 17 bounces
     W, H = 200, 160

@@ -10,6 +10,7 @@ what integer math and the vendored GLM define is pinned here:
 """
 import json
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -269,3 +270,42 @@ def test_oracle_matches_reference_shader_golden():
         blobs = load_scene_fixture(fix)
         got = g.run(ob.OracleScene(blobs), kind, W, H, g.push_constants(W, H, blobs, over), extra)
         assert np.array_equal(np.ascontiguousarray(got).view(np.uint32), want[name].view(np.uint32)), name
+
+
+def test_textured_real_asset_fixture(have_reference):
+    """tests/golden/scene_bobadog_textured.npz: a real textured asset (bobadog.obj + .mtl + .png, test_plane.obj + .mtl).
+    With the reference tree present, the reference's own host code rebuilds exactly those buffers; everywhere, the
+    oracle's texture extension changes the picture where the mapped materials are seen."""
+    z = np.load(os.path.join(GOLDEN, "scene_bobadog_textured.npz"))
+    blobs = {k: np.ascontiguousarray(z[k]) for k in ob.BLOB_NAMES}
+    textures = {int(k.split("_")[1]): np.ascontiguousarray(z[k]) for k in z.files if k.startswith("texture_")}
+    assert len(textures) == 2 and all(t.shape == (256, 256, 4) for t in textures.values())
+    mats = blobs["materials"].view(np.int32).reshape(-1, 16)
+    assert sorted(int(m[10]) for m in mats if m[10] >= 0) == [0, 1]
+    if have_reference:
+        import ref_engine_binding as re_
+        if re_.available():
+            sys.path.insert(0, GOLDEN)
+            import make_textured_fixture as mk
+            r = re_.RefEngine()
+            o = ob.OracleBuilder()
+            o.push_default_materials()
+            for m in np.split(o.blobs()["materials"], 6):
+                r.add_material(m)
+            mk.build(r)
+            rb = r.blobs()
+            for k in ob.BLOB_NAMES:
+                if k != "spheres":
+                    assert np.array_equal(re_.defined_bytes(k, rb[k]), re_.defined_bytes(k, blobs[k])), k
+            assert [os.path.basename(p) for p in r.texture_paths()] == ["bobaxture2.png", "vase_dif.png"]
+    W, H = 64, 48
+    pc = ob.default_push_constants(W, H, 0, blobs["objects"].size // 80)
+    pc.view(np.float32)[39] = 1.0
+    sc = ob.OracleScene(blobs)
+    for slot, t in textures.items():
+        sc.set_texture(slot, t)
+    plain, _ = sc.render_frames(pc, W, H, 0, 2)
+    sc.use_textures(True)
+    mapped, _ = sc.render_frames(pc, W, H, 0, 2)
+    changed = (plain != mapped).any(axis=2).mean()
+    assert 0.2 < changed < 0.9
