@@ -11,6 +11,7 @@
 //   issue_ginst            warp instructions per second with FMA- and ALU-pipe instructions interleaved (the
 //                          schedulers' issue ceiling: 4 per SM per clock)
 //   alu_ginst / fmnmx / prmt / i2f / imad   single-pipe rates (warp instructions per second)
+//   ffma2_ginst / issue_ffma2_lop3_ginst   packed FP32 FMA (FFMA2, sm_100): its own rate, and interleaved with LOP3
 // Every figure is the best of 5 timed repetitions after a warm-up, CUDA events on the launching stream.
 #include <cuda_runtime.h>
 
@@ -123,6 +124,36 @@ __global__ void k_rate(uint32_t* out, int iters, uint32_t x, uint32_t y) {
     if (s == 0x12345678u) *out = s;
 }
 
+// packed FP32 FMA of sm_100 (fma.rn.f32x2 -> FFMA2: two FMAs per issued instruction). PAIRED = 0: 8 chains of FFMA2;
+// PAIRED = 1: FFMA2 and LOP3 interleaved (does an FFMA2 take one issue slot?)
+template <int WITH_LOP3>
+__global__ void k_ffma2(uint32_t* out, int iters, float x, float y, uint32_t ux, uint32_t uy) {
+    unsigned long long a[CH];
+    uint32_t b[CH];
+#pragma unroll
+    for (int c = 0; c < CH; ++c) {
+        float lo = threadIdx.x * 1e-3f + c, hi = lo + 0.5f;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(a[c]) : "f"(lo), "f"(hi));
+        b[c] = threadIdx.x + c * 977u;
+    }
+    unsigned long long xs, ys;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(xs) : "f"(x));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(ys) : "f"(y));
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                if (!WITH_LOP3 || !(c & 1)) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(a[c]) : "l"(xs), "l"(ys));
+                else asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(b[c]) : "r"(ux), "r"(uy));
+            }
+    }
+    uint32_t s = 0;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) s += (uint32_t)a[c] + (uint32_t)(a[c] >> 32) + b[c];
+    if (s == 0x12345678u) *out = s;
+}
+
 int main(int argc, char** argv) {
     int dev = 0;
     CK(cudaSetDevice(dev));
@@ -189,6 +220,10 @@ int main(int argc, char** argv) {
             double n = warpInst * (k == 1 ? 0.5 : 1.0);     // two max.f32 = one FMNMX3; the I2F figure counts conversions only
             printf(", \"%s\": %.1f", names[k], n / (t[k] * 1e-3) / 1e9);
         }
+        float t2 = best_ms([&] { k_ffma2<0><<<grid, block>>>(sink, iters, 1.0001f, 0.5f, 0x55u, 0x33u); });
+        float t3 = best_ms([&] { k_ffma2<1><<<grid, block>>>(sink, iters, 1.0001f, 0.5f, 0x55u, 0x33u); });
+        printf(", \"ffma2_ginst\": %.1f, \"ffma2_tflops\": %.2f, \"issue_ffma2_lop3_ginst\": %.1f", warpInst / (t2 * 1e-3) / 1e9,
+               warpInst * 32 * 4 / (t2 * 1e-3) / 1e12, warpInst / (t3 * 1e-3) / 1e9);
         printf(", \"issue_nominal_ginst\": %.1f", sms * 4.0 * clockKHz / 1e6);
         cudaFree(fout);
     }

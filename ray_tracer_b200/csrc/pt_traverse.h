@@ -123,6 +123,24 @@ PT_HD uint32_t pick_word(bool neg, uint32_t ifNeg, uint32_t ifPos) {
     return neg ? ifNeg : ifPos;
 #endif
 }
+#ifndef PT_NODE_FFMA2
+#define PT_NODE_FFMA2 0           /* node test: child planes two at a time through FFMA2 (device only). A/B on B200: 306.2 vs 311.7 Mpaths/s without —
+                                     an FFMA2 takes one issue slot (peaks_micro: FFMA2 + LOP3 interleaved 1108 G/s) but holds the FMA pipe for two
+                                     cycles and wants aligned register pairs: 24 fewer instructions per node visit, a few spills at the 72-register cap */
+#endif
+#if defined(__CUDA_ARCH__)
+// (a0, a1) * s + o with one packed FMA (fma.rn.f32x2, sm_100): each half rounds exactly like fma.rn.f32
+static __device__ __forceinline__ float2 fma2_bcast(float a0, float a1, float s, float o) {
+    unsigned long long a, ss, oo, r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(a0), "f"(a1));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(ss) : "f"(s));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(oo) : "f"(o));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(ss), "l"(oo));
+    float2 w;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(w.x), "=f"(w.y) : "l"(r));
+    return w;
+}
+#endif
 PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) {
     // entry planes: mantissa form Q * S + O (PRMT on the ALU pipe + FFMA); exit planes: q * s + o with q converted by
     // I2F (XU pipe + FFMA) — the ALU pipe is this kernel's busiest unit (ncu: 68 %), the XU pipe is nearly idle.
@@ -150,6 +168,26 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
         const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
         const uint32_t bitIndex4 = (meta4 ^ (br.octinv4 & innerMask4)) & 0x1f1f1f1fu;
         const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+#if defined(__CUDA_ARCH__) && PT_NODE_FFMA2
+        // two children per FFMA2 (sm_100 packed FP32 FMA: one issued instruction, the per-axis scale and offset broadcast):
+        // the same fma.rn per plane as the scalar form, half the FMA issue slots of a node visit (48 -> 24)
+#pragma unroll
+        for (int k = 0; k < 4; k += 2) {
+            const float2 t0x = PT_NODE_I2F_NEAR > 0 ? fma2_bcast(byte_to_float(nx[h], k), byte_to_float(nx[h], k + 1), sx, ofx)
+                                                    : fma2_bcast(byte_as_unit_float(nx[h], k), byte_as_unit_float(nx[h], k + 1), Sx, onx);
+            const float2 t0y = PT_NODE_I2F_NEAR > 1 ? fma2_bcast(byte_to_float(ny[h], k), byte_to_float(ny[h], k + 1), sy, ofy)
+                                                    : fma2_bcast(byte_as_unit_float(ny[h], k), byte_as_unit_float(ny[h], k + 1), Sy, ony);
+            const float2 t0z = PT_NODE_I2F_NEAR > 2 ? fma2_bcast(byte_to_float(nz[h], k), byte_to_float(nz[h], k + 1), sz, ofz)
+                                                    : fma2_bcast(byte_as_unit_float(nz[h], k), byte_as_unit_float(nz[h], k + 1), Sz, onz);
+            const float2 t1x = fma2_bcast(byte_to_float(fx[h], k), byte_to_float(fx[h], k + 1), sx, ofx);
+            const float2 t1y = fma2_bcast(byte_to_float(fy[h], k), byte_to_float(fy[h], k + 1), sy, ofy);
+            const float2 t1z = fma2_bcast(byte_to_float(fz[h], k), byte_to_float(fz[h], k + 1), sz, ofz);
+            const float tn0 = fmaxf(fmaxf(t0x.x, t0y.x), fmaxf(t0z.x, 0.f)), tf0 = fminf(fminf(t1x.x, t1y.x), fminf(t1z.x, tmax));
+            const float tn1 = fmaxf(fmaxf(t0x.y, t0y.y), fmaxf(t0z.y, 0.f)), tf1 = fminf(fminf(t1x.y, t1y.y), fminf(t1z.y, tmax));
+            if (tn0 <= tf0) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);
+            if (tn1 <= tf1) hits |= ((childBits4 >> (8 * (k + 1))) & 0xffu) << ((bitIndex4 >> (8 * (k + 1))) & 0xffu);
+        }
+#else
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             float t0x = PT_NODE_I2F_NEAR > 0 ? pt_fma(byte_to_float(nx[h], k), sx, ofx) : pt_fma(byte_as_unit_float(nx[h], k), Sx, onx);
@@ -162,6 +200,7 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
             if (tn <= tf) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);
         }
+#endif
     }
     return hits;
 }
