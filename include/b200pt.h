@@ -137,7 +137,7 @@ int b200pt_trace_batch_device(b200pt_ctx* ctx, const void* push_constants_208, c
 /* b200pt_trace_batch_device for callers that cannot allocate. No counterpart in the reference: added
  * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
  * Same inputs, same records, same kernels; the scratch memory (ray slots, hits, queues, counters) is a file-scope
- * static device array of B200PT_STATIC_MAX_RAYS * 56 + 256 bytes (3.5 MiB, held by every GPU that loads the library
+ * static device array of B200PT_STATIC_MAX_RAYS * 60 + 256 bytes (3.75 MiB, held by every GPU that loads the library
  * until exit) instead of buffers grown with cudaMalloc. The call makes no cudaMalloc / cudaFree and calls no allocating
  * library routine; the scene must have been uploaded before (that is where allocation happens). n above
  * B200PT_STATIC_MAX_RAYS is rejected with B200PT_ERR_ARG and a message. Asynchronous on the context's stream.

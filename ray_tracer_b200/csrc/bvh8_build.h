@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 #include <vector>
 
 #include "pt_bvh8.h"
@@ -159,8 +160,49 @@ struct Builder2 {
         nodes.reserve(2 * n + 1);
         if (const char* e = std::getenv("B200PT_BVH_LEAF")) maxLeaf = std::max(1, std::min(3, std::atoi(e)));
         if (const char* e = std::getenv("B200PT_BVH_CT")) travCost = (float)std::atof(e);
+        if (const char* e = std::getenv("B200PT_BVH_COLLAPSE")) dpOn = std::string(e) == "dp";
+        if (const char* e = std::getenv("B200PT_BVH_CN")) cNode = (float)std::atof(e);
     }
     float cen(uint32_t i, int a) const { return a == 0 ? cx[i] : (a == 1 ? cy[i] : cz[i]); }
+
+    // SAH-optimal collapse into 8-wide nodes (Ylitie, Karras, Laine 2017, section 3.1), leaves being the binary leaves:
+    //   C(n, 1) = A(n) * cNode + D(n, 8)                       n becomes a wide node over at most 8 children
+    //   D(n, j) = min over 0 < k < j of C(left, k) + C(right, j - k)
+    //   C(n, i) = min(D(n, i), C(n, i - 1))                    the subtree of n as at most i children of some wide node
+    // dpK[n][j] = the k of D(n, j); dpUse[n] bit i = C(n, i) takes D(n, i). Tuning: B200PT_BVH_COLLAPSE=dp, B200PT_BVH_CN.
+    std::vector<float> dpC; std::vector<uint8_t> dpK; std::vector<uint16_t> dpUse;
+    bool dpOn = false;
+    float cNode = 1.f, cTri = 1.f;
+    void collapse_dp() {
+        const size_t n = nodes.size();
+        dpC.assign(n * 9, 0.f); dpK.assign(n * 9, 0); dpUse.assign(n, 0);
+        for (size_t m = n; m-- > 0;) {                        // children have larger indices than their parent
+            const Node2& nd = nodes[m];
+            float* C = &dpC[m * 9];
+            const float A = box_half_area(nd.box);
+            if (nd.count) { for (int i = 1; i <= 8; ++i) C[i] = A * nd.count * cTri; continue; }
+            const float* L = &dpC[(size_t)nd.left * 9]; const float* R = &dpC[(size_t)nd.right * 9];
+            float D[9];
+            for (int j = 2; j <= 8; ++j) {
+                float best = 1e30f; int bk = 1;
+                for (int k = 1; k < j; ++k) { float c = L[k] + R[j - k]; if (c < best) { best = c; bk = k; } }
+                D[j] = best; dpK[m * 9 + j] = (uint8_t)bk;
+            }
+            C[1] = A * cNode + D[8];
+            for (int i = 2; i <= 8; ++i) {
+                if (D[i] < C[i - 1]) { C[i] = D[i]; dpUse[m] |= (uint16_t)(1u << i); }
+                else C[i] = C[i - 1];
+            }
+        }
+    }
+    void dp_gather(uint32_t m, int i, uint32_t* ch, int& nch) const {
+        const Node2& nd = nodes[m];
+        if (nd.count) { ch[nch++] = m; return; }
+        while (i > 1 && !(dpUse[m] & (1u << i))) i--;
+        if (i == 1) { ch[nch++] = m; return; }
+        const int k = dpK[(size_t)m * 9 + i];
+        dp_gather(nd.left, k, ch, nch); dp_gather(nd.right, i - k, ch, nch);
+    }
 
     uint32_t build(uint32_t first, uint32_t count) {
         uint32_t me = (uint32_t)nodes.size();
@@ -251,8 +293,9 @@ inline void bvh8_emit(const b8::Builder2& B, const std::vector<b8::Instance>& in
     uint32_t ch[8]; int nch = 0;
     const Node2& root = B.nodes[n2];
     if (root.count) { ch[nch++] = n2; }
+    else if (B.dpOn) { const int k = B.dpK[(size_t)n2 * 9 + 8]; B.dp_gather(root.left, k, ch, nch); B.dp_gather(root.right, 8 - k, ch, nch); }
     else { ch[nch++] = root.left; ch[nch++] = root.right; }
-    while (nch < 8) {
+    while (!B.dpOn && nch < 8) {
         int best = -1; float bestA = -1.f;
         for (int i = 0; i < nch; ++i) {
             const Node2& c = B.nodes[ch[i]];
@@ -356,6 +399,7 @@ inline void bvh8_build(const std::vector<b8::Box>& boxes, const std::vector<b8::
     auto t0 = std::chrono::steady_clock::now();
     b8::Builder2 B(boxes);
     uint32_t root = B.build(0, (uint32_t)boxes.size());
+    if (B.dpOn) B.collapse_dp();
     auto t1 = std::chrono::steady_clock::now();
     out.prims.reserve(boxes.size()); out.shade.reserve(boxes.size()); out.uvs.reserve(boxes.size());
     bvh8_emit(B, inst, primOf, shadeOf, uvOf, root, 0, 1, out);

@@ -13,6 +13,7 @@ namespace pt {
 #define PT_HIT_SPHERE 0x80000000u
 #define PT_HIT_FRONT 0x40000000u
 #define PT_HIT_IDMASK 0x3fffffffu
+#define PT_HIT_CONTESTED 0x20000000u   /* only between k_extend and k_verify_extend / k_exact_extend (wavefront.cu): the ray goes to the reference-order re-trace; record indices stay below 2^29 */
 
 struct Hit {
     float dst;
@@ -263,13 +264,15 @@ PT_HD PrimRecord load_prim(const PrimRecord* prims, uint32_t i) {
 //     that contains h with the margin. Axes on which the leaf is flat (axis-aligned triangles) are
 //     exempt from the margin: there tMin == tMax is the plane distance itself and rounding is
 //     monotone in the box coordinate.
-PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, const ObjRayCache& c, float dst) {
+// quick accept: true = reachable for certain; false = the leaf -> root walk has to decide
+PT_HD bool ref_reachable_quick(const PrimRecord& p, const ObjRayCache& c, float dst) {
     const v3 h = c.r.o + c.r.d * dst;
     const float m = 2e-5f * (fmaxf(fmaxf(fabsf(h.x), fabsf(h.y)), fabsf(h.z)) + fmaxf(fmaxf(fabsf(c.r.o.x), fabsf(c.r.o.y)), fabsf(c.r.o.z))) + 1e-30f;
     const v3 dh = h - c.r.o;
     const bool farEnough = fmaxf(fmaxf(fabsf(dh.x), fabsf(dh.y)), fabsf(dh.z)) > m;
     const bool flatX = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_X) != 0, flatY = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Y) != 0,
                flatZ = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Z) != 0;
+    PT_DEBUG_COUNT(2);
     if (p.triIndexFlags & PT_PRIM_LEAF_IS_ROOT) return true;
     if (farEnough) {
         const float lx = p.p0x + fminf(fminf(p.e1x, p.e2x), 0.f), hx = p.p0x + fmaxf(fmaxf(p.e1x, p.e2x), 0.f);
@@ -279,7 +282,7 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
         const bool inY = flatY || (h.y >= ly + m && h.y <= hy - m);
         const bool inZ = flatZ || (h.z >= lz + m && h.z <= hz - m);
         const int nOut = (inX ? 0 : 1) + (inY ? 0 : 1) + (inZ ? 0 : 1);
-        if (nOut == 0) return true;
+        if (nOut == 0) { PT_DEBUG_COUNT(3); return true; }
         // (b) needs real margins on the other two axes: not when the leaf is flat on one of them (its slab interval there
         // is the single value of the plane distance, and a hit point m/16 outside the triangle's box on axis a means the
         // ray has left the zero-thickness box: found on the C4 stand-in, frame 402 pixel (1740, 780), a trim-box face)
@@ -290,13 +293,24 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
             if (!inX) ok = h.x >= lx - m16 && h.x <= hx + m16 && ((lx == hx && ax >= 1e-30f) || 4.f * ax >= fmaxf(ay, az));
             else if (!inY) ok = h.y >= ly - m16 && h.y <= hy + m16 && ((ly == hy && ay >= 1e-30f) || 4.f * ay >= fmaxf(ax, az));
             else ok = h.z >= lz - m16 && h.z <= hz + m16 && ((lz == hz && az >= 1e-30f) || 4.f * az >= fmaxf(ax, ay));
-            if (ok) return true;
+            if (ok) { PT_DEBUG_COUNT(4); return true; }
         }
     }
+    return false;
+}
+// the walk: the reference's slab tests leaf -> root
+PT_HD bool ref_reachable_walk(const UpNode* __restrict__ up, const PrimRecord& p, const ObjRayCache& c, float dst) {
+    const v3 h = c.r.o + c.r.d * dst;
+    const float m = 2e-5f * (fmaxf(fmaxf(fabsf(h.x), fabsf(h.y)), fabsf(h.z)) + fmaxf(fmaxf(fabsf(c.r.o.x), fabsf(c.r.o.y)), fabsf(c.r.o.z))) + 1e-30f;
+    const v3 dh = h - c.r.o;
+    const bool farEnough = fmaxf(fmaxf(fabsf(dh.x), fabsf(dh.y)), fabsf(dh.z)) > m;
+    const bool flatX = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_X) != 0, flatY = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Y) != 0,
+               flatZ = (p.triIndexFlags & PT_PRIM_LEAF_FLAT_Z) != 0;
+    PT_DEBUG_COUNT(5);
     const v3 inv = mk3(1.f / c.r.d.x, 1.f / c.r.d.y, 1.f / c.r.d.z);   // raytrace.comp:294
     UpNode n = up[p.leafNode];
     for (;;) {
-        if (box_test_ref(mk3(n.minX, n.minY, n.minZ), mk3(n.maxX, n.maxY, n.maxZ), c.r.o, inv) == PT_FAR) return false;
+        if (box_test_ref(mk3(n.minX, n.minY, n.minZ), mk3(n.maxX, n.maxY, n.maxZ), c.r.o, inv) == PT_FAR) { PT_DEBUG_COUNT(6); return false; }
         bool inX = flatX || (h.x >= n.minX + m && h.x <= n.maxX - m);
         bool inY = flatY || (h.y >= n.minY + m && h.y <= n.maxY - m);
         bool inZ = flatZ || (h.z >= n.minZ + m && h.z <= n.maxZ - m);
@@ -304,6 +318,9 @@ PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, con
         n = up[n.parent];
         if (n.parent == 0xffffffffu) return true;
     }
+}
+PT_HD bool ref_reachable(const UpNode* __restrict__ up, const PrimRecord& p, const ObjRayCache& c, float dst) {
+    return ref_reachable_quick(p, c, dst) || ref_reachable_walk(up, p, c, dst);
 }
 
 PT_HD TriEdges prim_edges(const PrimRecord& p) {
@@ -436,6 +453,12 @@ PT_HD void trav_node_step(const Bvh8View& bvh, Trav& t, Stack& stack, float tmax
 // reference's `hitInfo.dst < closestHit.dst`). `key` is the position of the current best hit in the
 // reference's loop order (sphere i -> i, object o -> nSpheres + o; 0xffffffff for none): the
 // reference keeps the FIRST of equal-distance hits.
+// REACH = false (the persistent k_extend): candidates are accepted WITHOUT the reachability confirmation — ref_reachable ran
+// at 2-3 lanes per warp and was 15 % of that kernel's instructions — and the ray's final hit is confirmed afterwards by
+// k_verify_extend at full lane count; a ray whose final hit fails goes to the reference-order re-trace, which is right by
+// construction. Until then an unreachable candidate can only shadow farther ones, and every candidate within the contest
+// window of the final hit is still seen (nodes are culled against best + window), flagged contested whether reachable or not.
+template <bool REACH = true>
 PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
                                  float extent, Trav& t, Hit& hit, uint32_t& key, float* bestInvCos = nullptr) {
     int k = highest_bit(t.tBits);
@@ -452,7 +475,7 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
 #if PT_CONTEST
     // only a hit that wins, or one that comes within tau of the best, can change the answer
     const bool near = fabsf(dst - hit.dst) <= contest_window(fmaxf(dst, hit.dst), extent) && hit.id != PT_HIT_MISS;
-    if (!(wins || near) || !ref_reachable(up, p, t.oc, dst)) return;
+    if (!(wins || near) || (REACH && !ref_reachable(up, p, t.oc, dst))) return;
     if (near && (hit.id & ~PT_HIT_FRONT) != pi) t.br.octinv4 |= PT_TRAV_CONTESTED;
     if (wins) {
         const float g = inv_cos_incidence(te, tr, invD0);
@@ -460,7 +483,7 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
         if (bestInvCos) *bestInvCos = g;
     }
 #else
-    if (!wins || !ref_reachable(up, p, t.oc, dst)) return;
+    if (!wins || (REACH && !ref_reachable(up, p, t.oc, dst))) return;
 #endif
     if (wins) {
         hit.dst = dst; hit.u = u; hit.v = v;
@@ -475,11 +498,15 @@ PT_HD void trav_tri_step_closest(const Bvh8View& bvh, const Xform* xforms, const
 #define PT_OCCL_NO 0
 #define PT_OCCL_YES 1
 #define PT_OCCL_CONTESTED 2
+// REACH = false (the persistent k_occlude): as in trav_tri_step_closest<false>, the occluder is taken without the
+// reachability confirmation and reported through `occluder` / `occDst`; k_verify_occluded confirms it afterwards.
+template <bool REACH = true>
 PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const UpNode* up, uint32_t nSpheres, uint32_t objectCount,
-                                 float extent, float windowScale, Trav& t, float tE, uint32_t keyE) {
+                                 float extent, float windowScale, Trav& t, float tE, uint32_t keyE, uint32_t* occluder = nullptr, float* occDst = nullptr) {
     int k = highest_bit(t.tBits);
     t.tBits &= ~(1u << k);
-    const PrimRecord p = load_prim(bvh.prims, t.tBase + (uint32_t)k);
+    const uint32_t pi = t.tBase + (uint32_t)k;
+    const PrimRecord p = load_prim(bvh.prims, pi);
     if (p.objectIndex >= objectCount || (p.triIndexFlags & PT_PRIM_EMISSIVE)) return PT_OCCL_NO;
     const Ray& tr = object_ray(t.oc, xforms, p.xformId, t.ray);
     float dst, u, v, invD0; bool front;
@@ -488,11 +515,12 @@ PT_HD int trav_tri_step_occluded(const Bvh8View& bvh, const Xform* xforms, const
     const bool closer = dst < tE || (dst == tE && nSpheres + p.objectIndex < keyE);
     const float gap = fabsf(dst - tE), window = contest_window(fmaxf(dst, tE), extent);
     const bool near = gap <= window * windowScale;          // windowScale >= 1: the emissive hit's own error grows with its 1 / cos
-    if (!(closer || near) || !ref_reachable(up, p, t.oc, dst)) return PT_OCCL_NO;
+    if (!(closer || near) || (REACH && !ref_reachable(up, p, t.oc, dst))) return PT_OCCL_NO;
 #if PT_CONTEST
     // an occluder far in front of tE decides unless its own distance error (which grows with 1 / cos) reaches back to tE
     if (near || gap <= window * inv_cos_incidence(te, tr, invD0) * (1.f / 16.f)) return PT_OCCL_CONTESTED;
 #endif
+    if (closer && occluder) { *occluder = pi; *occDst = dst; }
     return closer ? PT_OCCL_YES : PT_OCCL_NO;
 }
 

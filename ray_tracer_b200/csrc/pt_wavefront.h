@@ -114,7 +114,8 @@ PT_HD Hit wide_closest_hit(const WideScene& sc, const Ray& ray, uint32_t sphereC
 // buffers (pt_reftrace.h), expressed as the wavefront's Hit (record index of the triangle in the wide layout).
 PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl::RayTracerData& td, const Ray& ray, float wideDst) {
     // wideDst: the distance the wide traversal found (the smallest candidate): phantom bound of the re-trace (pt_reftrace.h)
-    const RefHit r = ref_closest_hit(ref, td, ray, nullptr, wideDst + 3.f * contest_window(wideDst, sc.extent));
+    // wideDst >= PT_FAR: the wide traversal's own hit was not reachable in the reference's BVH2 (k_verify_extend): no bound
+    const RefHit r = ref_closest_hit(ref, td, ray, nullptr, wideDst >= PT_FAR ? PT_FAR : wideDst + 3.f * contest_window(wideDst, sc.extent));
     Hit h; h.dst = r.dst; h.u = 0.f; h.v = 0.f; h.id = PT_HIT_MISS;
     if (r.kind == 1u) h.id = PT_HIT_SPHERE | (r.front ? PT_HIT_FRONT : 0u) | r.triHitIndex;
     else if (r.kind == 2u) {
@@ -122,6 +123,29 @@ PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl:
         h.u = r.u; h.v = r.v;
     }
     return h;
+}
+// Would the reference have tested the triangle of this (optimistically accepted, pt_traverse.h) closest hit? Spheres and
+// misses: nothing to confirm.
+PT_HD bool hit_reachable(const WideScene& sc, const Ray& ray, const Hit& h) {
+    if (h.id == PT_HIT_MISS || (h.id & PT_HIT_SPHERE)) return true;
+    const PrimRecord p = load_prim(sc.all.prims, h.id & PT_HIT_IDMASK & ~PT_HIT_CONTESTED);
+    ObjRayCache oc; oc.xform = 0xffffffffu;
+    object_ray(oc, sc.xforms, p.xformId, ray);
+    return ref_reachable(sc.up, p, oc, h.dst);
+}
+// the two halves of it, for a kernel pair: the quick accept at full lane count, the rare walk from a compacted queue
+PT_HD bool hit_reachable_quick(const WideScene& sc, const Ray& ray, const Hit& h) {
+    if (h.id == PT_HIT_MISS || (h.id & PT_HIT_SPHERE)) return true;
+    const PrimRecord p = load_prim(sc.all.prims, h.id & PT_HIT_IDMASK & ~PT_HIT_CONTESTED);
+    ObjRayCache oc; oc.xform = 0xffffffffu;
+    object_ray(oc, sc.xforms, p.xformId, ray);
+    return ref_reachable_quick(p, oc, h.dst);
+}
+PT_HD bool hit_reachable_walk(const WideScene& sc, const Ray& ray, const Hit& h) {
+    const PrimRecord p = load_prim(sc.all.prims, h.id & PT_HIT_IDMASK & ~PT_HIT_CONTESTED);
+    ObjRayCache oc; oc.xform = 0xffffffffu;
+    object_ray(oc, sc.xforms, p.xformId, ray);
+    return ref_reachable_walk(sc.up, p, oc, h.dst);
 }
 PT_HD void stage_extend(const WfParams& P, const WideScene& sc, const RefScene& ref, const PathArrays& A, uint32_t p) {
     Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
@@ -420,6 +444,23 @@ PT_HD void connect_exact(const RefScene& ref, const WideScene& sc, const ptl::Ra
 }
 PT_HD void connect_job_occluded(const PathArrays& A, uint32_t p) {
     reinterpret_cast<float*>(&A.qE[p])[0] = PT_NO_EMISSIVE;
+}
+// k_occlude<*, true>: occluded by a triangle that is not yet confirmed reachable (pt_traverse.h) — the record index and its
+// distance ride in qE.y / qE.z (dead once qE.x says "no emissive hit") until k_verify_occluded has looked at them
+PT_HD void connect_job_occluded_by(const PathArrays& A, uint32_t p, uint32_t prim, float dst) {
+    float4 e = A.qE[p];
+    e.x = PT_NO_EMISSIVE; e.y = as_float(prim); e.z = dst;
+    A.qE[p] = e;
+}
+// -> false when the reference would not have tested that occluder: the query has to be answered by connect_exact
+PT_HD bool connect_job_occluder_reachable(const WideScene& sc, const PathArrays& A, uint32_t p) {
+    const float4 e = A.qE[p];
+    if (e.x >= 0.f) return true;                       // not occluded (or contested: k_exact_nee answers)
+    const PrimRecord pr = load_prim(sc.all.prims, as_uint(e.y));
+    Ray r; r.o = xyz(A.qO[p]); r.d = xyz(A.qL[p]);
+    ObjRayCache oc; oc.xform = 0xffffffffu;
+    object_ray(oc, sc.xforms, pr.xformId, r);
+    return ref_reachable(sc.up, pr, oc, e.z);
 }
 // The light-sample ray of path p: when its closest hit is the emissive one at distance qE.x (found by prep, not occluded)
 // — pdf, power-heuristic weight and direct light of diffuseBRDF (raytrace.comp:447-460); otherwise nothing (see above).

@@ -30,6 +30,7 @@ struct WavefrontState {
     // path state
     DeviceBuffer dPaths[9];
     DeviceBuffer dHit, dQueue[2], dShadowQ, dJobQ, dCounts, dRayCounters, dSampleSum;
+    DeviceBuffer dWalkQ;               // rays whose final hit needs the leaf -> root reachability walk (k_verify_walk)
     DeviceBuffer dExactQ, dExactNeeQ;  // contested rays / light-sample queries: re-traced in the reference's order (pt_traverse.h)
     DeviceBuffer dPrimOf, dInstBase, dTriFirst;
     PathArrays arrays{};
@@ -46,6 +47,7 @@ struct WavefrontState {
     int gridOcclude = 0;
     int gridShade = 0, gridPrep = 0, gridFinish = 0;
     int gridExtend = 0;               // resident blocks of the persistent kernels (occupancy x SMs)
+    int gridVerify = 0;               // one wave of k_verify_extend
     // per-stage device time: an event between consecutive launches (generate, extend, shade, connect, accumulate)
     std::vector<cudaEvent_t> events;
     std::vector<int> eventStage;      // stage of the launch that FOLLOWS event i (-1: batch end)
@@ -96,7 +98,7 @@ void wavefront_stage_times(b200pt_ctx* c, double* ms8, uint64_t* launches8, bool
 }
 
 #define WF_THREADS 128
-#define WF_COUNT_ARRAYS 9        /* per-bounce device counters: qCount sCount workE workO oCount primaryCount mCount xCount xnCount */
+#define WF_COUNT_ARRAYS 10       /* per-bounce device counters: qCount sCount workE workO oCount primaryCount mCount xCount xnCount wCount */
 #define WF_RAY_COUNTERS 16      /* device-side u64 counters: k_fold's five, then work counters [8..11] (option count_work) */
 
 static __device__ __forceinline__ uint32_t warp_push(uint32_t* counter, bool pred) {
@@ -205,6 +207,9 @@ static __device__ __forceinline__ unsigned warp_votes(bool busy, bool hasTri, bo
 #ifndef PT_EXTEND_MIN_BLOCKS
 #define PT_EXTEND_MIN_BLOCKS 7     /* 72 registers: 7 blocks x 4 warps per SM (A/B: 6 -> 80 regs, 8 -> 64 regs + spills) */
 #endif
+#ifndef PT_EXTEND_MIN_BLOCKS_OPT
+#define PT_EXTEND_MIN_BLOCKS_OPT 8 /* the kernels without the in-loop reachability confirmation fit 64 registers (k_extend: no spill, k_occlude: 20 bytes) */
+#endif
 // COUNT (option "count_work"): node visits and triangle tests of the launch are added to work[0], work[1] — the
 // kernel's own algorithmic work in the WIDE layout (80 B per node visit, 64 B per triangle test), which the bench's
 // roofline divides by the measured L2 gather bandwidth.
@@ -213,8 +218,12 @@ static __device__ __forceinline__ void flush_work(unsigned long long* work, uint
     tris = __reduce_add_sync(0xffffffffu, tris);
     if ((threadIdx.x & 31u) == 0u) { atomicAdd(work, (unsigned long long)nodes); atomicAdd(work + 1, (unsigned long long)tris); }
 }
-template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+// OPT (option exact_order = 1, the default): candidate hits are accepted without the reachability confirmation
+// (pt_traverse.h: trav_tri_step_closest<false>), a contested ray is only MARKED (PT_HIT_CONTESTED in the stored id), and
+// k_verify_extend confirms every ray's final hit at full lane count and queues the rays for k_exact_extend. Without OPT
+// (exact_order = 0: no re-trace to fall back on) the confirmation stays inside the loop.
+template <bool COUNT, bool OPT>
+__global__ void __launch_bounds__(WF_THREADS, OPT ? PT_EXTEND_MIN_BLOCKS_OPT : PT_EXTEND_MIN_BLOCKS) k_extend(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                        const uint32_t* __restrict__ queue, const uint32_t* __restrict__ qCount,
                                                        uint32_t* workCounter, Hit* __restrict__ hitOut, uint32_t* exactQueue, uint32_t* exactCount,
                                                        unsigned long long* work) {
@@ -232,8 +241,13 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
     for (;;) {
         // lanes with nothing in hand take the next group from their stack, or finish
         if (busy && !trav_has_node(t) && !trav_has_tri(t) && !trav_pop(t, stack)) {
-            hitOut[p] = hit;
-            if (trav_contested(t)) exactQueue[atomicAdd(exactCount, 1u)] = p;      // rare (coincident surfaces): k_exact_extend overwrites the hit
+            if (OPT) {
+                if (trav_contested(t)) hit.id |= PT_HIT_CONTESTED;                  // contested implies a hit (pt_traverse.h)
+                hitOut[p] = hit;
+            } else {
+                hitOut[p] = hit;
+                if (trav_contested(t)) exactQueue[atomicAdd(exactCount, 1u)] = p;  // rare (coincident surfaces): k_exact_extend overwrites the hit
+            }
             busy = false;
         }
         const bool hasTri = busy && trav_has_tri(t);
@@ -256,7 +270,7 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
             if (hasTri) {
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP && trav_has_tri(t); ++r) {
-                    trav_tri_step_closest(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, t, hit, key);
+                    trav_tri_step_closest<!OPT>(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, t, hit, key);
                     if (COUNT) cntTri++;
                 }
             }
@@ -269,6 +283,53 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_extend(con
         }
     }
     if (COUNT) flush_work(work, cntNode, cntTri);
+}
+
+// After k_extend<*, true>: every ray's final hit, at full lane count. A triangle hit that the reference would not have
+// tested (pt_traverse.h: ref_reachable) and every ray marked contested go to k_exact_extend; for the former the stored
+// distance becomes PT_FAR, which tells the re-trace not to use it as its starting bound. Two kernels: the quick accept
+// for every ray here, the leaf -> root walk (1 % of the hits) from a compacted queue in k_verify_walk — inside one
+// kernel a warp with one walking lane waited for it (10 of 32 lanes per instruction, 7.2 ms per step instead of ~3).
+__global__ void __launch_bounds__(WF_THREADS) k_verify_extend(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ queue,
+                                                              const uint32_t* __restrict__ qCount, const Hit* __restrict__ hit, uint32_t* exactQueue,
+                                                              uint32_t* exactCount, uint32_t* walkQueue, uint32_t* walkCount) {
+    const uint32_t n = *qCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = queue[i];
+        const Hit h = hit[p];
+        if (h.id == PT_HIT_MISS) continue;
+        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+        if (!hit_reachable_quick(sc, r, h)) walkQueue[atomicAdd(walkCount, 1u)] = p;
+        else if (h.id & PT_HIT_CONTESTED) exactQueue[atomicAdd(exactCount, 1u)] = p;
+    }
+}
+__global__ void __launch_bounds__(WF_THREADS) k_verify_walk(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ walkQueue,
+                                                            const uint32_t* __restrict__ walkCount, Hit* hit, uint32_t* exactQueue, uint32_t* exactCount) {
+    const uint32_t n = *walkCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = walkQueue[i];
+        const Hit h = hit[p];
+        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+        const bool ok = hit_reachable_walk(sc, r, h);
+        if (!ok) hit[p].dst = PT_FAR;
+        if (!ok || (h.id & PT_HIT_CONTESTED)) exactQueue[atomicAdd(exactCount, 1u)] = p;
+    }
+}
+static void launch_verify(b200pt_ctx* c, int grid, int smCount, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
+                          const uint32_t* count, uint32_t* exactQ, uint32_t* xCount, uint32_t* walkQ, uint32_t* wCount) {
+    k_verify_extend<<<grid, WF_THREADS, 0, st>>>(sc, A, queue, count, A.hit, exactQ, xCount, walkQ, wCount);
+    k_verify_walk<<<smCount * 4, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);
+    c->counters[0] += 2;
+}
+static void launch_extend(b200pt_ctx* c, int grid, const WfParams& P, const WideScene& sc, const PathArrays& A, const uint32_t* queue, const uint32_t* count,
+                          uint32_t* workCounter, uint32_t* exactQ, uint32_t* xCount, unsigned long long* workCnt) {
+    if (c->exactOrder) {
+        if (c->countWork) k_extend<true, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        else k_extend<false, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
+    } else {
+        if (c->countWork) k_extend<true, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        else k_extend<false, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
+    }
 }
 
 // Block-aggregated queue append: ONE global atomic per block per round instead of one per warp. With 16 M paths per
@@ -371,8 +432,8 @@ __global__ void __launch_bounds__(WF_THREADS, PT_PREP_MIN_BLOCKS) k_connect_prep
 }
 
 // connect, part 2: bounded any-hit walks of the full BVH, same warp scheduling as k_extend
-template <bool COUNT>
-__global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
+template <bool COUNT, bool OPT>
+__global__ void __launch_bounds__(WF_THREADS, OPT ? PT_EXTEND_MIN_BLOCKS_OPT : PT_EXTEND_MIN_BLOCKS) k_occlude(const __grid_constant__ WfParams P, const __grid_constant__ WideScene sc, PathArrays A,
                                                         const uint32_t* __restrict__ jobQueue, const uint32_t* __restrict__ jobCount,
                                                         uint32_t* workCounter, uint32_t* exactQueue, uint32_t* exactCount, unsigned long long* work) {
     uint32_t cntNode = 0, cntTri = 0;
@@ -408,9 +469,10 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
 #pragma unroll 1
                 for (int r = 0; r < PT_TRI_PER_STEP_OCCL && trav_has_tri(t); ++r) {
                     if (COUNT) cntTri++;
-                    const int o = trav_tri_step_occluded(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, ws, t, tE, keyE);
+                    uint32_t occluder = 0; float occDst = 0.f;
+                    const int o = trav_tri_step_occluded<!OPT>(sc.all, sc.xforms, sc.up, sc.nSpheres, objectCount, sc.extent, ws, t, tE, keyE, &occluder, &occDst);
                     if (o != PT_OCCL_NO) {
-                        if (o == PT_OCCL_YES) connect_job_occluded(A, job);
+                        if (o == PT_OCCL_YES) { if (OPT) connect_job_occluded_by(A, job, occluder, occDst); else connect_job_occluded(A, job); }
                         else exactQueue[atomicAdd(exactCount, 1u)] = job;      // contested: k_exact_nee answers in the reference's order
                         busy = false;
                         break;
@@ -426,6 +488,17 @@ __global__ void __launch_bounds__(WF_THREADS, PT_EXTEND_MIN_BLOCKS) k_occlude(co
         }
     }
     if (COUNT) flush_work(work, cntNode, cntTri);
+}
+
+// After k_occlude<*, true>: the occluders found, at full lane count; a query whose occluder the reference would not have tested
+// is answered by k_exact_nee instead (qE.x < 0 there means: no bound for the search).
+__global__ void __launch_bounds__(WF_THREADS) k_verify_occluded(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ jobQueue,
+                                                                const uint32_t* __restrict__ jobCount, uint32_t* exactQueue, uint32_t* exactCount) {
+    const uint32_t n = *jobCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t job = jobQueue[i];
+        if (!connect_job_occluder_reachable(sc, A, job)) exactQueue[atomicAdd(exactCount, 1u)] = job;
+    }
 }
 
 // connect, part 3: pdf, power-heuristic weight, direct light of the paths whose light-sample ray reached the light (the
@@ -711,6 +784,7 @@ int wavefront_build_scene(b200pt_ctx* c, int changed) {
     WCU(wf_upload(c, w->dXforms, host.xforms));
     WCU(wf_upload(c, w->dObjXform, host.objXform));
     WCU(wf_upload(c, w->dUp, host.up));
+    if (nPrimsAll >= PT_HIT_CONTESTED) { c->error = "wavefront: more than 2^29 instance triangles"; return 1; }      // hit ids keep bit 29 for PT_HIT_CONTESTED
     // (object, triangle) -> record index, for hits found by the reference-order re-trace of contested rays
     WCU(wf_upload(c, w->dInstBase, host.instBase));
     WCU(wf_upload(c, w->dTriFirst, host.triFirst));
@@ -761,7 +835,7 @@ void wavefront_destroy(b200pt_ctx* c) {
     wf_release_tree(w);
     DeviceBuffer* all[] = {&w->dNodes, &w->dPrims, &w->dShade, &w->dUv, &w->dNodesE, &w->dPrimsE, &w->dShadeE, &w->dXforms, &w->dObjXform, &w->dUp,
                            &w->dHit, &w->dQueue[0], &w->dQueue[1], &w->dShadowQ, &w->dJobQ, &w->dCounts, &w->dRayCounters, &w->dSampleSum,
-                           &w->dExactQ, &w->dExactNeeQ, &w->dPrimOf, &w->dInstBase, &w->dTriFirst};
+                           &w->dExactQ, &w->dExactNeeQ, &w->dWalkQ, &w->dPrimOf, &w->dInstBase, &w->dTriFirst};
     for (DeviceBuffer* b : all) wf_free(*b);
     for (auto& b : w->dPaths) wf_free(b);
     for (cudaEvent_t e : w->events) cudaEventDestroy(e);
@@ -786,6 +860,7 @@ static int wf_reserve(b200pt_ctx* c, size_t paths, uint32_t bounces) {
         WCU(wf_resize(w->dJobQ, paths * 8));
         WCU(wf_resize(w->dExactQ, paths * 4));
         WCU(wf_resize(w->dExactNeeQ, paths * 4));
+        WCU(wf_resize(w->dWalkQ, paths * 4));
         w->capacity = paths;
         PathArrays& A = w->arrays;
         A.rayO = (float4*)w->dPaths[0].p; A.rayD = (float4*)w->dPaths[1].p; A.atten = (float4*)w->dPaths[2].p;
@@ -853,17 +928,21 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* mCount = primaryCount + w->countSlots;
     uint32_t* xCount = mCount + w->countSlots;          // contested extension rays per bounce
     uint32_t* xnCount = xCount + w->countSlots;         // contested light-sample queries per bounce
+    uint32_t* wCount = xnCount + w->countSlots;         // hits that need the reachability walk, per bounce
+    uint32_t* walkQ = (uint32_t*)w->dWalkQ.p;
     unsigned long long* exactTotals = (unsigned long long*)w->dRayCounters.p + 12;      // [12] extension rays, [13] light-sample queries re-traced exactly
     const int gridExact = w->smCount * 4;
     if (!w->gridOcclude) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude<false>, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude<false, true>, WF_THREADS, 0));
         w->gridOcclude = std::max(1, perSm) * w->smCount;
     }
     if (!w->gridExtend) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false, true>, WF_THREADS, 0));
         w->gridExtend = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_verify_extend, WF_THREADS, 0));
+        w->gridVerify = std::max(1, perSm) * w->smCount;
     }
     for (uint32_t done = 0; done < n; done += slots) {
         P.nSlots = std::min(slots, n - done);
@@ -907,10 +986,12 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             unsigned long long* workCnt = (unsigned long long*)w->dRayCounters.p + 8;     // [8,9] extend, [10,11] occlude
             uint32_t* exactQ = (uint32_t*)w->dExactQ.p;
             uint32_t* exactNeeQ = (uint32_t*)w->dExactNeeQ.p;
-            if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, workCnt);
-            else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, w->arrays.hit, exactQ, xCount, nullptr);
+            launch_extend(c, w->gridExtend, P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, exactQ, xCount, workCnt);
             wf_mark(c, ST_EXACT);
-            if (c->exactOrder) k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
+            if (c->exactOrder) {
+                launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, exactQ, xCount, walkQ, wCount);
+                k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
+            }
             for (uint32_t j = 0; j < nB; ++j) {
                 wf_mark(c, ST_SHADE);
                 k_shade<<<gridShade, SHADE_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qa, qCount + j, qb, qCount + j + 1,
@@ -923,24 +1004,36 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                         cs = w->sideStream;
                     }
                     wf_mark(c, ST_EXTEND);
-                    if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, workCnt);
-                    else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, w->arrays.hit, exactQ, xCount + j + 1, nullptr);
+                    launch_extend(c, w->gridExtend, P, w->scene, w->arrays, qb, qCount + j + 1, workE + j + 1, exactQ, xCount + j + 1, workCnt);
                     wf_mark(c, ST_EXACT);
                     if (exactAside) {
                         WCU(cudaEventRecord(w->evX0, c->stream));
                         WCU(cudaStreamWaitEvent(w->exactStream, w->evX0, 0));
                     }
-                    if (c->exactOrder) k_exact_extend<<<gridExact, WF_THREADS, 0, exactAside ? w->exactStream : c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
+                    if (c->exactOrder) {
+                        cudaStream_t xs = exactAside ? w->exactStream : c->stream;
+                        launch_verify(c, w->gridVerify, w->smCount, xs, w->scene, w->arrays, qb, qCount + j + 1, exactQ, xCount + j + 1, walkQ, wCount + j + 1);
+                        k_exact_extend<<<gridExact, WF_THREADS, 0, xs>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
+                    }
                     if (exactAside) WCU(cudaEventRecord(w->evX1, w->exactStream));
                     wf_mark(c, ST_CONNECT);
                     k_connect_prep<<<w->gridPrep, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j,
                                                                        (uint32_t*)w->dJobQ.p, oCount + j, exactNeeQ, xnCount + j);
                     wf_mark(c, ST_OCCLUDE);
                     uint32_t* misQ = (uint32_t*)w->dJobQ.p + w->capacity;      // second half of the job buffer
-                    if (c->countWork) k_occlude<true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
-                    else k_occlude<false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
+                    if (c->exactOrder) {
+                        if (c->countWork) k_occlude<true, true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
+                        else k_occlude<false, true><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
+                    } else {
+                        if (c->countWork) k_occlude<true, false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, workCnt + 2);
+                        else k_occlude<false, false><<<w->gridOcclude, WF_THREADS, 0, cs>>>(P, w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, workO + j, exactNeeQ, xnCount + j, nullptr);
+                    }
                     wf_mark(c, ST_EXACT);
-                    if (c->exactOrder) k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, w->scene, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
+                    if (c->exactOrder) {
+                        k_verify_occluded<<<w->gridVerify, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dJobQ.p, oCount + j, exactNeeQ, xnCount + j);
+                        k_exact_nee<<<gridExact, WF_THREADS, 0, cs>>>(P, w->scene, c->ref, w->arrays, exactNeeQ, xnCount + j, exactTotals + 1);
+                        c->counters[0] += 1;
+                    }
                     wf_mark(c, ST_FINISH);
                     k_connect_finish<<<w->gridFinish, WF_THREADS, 0, cs>>>(w->scene, w->arrays, (const uint32_t*)w->dShadowQ.p, sCount + j, misQ, mCount + j);
                     k_connect_mis<<<w->smCount, WF_THREADS, 0, cs>>>(P, c->ref, w->arrays, misQ, mCount + j);
@@ -954,7 +1047,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                 c->counters[0] += (j + 1 < nB) ? 8 : 1;
             }
             k_fold<<<1, 32, 0, c->stream>>>(qCount, sCount, oCount, mCount, primaryCount, P.sharePrimary, nB, (unsigned long long*)w->dRayCounters.p);
-            c->counters[0] += 4;                                      // generate, extend(0) + its exact re-trace, fold
+            c->counters[0] += 4;                                      // generate, extend(0) + its exact re-trace, fold (the verify pair counts itself)
             if (samples > 1) {
                 k_sample_sum<<<grid, WF_THREADS, 0, c->stream>>>(w->arrays, (float4*)w->dSampleSum.p, P.nPaths, smp, samples);
                 c->counters[0] += 1;
@@ -979,8 +1072,10 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
     if (int rc = wf_reserve(c, (size_t)std::min<uint64_t>(n, chunkMax), pc.params.bounceLimit)) return rc;
     if (!w->gridExtend) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false, true>, WF_THREADS, 0));
         w->gridExtend = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_verify_extend, WF_THREADS, 0));
+        w->gridVerify = std::max(1, perSm) * w->smCount;
     }
     WfParams P;
     memset(&P, 0, sizeof(P));
@@ -996,9 +1091,10 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
         k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays + 2 * done, m, w->arrays, (uint32_t*)w->dQueue[0].p, qCount);
         wf_mark(c, ST_EXTEND);
         uint32_t* xCount = qCount + 7 * w->countSlots;
-        if (c->countWork) k_extend<true><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, (uint32_t*)w->dExactQ.p, xCount, workCnt);
-        else k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, w->arrays.hit, (uint32_t*)w->dExactQ.p, xCount, nullptr);
+        launch_extend(c, w->gridExtend, P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, (uint32_t*)w->dExactQ.p, xCount, workCnt);
         wf_mark(c, -1);
+        if (c->exactOrder) launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, (uint32_t*)w->dExactQ.p, xCount,
+                                         (uint32_t*)w->dWalkQ.p, qCount + 9 * w->countSlots);
         k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, (const uint32_t*)w->dExactQ.p, xCount, w->arrays.hit,
                                                                    (unsigned long long*)w->dRayCounters.p + 12);
         k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, w->arrays, m, dHits + done);
@@ -1014,15 +1110,15 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
 // wavefront_trace_batch keeps its scratch (ray slots, hits, queues, counters) in buffers that wf_reserve grows with
 // cudaMalloc. Callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid it) get a variant
 // whose scratch is this file-scope device array: a fixed size, held by every GPU that loads the library until exit.
-// Layout: 256-byte header {qCount, k_extend's work counter, contested count, pad, u64 re-trace total}, then per-ray
-// arrays origin (16 B) | direction (16 B) | Hit (16 B) | queue (4 B) | contested queue (4 B).
+// Layout: 256-byte header {qCount, k_extend's work counter, contested count, walk count, u64 re-trace total}, then per-ray
+// arrays origin (16 B) | direction (16 B) | Hit (16 B) | queue (4 B) | contested queue (4 B) | walk queue (4 B).
 // The NAME below is a host-side stand-in in host code, not a device address: its device address is looked up once per
 // device (cudaGetSymbolAddress with that device current) and only that pointer is handed to kernels.
 // Every call shares the array and finds the previous call's contents in it: the header is cleared at the start of each
 // call, the per-ray arrays are written before they are read. Calls that overlap on one GPU (two streams, two contexts,
 // two threads) race on it.
 #define WF_STATIC_HEADER 256
-#define WF_STATIC_PER_RAY 56
+#define WF_STATIC_PER_RAY 60
 static __device__ __align__(256) unsigned char g_staticScratch[WF_STATIC_HEADER + (size_t)B200PT_STATIC_MAX_RAYS * WF_STATIC_PER_RAY];
 static_assert(sizeof(Hit) == 16, "scratch layout");
 static unsigned char* g_staticScratchAddr[64] = {nullptr};      // per device ordinal
@@ -1053,8 +1149,10 @@ int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, co
     }
     if (!w->gridExtend) {
         int perSm = 0;
-        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false>, WF_THREADS, 0));
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_extend<false, true>, WF_THREADS, 0));
         w->gridExtend = std::max(1, perSm) * w->smCount;
+        WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_verify_extend, WF_THREADS, 0));
+        w->gridVerify = std::max(1, perSm) * w->smCount;
     }
     const size_t cap = B200PT_STATIC_MAX_RAYS;
     uint32_t* header = (uint32_t*)base;
@@ -1065,6 +1163,7 @@ int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, co
     A.hit = (Hit*)(A.rayD + cap);
     uint32_t* queue = (uint32_t*)(A.hit + cap);
     uint32_t* exactQ = queue + cap;
+    uint32_t* walkQ = exactQ + cap;
     uint32_t* qCount = header, *workE = header + 1, *xCount = header + 2;
     unsigned long long* total = (unsigned long long*)(header + 4);
     WfParams P;
@@ -1075,8 +1174,14 @@ int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, co
     const int grid = std::min<int>(w->smCount * 8, (int)((m + WF_THREADS - 1) / WF_THREADS));
     WCU(cudaMemsetAsync(header, 0, WF_STATIC_HEADER, c->stream));
     k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays, m, A, queue, qCount);
-    k_extend<false><<<w->gridExtend, WF_THREADS, 0, c->stream>>>(P, w->scene, A, queue, qCount, workE, A.hit, exactQ, xCount, nullptr);
-    if (c->exactOrder) k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, A, exactQ, xCount, A.hit, total);
+    const int countWork = c->countWork;
+    c->countWork = 0;
+    launch_extend(c, w->gridExtend, P, w->scene, A, queue, qCount, workE, exactQ, xCount, nullptr);
+    c->countWork = countWork;
+    if (c->exactOrder) {
+        launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, A, queue, qCount, exactQ, xCount, walkQ, header + 3);
+        k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, A, exactQ, xCount, A.hit, total);
+    }
     k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, A, m, dHits);
     c->counters[0] += 4;
     WCU(cudaGetLastError());
