@@ -69,6 +69,16 @@ PT_HD_NOINLINE RefHit ref_closest_hit(const RefScene& sc, const ptl::RayTracerDa
         tr.o = mul_point(Minv, ray.o);
         v3 inv = mk3(1.f / tr.d.x, 1.f / tr.d.y, 1.f / tr.d.z);
 
+        // Without counters to keep (the re-trace of contested rays): an object whose ROOT box the ray misses, or enters beyond
+        // the closest hit so far, contributes nothing — the shader never tests that box (:301-307), but both children's boxes
+        // lie inside it float for float (update_bvh_bounds takes min / max over subsets of the same vertices) and
+        // boxIntersection is monotone in the box (rounding of (b - o) * inv, min, max), so each child's distance is >= the
+        // root's and the loop below would push neither. Exactly the same result, minus two node loads and box tests.
+        if (!stats) {
+            const ptl::BVHNode root = sc.nodes[obj.bvhIndex];
+            if (root.triCount == 0 && tr.d.x != 0.f && tr.d.y != 0.f && tr.d.z != 0.f &&      // finite 1 / d: no 0 * inf = NaN in either test, the order argument holds
+                !(box_test_ref(mk3(root.minX, root.minY, root.minZ), mk3(root.maxX, root.maxY, root.maxZ), tr.o, inv) < best.dst)) continue;
+        }
         uint32_t stack[72];                     // the shader has 64 slots for a depth-64 tree (A-Q16)
         uint32_t sp = 1;
         stack[0] = obj.bvhIndex;

@@ -931,7 +931,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
     uint32_t* wCount = xnCount + w->countSlots;         // hits that need the reachability walk, per bounce
     uint32_t* walkQ = (uint32_t*)w->dWalkQ.p;
     unsigned long long* exactTotals = (unsigned long long*)w->dRayCounters.p + 12;      // [12] extension rays, [13] light-sample queries re-traced exactly
-    const int gridExact = w->smCount * 4;
+    const int gridExact = w->smCount * 7;      // 72 registers: 7 resident blocks per SM; the re-trace is bound by the latency of its dependent node loads (4 blocks: 4.9 -> ? ms per step)
     if (!w->gridOcclude) {
         int perSm = 0;
         WCU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_occlude<false, true>, WF_THREADS, 0));
