@@ -253,7 +253,7 @@ def run_reference(args, rank, world):
                                  what="shaders/raytrace.comp compiled for the CPU by oracle/ref_from_glsl.py (oracle/_ref/libraytrace_comp.so)"
                                       if r["kind"] == "reference" else "oracle/liboracle.so (hand-written restatement)"),
                e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def load_json(*path):
@@ -344,8 +344,32 @@ def build_roofline(args, cfg, F, steps, stages, counted, peaks, pm, tj, avoided,
     return out
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """From here on whatever native libraries write to file descriptor 1 (NCCL's version banner, for one) goes to stderr; the
+    contract's one JSON line is written by emit() to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = json.dumps(obj) + "\n"
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, line.encode())
+
+
 def main():
     args = parse_args()
+    quiet_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -360,8 +384,12 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the backend has no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # NCCL writes its debug output — the "NCCL version ..." banner of its first communicator included — to stdout, in front of
+    # the JSON line: send it to stderr instead (warnings stay visible, stdout holds the one line the contract asks for)
+    # (NCCL honours NCCL_DEBUG_FILE only above the VERSION level, and prints the banner at VERSION and WARN)
     if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"          # NCCL would print its version banner on stdout, in front of the JSON line
+        os.environ["NCCL_DEBUG"] = "WARN"
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -477,7 +505,7 @@ def main():
     if args.only_value:
         out["stage_ms_per_step"] = {k: v[0] / args.steps for k, v in stages.items()}
         if rank == 0:
-            print(json.dumps(out), flush=True)
+            emit(out)
         cp.close()
         if N > 1:
             dist.barrier()
@@ -659,7 +687,7 @@ def main():
                                     note="one 1-spp progressive frame at a time (latency), vs ms_per_frame_1spp = throughput mode / frames"))
         if args.dump:
             np.save(args.dump, pinned_np[..., :3] / np.maximum(pinned_np[..., 3:4], 1))
-        print(json.dumps(out), flush=True)
+        emit(out)
     if cp is not None:
         cp.close()
     if N > 1:
@@ -734,9 +762,9 @@ def bench_soup(args, rank, N, dev, stream, new_pass, device_ms):
         value = n * args.steps / ms / 1e3
         cfg.update(rays_per_step=n, ray_distribution="origins uniform in [-0.95, 0.95]^3, directions uniform on the sphere", hit_fraction=hit_frac,
                    l2="tree + triangle records %.0f MB >> 126 MB L2, rays incoherent by construction; no flush" % (sum(wide_sizes(info))))
-        print(json.dumps(dict(metric="Mrays_per_s_soup_closest_hit", value=value, unit="Mrays/s", n_gpus=N, steps=args.steps, warmup=args.warmup,
+        emit(dict(metric="Mrays_per_s_soup_closest_hit", value=value, unit="Mrays/s", n_gpus=N, steps=args.steps, warmup=args.warmup,
                               ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                              config=cfg, clocks=clocks, gpu_launches=cw["launches"], roofline=roof)), flush=True)
+                              config=cfg, clocks=clocks, gpu_launches=cw["launches"], roofline=roof))
     cp.close()
 
 
