@@ -192,9 +192,11 @@ int b200pt_render_frame_interleaved(b200pt_ctx* ctx, const void* push_constants_
  * (results do not depend on them); "wide_build" 1 (default) / 0: the internal wide BVH of all triangles is built on
  * the device / on the host at b200pt_upload_scene and b200pt_update_* (read before the upload; images do not depend
  * on it); "refit_on_update" 1 (default) / 0; "exact_order" 1 (default) / 0: rays on which two candidates lie
- * closer together than the rounding error of their distances (coincident surfaces; about 5 per thousand in the C4 stand-in)
- * are re-traced in the reference's own traversal order, which makes every result the reference's bit for bit; 0 skips the
- * re-trace (2 ms less latency per 1-spp frame, about 1e-4 of the paths then depend on the traversal order). Read-only: "last_scene_build_us", "last_wide_device_us",
+ * closer together than the rounding error of their distances (coincident surfaces; about 6 per thousand in the C4 stand-in)
+ * are re-traced in the reference's own traversal order, which makes every result the reference's bit for bit; with it the
+ * traversal kernels also accept candidate hits optimistically and separate kernels confirm each ray's final hit against the
+ * reference's BVH2 (failures join the re-trace). 0 skips the re-trace and keeps that confirmation inside the traversal
+ * loop (1.6 ms less latency per 1-spp frame, about 1e-4 of the paths then depend on the traversal order). Read-only: "last_scene_build_us", "last_wide_device_us",
  * "last_update_was_refit". Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
@@ -209,14 +211,15 @@ int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
  * with option "count_work": [7] node visits and [8] triangle tests of the closest-hit kernel, [9] and [10] the same
  * for the occlusion kernel (wide layout: 80 B per node, 64 B per triangle record); [11] extension rays and [12]
  * light-sample queries that were CONTESTED (two candidates closer together than the rounding slack of their distances:
- * coincident surfaces) and were re-traced in the reference's own order over the reference's own buffers, so that the
- * result is the reference's bit for bit; [13..15] reserved. */
+ * coincident surfaces), or whose optimistically accepted hit the reference would not have tested, and were re-traced in
+ * the reference's own order over the reference's own buffers, so that the result is the reference's bit for bit;
+ * [13..15] reserved. */
 int b200pt_read_counters(b200pt_ctx* ctx, uint64_t* out16);
 int b200pt_reset_counters(b200pt_ctx* ctx);
 /* With option "profile_stages" = 1 the wavefront records a CUDA event between consecutive launches; this
  * returns the accumulated device milliseconds and launch counts per stage, 8 entries each
- * (0 generate, 1 extend, 2 shade, 3 connect-prep, 4 accumulate, 5 occlude, 6 connect-finish, 7 reference-order re-trace of
- * contested rays)
+ * (0 generate, 1 extend, 2 shade, 3 connect-prep, 4 accumulate, 5 occlude, 6 connect-finish, 7 confirmation of the
+ * traversal kernels' hits + reference-order re-trace of contested rays)
  * and optionally resets them. */
 int b200pt_read_stage_times(b200pt_ctx* ctx, double* ms8, uint64_t* launches8, int reset);
 /* Device time of the last render call in milliseconds (CUDA events on the context's stream). */
