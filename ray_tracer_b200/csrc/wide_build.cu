@@ -67,6 +67,8 @@ struct Dev {
                                              // [7] next emit list [8] max depth [9] instances dropped (non-finite vertices)
     uint32_t* nextList[4];                   // by triangle count: <= 64, <= 4096, <= HUGE_MIN, above
     int maxLeaf; float travCost;
+    // SAH-optimal collapse (k_dp_*): per binary node the cost of its subtree as at most i = 1..8 children of a wide node
+    float* dpC; uint8_t* dpK; uint8_t* dpUse; uint32_t* parent; uint32_t* arrived; int dp;
     // output
     Bvh8Node* outNodes; PrimRecord* outPrim; ShadeRecord* outShade; UvRecord* outUv;
     EmitItem* emitNext;
@@ -470,6 +472,58 @@ __device__ __forceinline__ uint8_t exponent_for(float extent) {     // smallest 
     return (uint8_t)max(1, min(254, b));
 }
 
+// ---- SAH-optimal collapse of the binary tree into 8-wide nodes (Ylitie, Karras, Laine 2017, section 3.1; b8::Builder2::
+// collapse_dp is the host form), with the binary leaves as the leaves:
+//   C(n, 1) = A(n) + D(n, 8)                              n becomes a wide node over at most 8 children
+//   D(n, j) = min over 0 < k < j of C(left, k) + C(right, j - k)
+//   C(n, i) = min(D(n, i), C(n, i - 1))                   the subtree of n as at most i children of some wide node
+// dpK[n][j] = the k of D(n, j); bit i - 1 of dpUse[n] = C(n, i) takes D(n, i). Bottom-up: one thread per binary node starts
+// at the leaves, and the second child to arrive at a parent computes it (children are read around L1: volatile).
+__global__ void k_dp_parent(Dev d, uint32_t nNodes2) {
+    const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= nNodes2) return;
+    if (m == 0) d.parent[0] = 0xffffffffu;
+    const Node2 nd = d.nodes2[m];
+    if (nd.count == 0) { d.parent[nd.left] = m; d.parent[nd.right] = m; }
+}
+__global__ void k_dp_up(Dev d, uint32_t nNodes2) {
+    uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= nNodes2) return;
+    {
+        const Node2 nd = d.nodes2[m];
+        if (nd.count == 0) return;
+        const float c = half_area(nd.lo, nd.hi) * (float)nd.count;
+        for (int i = 1; i <= 8; ++i) d.dpC[(size_t)m * 8 + i - 1] = c;
+    }
+    for (;;) {
+        const uint32_t p = d.parent[m];
+        if (p == 0xffffffffu) return;
+        __threadfence();
+        if (atomicAdd(&d.arrived[p], 1u) == 0u) return;           // the sibling's subtree is not finished: its thread goes on
+        __threadfence();
+        const Node2 nd = d.nodes2[p];
+        const volatile float* L = d.dpC + (size_t)nd.left * 8;
+        const volatile float* R = d.dpC + (size_t)nd.right * 8;
+        float l[8], r[8];
+        for (int i = 0; i < 8; ++i) { l[i] = L[i]; r[i] = R[i]; }
+        float D[9];
+        for (int j = 2; j <= 8; ++j) {
+            float best = 3.0e38f; int bk = 1;
+            for (int k = 1; k < j; ++k) { const float c = l[k - 1] + r[j - k - 1]; if (c < best) { best = c; bk = k; } }
+            D[j] = best; d.dpK[(size_t)p * 8 + j - 1] = (uint8_t)bk;
+        }
+        float C = half_area(nd.lo, nd.hi) + D[8];
+        uint32_t use = 0;
+        d.dpC[(size_t)p * 8] = C;
+        for (int i = 2; i <= 8; ++i) {
+            if (D[i] < C) { C = D[i]; use |= 1u << (i - 1); }
+            d.dpC[(size_t)p * 8 + i - 1] = C;
+        }
+        d.dpUse[p] = (uint8_t)use;
+        m = p;
+    }
+}
+
 // bvh8_emit (bvh8_build.h) for one wide node: gather up to 8 children by opening the largest inner child, assign
 // octant-ordered slots, quantise, copy the leaf triangles' records, queue the inner children for the next level.
 __global__ void k_wide_emit(Dev d, const EmitItem* __restrict__ items, uint32_t nItems) {
@@ -480,8 +534,27 @@ __global__ void k_wide_emit(Dev d, const EmitItem* __restrict__ items, uint32_t 
     uint32_t ch[8]; Node2 cn[8]; int nch = 0;
     const Node2 root = d.nodes2[it.n2];
     if (root.count) { ch[0] = it.n2; cn[0] = root; nch = 1; }
+    else if (d.dp) {
+        // the children the DP chose: D(root, 8) splits its 8 places between the two subtrees, and so on down
+        uint32_t stN[16]; int stI[16]; int sp = 0;
+        const int k8 = d.dpK[(size_t)it.n2 * 8 + 7];
+        stN[sp] = root.right; stI[sp++] = 8 - k8;
+        stN[sp] = root.left; stI[sp++] = k8;
+        while (sp > 0) {
+            const uint32_t m = stN[--sp]; int i = stI[sp];
+            const Node2 nd = d.nodes2[m];
+            if (nd.count == 0) {
+                const uint32_t use = d.dpUse[m];
+                while (i > 1 && !(use & (1u << (i - 1)))) i--;
+            }
+            if (nd.count != 0 || i == 1 || nch + sp >= 7) { ch[nch] = m; cn[nch] = nd; nch++; continue; }    // (the last test cannot trigger: the places add up to 8)
+            const int k = d.dpK[(size_t)m * 8 + i - 1];
+            stN[sp] = nd.right; stI[sp++] = i - k;
+            stN[sp] = nd.left; stI[sp++] = k;
+        }
+    }
     else { ch[0] = root.left; ch[1] = root.right; cn[0] = d.nodes2[ch[0]]; cn[1] = d.nodes2[ch[1]]; nch = 2; }
-    while (nch < 8) {
+    while (!d.dp && nch < 8) {
         int best = -1; float bestA = -1.f;
         for (int k = 0; k < nch; ++k) {
             if (cn[k].count) continue;
@@ -603,6 +676,10 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
                  oUv = plan(n, sizeof(UvRecord)), oBox = plan(n, sizeof(WideBox)), oIdx = plan(n, 4), oIdxT = plan(n, 4), oValid = plan(n, 1),
                  oNodes2 = plan(2 * n + 1, sizeof(Node2)), oCnt = plan(16, 4), oEmit0 = plan(n + 1, sizeof(EmitItem)), oEmit1 = plan(n + 1, sizeof(EmitItem)),
                  oHuge = plan(maxHuge, sizeof(HugeNode)), oChunks = plan(maxChunks, sizeof(HugeChunk)), oChunkLeft = plan(maxChunks, 4);
+    d.dp = 1;                                 // B200PT_BVH_COLLAPSE=greedy: open the largest child instead (the round-1 collapse)
+    if (const char* e = std::getenv("B200PT_BVH_COLLAPSE")) d.dp = std::string(e) == "greedy" ? 0 : 1;
+    const size_t oDpC = plan(d.dp ? 2 * n + 1 : 1, 32), oDpK = plan(d.dp ? 2 * n + 1 : 1, 8), oDpUse = plan(d.dp ? 2 * n + 1 : 1, 1),
+                 oParent = plan(d.dp ? 2 * n + 1 : 1, 4), oArrived = plan(d.dp ? 2 * n + 1 : 1, 4);
     size_t oList[8];
     for (auto& o : oList) o = plan(n / 2 + 1, 4);              // a listed node holds at least 2 triangles
     if (arena.bytes < need) {
@@ -620,6 +697,8 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
     emit[0] = (EmitItem*)(base + oEmit0); emit[1] = (EmitItem*)(base + oEmit1);
     hugeNodes = (HugeNode*)(base + oHuge); hugeChunks = (HugeChunk*)(base + oChunks); chunkLeft = (uint32_t*)(base + oChunkLeft);
     for (int i = 0; i < 8; ++i) lists[i] = (uint32_t*)(base + oList[i]);
+    d.dpC = (float*)(base + oDpC); d.dpK = (uint8_t*)(base + oDpK); d.dpUse = (uint8_t*)(base + oDpUse);
+    d.parent = (uint32_t*)(base + oParent); d.arrived = (uint32_t*)(base + oArrived);
     // the four result buffers: the caller's previous ones are written again when they are large enough
     struct Fresh { std::vector<void*> p; ~Fresh() { for (void* q : p) cudaFree(q); } } fresh;      // freed unless handed over
     const size_t capNodes = (n + 1) * sizeof(Bvh8Node), capPrim = std::max<size_t>(n, 1) * sizeof(PrimRecord),
@@ -727,6 +806,13 @@ const char* wide_build_device(cudaStream_t st, const WideDeviceInputs& in, const
                 k_huge_copyback<<<nChunks, HUGE_THREADS, 0, st>>>(d, hugeNodes, hugeChunks);
                 k_huge_children<<<(2 * nHuge + 63) / 64, 64, 0, st>>>(d, hugeNodes, nHuge);
             }
+            WBC(cudaGetLastError());
+        }
+        if (d.dp) {
+            const uint32_t nNodes2 = h[1];
+            WBC(cudaMemsetAsync(d.arrived, 0, (size_t)nNodes2 * 4, st));
+            k_dp_parent<<<(nNodes2 + 255) / 256, 256, 0, st>>>(d, nNodes2);
+            k_dp_up<<<(nNodes2 + 127) / 128, 128, 0, st>>>(d, nNodes2);
             WBC(cudaGetLastError());
         }
         // collapse + emit, level by level from the root (wide node 0 <- binary node 0)
