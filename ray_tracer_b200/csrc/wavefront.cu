@@ -318,7 +318,8 @@ __global__ void __launch_bounds__(WF_THREADS) k_verify_walk(const __grid_constan
 static void launch_verify(b200pt_ctx* c, int grid, int smCount, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
                           const uint32_t* count, uint32_t* exactQ, uint32_t* xCount, uint32_t* walkQ, uint32_t* wCount) {
     k_verify_extend<<<grid, WF_THREADS, 0, st>>>(sc, A, queue, count, A.hit, exactQ, xCount, walkQ, wCount);
-    k_verify_walk<<<smCount * 4, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);
+    k_verify_walk<<<grid, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);      // a chain of dependent parent loads per ray: as many resident warps as fit
+    (void)smCount;
     c->counters[0] += 2;
 }
 static void launch_extend(b200pt_ctx* c, int grid, const WfParams& P, const WideScene& sc, const PathArrays& A, const uint32_t* queue, const uint32_t* count,

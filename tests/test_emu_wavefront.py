@@ -135,3 +135,18 @@ def test_contested_rays_take_the_reference_order():
             ((got["kind"] != 2) | ((got["objectHitIndex"] == want["objectHitIndex"]) & (got["triHitIndex"] == want["triHitIndex"]))))
     assert same.all(), np.nonzero(~same)[0][:10]
     assert 0 < contested < 0.02 * len(rays)
+
+
+def test_sah_optimal_collapse_gives_the_same_hits(bunny_blobs, monkeypatch):
+    # bvh8_build.h: collapse_dp (B200PT_BVH_COLLAPSE=dp; the device builder's default, wide_build.cu: k_dp_up) only changes
+    # which binary nodes become children of which wide node: hits cannot depend on it
+    nobj = bunny_blobs["objects"].size // 80
+    pc = ob.default_push_constants(128, 128, 10, nobj)
+    rays = np.concatenate([camera_rays(pc, 128, 128), random_rays(20000, seed=8)])
+    monkeypatch.setenv("B200PT_BVH_COLLAPSE", "greedy")
+    greedy = emu.EmuScene(bunny_blobs).trace_batch(pc, rays)
+    monkeypatch.setenv("B200PT_BVH_COLLAPSE", "dp")
+    dp = emu.EmuScene(bunny_blobs).trace_batch(pc, rays)
+    assert greedy.tobytes() == dp.tobytes()
+    want, _ = ob.OracleScene(bunny_blobs).trace_batch(pc, rays)
+    assert _compare_hits(dp, want).all()
