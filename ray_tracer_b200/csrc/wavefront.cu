@@ -285,54 +285,6 @@ __global__ void __launch_bounds__(WF_THREADS, OPT ? PT_EXTEND_MIN_BLOCKS_OPT : P
     if (COUNT) flush_work(work, cntNode, cntTri);
 }
 
-// After k_extend<*, true>: every ray's final hit, at full lane count. A triangle hit that the reference would not have
-// tested (pt_traverse.h: ref_reachable) and every ray marked contested go to k_exact_extend; for the former the stored
-// distance becomes PT_FAR, which tells the re-trace not to use it as its starting bound. Two kernels: the quick accept
-// for every ray here, the leaf -> root walk (1 % of the hits) from a compacted queue in k_verify_walk — inside one
-// kernel a warp with one walking lane waited for it (10 of 32 lanes per instruction, 7.2 ms per step instead of ~3).
-__global__ void __launch_bounds__(WF_THREADS) k_verify_extend(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ queue,
-                                                              const uint32_t* __restrict__ qCount, const Hit* __restrict__ hit, uint32_t* exactQueue,
-                                                              uint32_t* exactCount, uint32_t* walkQueue, uint32_t* walkCount) {
-    const uint32_t n = *qCount;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t p = queue[i];
-        const Hit h = hit[p];
-        if (h.id == PT_HIT_MISS) continue;
-        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-        if (!hit_reachable_quick(sc, r, h)) walkQueue[atomicAdd(walkCount, 1u)] = p;
-        else if (h.id & PT_HIT_CONTESTED) exactQueue[atomicAdd(exactCount, 1u)] = p;
-    }
-}
-__global__ void __launch_bounds__(WF_THREADS) k_verify_walk(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ walkQueue,
-                                                            const uint32_t* __restrict__ walkCount, Hit* hit, uint32_t* exactQueue, uint32_t* exactCount) {
-    const uint32_t n = *walkCount;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t p = walkQueue[i];
-        const Hit h = hit[p];
-        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
-        const bool ok = hit_reachable_walk(sc, r, h);
-        if (!ok) hit[p].dst = PT_FAR;
-        if (!ok || (h.id & PT_HIT_CONTESTED)) exactQueue[atomicAdd(exactCount, 1u)] = p;
-    }
-}
-static void launch_verify(b200pt_ctx* c, int grid, int smCount, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
-                          const uint32_t* count, uint32_t* exactQ, uint32_t* xCount, uint32_t* walkQ, uint32_t* wCount) {
-    k_verify_extend<<<grid, WF_THREADS, 0, st>>>(sc, A, queue, count, A.hit, exactQ, xCount, walkQ, wCount);
-    k_verify_walk<<<grid, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);      // a chain of dependent parent loads per ray: as many resident warps as fit
-    (void)smCount;
-    c->counters[0] += 2;
-}
-static void launch_extend(b200pt_ctx* c, int grid, const WfParams& P, const WideScene& sc, const PathArrays& A, const uint32_t* queue, const uint32_t* count,
-                          uint32_t* workCounter, uint32_t* exactQ, uint32_t* xCount, unsigned long long* workCnt) {
-    if (c->exactOrder) {
-        if (c->countWork) k_extend<true, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
-        else k_extend<false, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
-    } else {
-        if (c->countWork) k_extend<true, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
-        else k_extend<false, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
-    }
-}
-
 // Block-aggregated queue append: ONE global atomic per block per round instead of one per warp. With 16 M paths per
 // launch the per-warp form issued 0.5 M atomics on each of two addresses and shade's stall samples pointed at them
 // (54 %, profiles/r01/k_shade_v12_by_line.txt); measured gain 0.4 ms of 9.5 per step — the wait was mostly overlapped.
@@ -365,6 +317,67 @@ static __device__ __forceinline__ void block_push(uint32_t* const (&counters)[NQ
         slot[q] = blockBase[q] + before + (uint32_t)__popc(mask[q] & ((1u << lane) - 1u));
     }
     __syncthreads();            // warpCount is reused by the next round
+}
+
+// After k_extend<*, true>: every ray's final hit, at full lane count. A triangle hit that the reference would not have
+// tested (pt_traverse.h: ref_reachable) and every ray marked contested go to k_exact_extend; for the former the stored
+// distance becomes PT_FAR, which tells the re-trace not to use it as its starting bound. Two kernels: the quick accept
+// for every ray here, the leaf -> root walk (1 % of the hits) from a compacted queue in k_verify_walk — inside one
+// kernel a warp with one walking lane waited for it (10 of 32 lanes per instruction, 7.2 ms per step instead of ~3).
+__global__ void __launch_bounds__(WF_THREADS) k_verify_extend(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ queue,
+                                                              const uint32_t* __restrict__ qCount, const Hit* __restrict__ hit, uint32_t* exactQueue,
+                                                              uint32_t* exactCount, uint32_t* walkQueue, uint32_t* walkCount) {
+    const uint32_t n = *qCount;
+    uint32_t* const counters[2] = {walkCount, exactCount};
+    // uniform trip count: the two appends are aggregated per block (one atomic per block and queue: the per-ray form put
+    // 0.6 M atomics per launch on two addresses)
+    for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < n; i0 += gridDim.x * blockDim.x) {
+        const uint32_t i = i0 + threadIdx.x;
+        bool pred[2] = {false, false};
+        uint32_t p = 0;
+        if (i < n) {
+            p = queue[i];
+            const Hit h = hit[p];
+            if (h.id != PT_HIT_MISS) {
+                Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+                if (!hit_reachable_quick(sc, r, h)) pred[0] = true;
+                else if (h.id & PT_HIT_CONTESTED) pred[1] = true;
+            }
+        }
+        uint32_t slot[2];
+        block_push<2>(counters, pred, slot);
+        if (pred[0]) walkQueue[slot[0]] = p;
+        if (pred[1]) exactQueue[slot[1]] = p;
+    }
+}
+__global__ void __launch_bounds__(WF_THREADS) k_verify_walk(const __grid_constant__ WideScene sc, PathArrays A, const uint32_t* __restrict__ walkQueue,
+                                                            const uint32_t* __restrict__ walkCount, Hit* hit, uint32_t* exactQueue, uint32_t* exactCount) {
+    const uint32_t n = *walkCount;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = walkQueue[i];
+        const Hit h = hit[p];
+        Ray r; r.o = xyz(A.rayO[p]); r.d = xyz(A.rayD[p]);
+        const bool ok = hit_reachable_walk(sc, r, h);
+        if (!ok) hit[p].dst = PT_FAR;
+        if (!ok || (h.id & PT_HIT_CONTESTED)) exactQueue[atomicAdd(exactCount, 1u)] = p;
+    }
+}
+static void launch_verify(b200pt_ctx* c, int grid, int smCount, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
+                          const uint32_t* count, uint32_t* exactQ, uint32_t* xCount, uint32_t* walkQ, uint32_t* wCount) {
+    k_verify_extend<<<grid, WF_THREADS, 0, st>>>(sc, A, queue, count, A.hit, exactQ, xCount, walkQ, wCount);
+    k_verify_walk<<<grid, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);      // a chain of dependent parent loads per ray: as many resident warps as fit
+    (void)smCount;
+    c->counters[0] += 2;
+}
+static void launch_extend(b200pt_ctx* c, int grid, const WfParams& P, const WideScene& sc, const PathArrays& A, const uint32_t* queue, const uint32_t* count,
+                          uint32_t* workCounter, uint32_t* exactQ, uint32_t* xCount, unsigned long long* workCnt) {
+    if (c->exactOrder) {
+        if (c->countWork) k_extend<true, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        else k_extend<false, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
+    } else {
+        if (c->countWork) k_extend<true, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        else k_extend<false, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
+    }
 }
 
 #ifndef PT_SHADE_MIN_BLOCKS
