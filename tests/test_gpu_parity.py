@@ -514,6 +514,41 @@ def test_real_asset_with_its_texture_maps(gpu):
     _assert_explained(blobs, pc, W, H, range(8), cp.read_accum(), plain)
 
 
+@pytest.mark.parametrize("name", ["cornell_blobs", "bunny_blobs"])
+def test_exact_order_off_keeps_the_in_loop_confirmation(gpu, name, request):
+    # option exact_order = 0 (interactive use): no reference-order re-trace, and the traversal kernels confirm reachability
+    # inside their loops again (k_extend<*, false> / k_occlude<*, false>) since there is no re-trace to fall back on. The
+    # image may differ from the exact one only where two surfaces coincide (which of them is reported): a handful of
+    # pixels at most on these scenes, and the estimate is the same.
+    blobs = request.getfixturevalue(name)
+    W, H = 256, 192
+    nobj = blobs["objects"].size // 80
+    pc = ob.default_push_constants(W, H, 10, nobj)
+    pc.view(np.float32)[39] = 1.0
+    cp = _pass(gpu, blobs, W, H)
+    cp.render_frames(pc, 0, 6)
+    exact = cp.read_accum()
+    cp.clear()
+    cp.set_option("exact_order", 0)
+    cp.render_frames(pc, 0, 6)
+    loose = cp.read_accum()
+    c = cp.counters()
+    assert _differing(exact, loose) <= 2e-3
+    assert relrmse(loose[..., :3], exact[..., :3]) <= 1e-3
+    cp.set_option("exact_order", 1)
+    cp.clear()
+    cp.render_frames(pc, 0, 6)
+    assert np.array_equal(cp.read_accum().view(np.uint32), exact.view(np.uint32))
+    # first hits: both forms agree wherever the exact form did not need the re-trace's verdict on coincident surfaces
+    rays = np.concatenate([camera_rays(pc, 128, 128), random_rays(30000, seed=3)])
+    a = cp.trace_batch(pc, rays)
+    cp.set_option("exact_order", 0)
+    b = cp.trace_batch(pc, rays)
+    same = _same_hits(a, b)
+    assert (same | (np.abs(a["dst"] - b["dst"]) <= 1e-4 * (1 + np.abs(a["dst"])))).all()
+    assert same.mean() > 0.995
+
+
 def test_depth16_and_deep_roulette(gpu, bunny_blobs):
     # C5's bounce limit (16): Russian roulette is live for j > 5 (raytrace.comp:519-524), the queues run 17 bounces
     W, H = 200, 160
