@@ -124,6 +124,9 @@ PT_HD uint32_t pick_word(bool neg, uint32_t ifNeg, uint32_t ifPos) {
     return neg ? ifNeg : ifPos;
 #endif
 }
+#ifndef PT_NODE_HITBITS_PRMT
+#define PT_NODE_HITBITS_PRMT 1     /* hit-bit assembly: one PRMT per child extracts (count, position) */
+#endif
 #ifndef PT_NODE_FFMA2
 #define PT_NODE_FFMA2 0           /* node test: child planes two at a time through FFMA2 (device only). A/B on B200: 306.2 vs 311.7 Mpaths/s without —
                                      an FFMA2 takes one issue slot (peaks_micro: FFMA2 + LOP3 interleaved 1108 G/s) but holds the FMA pipe for two
@@ -169,6 +172,11 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
         const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
         const uint32_t bitIndex4 = (meta4 ^ (br.octinv4 & innerMask4)) & 0x1f1f1f1fu;
         const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
+#if defined(__CUDA_ARCH__) && PT_NODE_HITBITS_PRMT
+        // per child one byte: unary count in bits 5..7, final bit position in bits 0..4 — one PRMT extracts it, the shift
+        // count of a 32-bit shift takes its low five bits by itself
+        const uint32_t posCount4 = (meta4 & 0xe0e0e0e0u) | bitIndex4;
+#endif
 #if defined(__CUDA_ARCH__) && PT_NODE_FFMA2
         // two children per FFMA2 (sm_100 packed FP32 FMA: one issued instruction, the per-axis scale and offset broadcast):
         // the same fma.rn per plane as the scalar form, half the FMA issue slots of a node visit (48 -> 24)
@@ -199,7 +207,12 @@ PT_HD uint32_t bvh8_node_hits(const NodeWords& n, const BoxRay& br, float tmax) 
             float t1z = pt_fma(byte_to_float(fz[h], k), sz, ofz);
             float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
             float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+#if defined(__CUDA_ARCH__) && PT_NODE_HITBITS_PRMT
+            const uint32_t pc = __byte_perm(posCount4, 0u, 0x4440u + (uint32_t)k);
+            if (tn <= tf) hits |= (pc >> 5) << (pc & 31u);
+#else
             if (tn <= tf) hits |= ((childBits4 >> (8 * k)) & 0xffu) << ((bitIndex4 >> (8 * k)) & 0xffu);
+#endif
         }
 #endif
     }
