@@ -4,7 +4,7 @@
 set -x
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 mkdir -p gpurun_out
-T=r03g
+T=r03j
 timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/${T}_noalloc_alone.log 2>&1; echo "noalloc alone rc=$?" >> gpurun_out/${T}_noalloc_alone.log
 timeout 1800 python -m pytest tests -m gpu -x -q --durations=6 > gpurun_out/${T}_gputests.log 2>&1; echo "gputests rc=$?" >> gpurun_out/${T}_gputests.log
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/${T}_bench_atrium.json 2> gpurun_out/${T}_bench_atrium.err
