@@ -158,7 +158,7 @@ class OracleScene:
 
     def pixel_ties(self, pc, W, H, frame, xy):
         """For pixels xy (n, 2) of frame `frame`: number of rays on the pixel's path whose closest hit lies at exactly the
-        same distance on two triangles of one object (the documented tie class)."""
+        same distance on two triangles of one object (round 1's tie class; the kernels now settle those in the reference's order)."""
         pcb = self._pc(pc)
         xy = np.ascontiguousarray(xy, np.uint32).reshape(-1, 2)
         out = np.zeros(xy.shape[0], np.uint32)

@@ -29,10 +29,8 @@ def test_first_hit_ids_bit_exact(name, request):
     want, _ = ob.OracleScene(blobs).trace_batch(pc, rays)
     got = emu.EmuScene(blobs).trace_batch(pc, rays)
     same = _compare_hits(got, want)
-    # documented tie class: equal-distance hits on shared edges / coplanar faces may resolve to the other triangle
-    ties = ~same & (got["dst"] == want["dst"]) & (got["kind"] == want["kind"])
-    assert (same | ties).all(), np.flatnonzero(~(same | ties))[:10]
-    assert ties.mean() < 2e-3, ties.mean()
+    # no tie class: contested rays (coincident surfaces, equal distances) take the reference's own order (pt_traverse.h)
+    assert same.all(), np.flatnonzero(~same)[:10]
     hit = same & (want["kind"] != 0)
     assert np.array_equal(got["normal"][hit].view(np.uint32), want["normal"][hit].view(np.uint32))
     assert np.array_equal(got["hitPoint"][hit].view(np.uint32), want["hitPoint"][hit].view(np.uint32))
