@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__
 #define PT_FETCH_MIN_IDLE 8        /* refill once this many lanes are idle (or all are) */
 
 struct WarpFeeder {                // warp-uniform
+    uint32_t chunk = PT_CHUNK;     // indices per global atomic (feeder_chunk)
     uint32_t next = 0, end = 0;
     bool exhausted = false;
 };
@@ -143,10 +144,10 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     const unsigned lane = threadIdx.x & 31u;
     if (f.next == f.end) {
         uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(workCounter, PT_CHUNK);
+        if (lane == 0) base = atomicAdd(workCounter, f.chunk);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base >= n) { f.exhausted = true; return false; }
-        f.next = base; f.end = min(base + PT_CHUNK, n);
+        f.next = base; f.end = min(base + f.chunk, n);
     }
     uint32_t give = min((uint32_t)__popc(idleMask), f.end - f.next);
     uint32_t rank = (uint32_t)__popc(idleMask & ((1u << lane) - 1u));
@@ -154,6 +155,17 @@ static __device__ __forceinline__ bool feeder_take(WarpFeeder& f, uint32_t* work
     index = f.next + rank;
     f.next += give;
     return got;
+}
+
+// A queue too short to give every resident warp a full chunk is handed out a warp's width at a time: with 128 a launch
+// of 259 k rays (one eighth of a 1080p frame) kept 2 000 of the 4 700 resident warps busy for four generations of rays each,
+// with 32 all of them for two — the length of a small launch is the time ONE warp needs.
+#ifndef PT_CHUNK_SMALL
+#define PT_CHUNK_SMALL 32u
+#endif
+static __device__ __forceinline__ uint32_t feeder_chunk(uint32_t n) {
+    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+    return n < PT_CHUNK * warps ? PT_CHUNK_SMALL : PT_CHUNK;
 }
 
 #ifndef PT_STREAM_PREFETCH
@@ -232,6 +244,7 @@ __global__ void __launch_bounds__(WF_THREADS, OPT ? PT_EXTEND_MIN_BLOCKS_OPT : P
     const uint32_t sphereCount = P.pc.params.sphereCount, objectCount = P.pc.params.objectCount;
     PT_DECLARE_STACK(stack);
     WarpFeeder feed;
+    feed.chunk = feeder_chunk(n);
     Trav t;
     Hit hit;
     uint32_t key = 0xffffffffu, p = 0;
@@ -455,6 +468,7 @@ __global__ void __launch_bounds__(WF_THREADS, OPT ? PT_EXTEND_MIN_BLOCKS_OPT : P
     const uint32_t objectCount = P.pc.params.objectCount;
     PT_DECLARE_STACK(stack);
     WarpFeeder feed;
+    feed.chunk = feeder_chunk(n);
     Trav t;
     float tE = 0.f, ws = 1.f;
     uint32_t keyE = 0, job = 0;
