@@ -196,7 +196,7 @@ int b200pt_render_frame_interleaved(b200pt_ctx* ctx, const void* push_constants_
  * are re-traced in the reference's own traversal order, which makes every result the reference's bit for bit; with it the
  * traversal kernels also accept candidate hits optimistically and separate kernels confirm each ray's final hit against the
  * reference's BVH2 (failures join the re-trace). 0 skips the re-trace and keeps that confirmation inside the traversal
- * loop (1.6 ms less latency per 1-spp frame, about 1e-4 of the paths then depend on the traversal order). Read-only: "last_scene_build_us", "last_wide_device_us",
+ * loop (1.5 ms less latency per 1-spp frame on one GPU, 2.1 ms less on eight, about 1e-4 of the paths then depend on the traversal order). Read-only: "last_scene_build_us", "last_wide_device_us",
  * "last_update_was_refit". Unknown keys fail. */
 int b200pt_set_option(b200pt_ctx* ctx, const char* key, int64_t value);
 int b200pt_get_option(b200pt_ctx* ctx, const char* key, int64_t* value);
