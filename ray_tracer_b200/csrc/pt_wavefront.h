@@ -126,14 +126,7 @@ PT_HD Hit exact_closest_hit(const RefScene& ref, const WideScene& sc, const ptl:
 }
 // Would the reference have tested the triangle of this (optimistically accepted, pt_traverse.h) closest hit? Spheres and
 // misses: nothing to confirm.
-PT_HD bool hit_reachable(const WideScene& sc, const Ray& ray, const Hit& h) {
-    if (h.id == PT_HIT_MISS || (h.id & PT_HIT_SPHERE)) return true;
-    const PrimRecord p = load_prim(sc.all.prims, h.id & PT_HIT_IDMASK & ~PT_HIT_CONTESTED);
-    ObjRayCache oc; oc.xform = 0xffffffffu;
-    object_ray(oc, sc.xforms, p.xformId, ray);
-    return ref_reachable(sc.up, p, oc, h.dst);
-}
-// the two halves of it, for a kernel pair: the quick accept at full lane count, the rare walk from a compacted queue
+// In two halves, for a kernel pair: the quick accept at full lane count, the rare walk from a compacted queue
 PT_HD bool hit_reachable_quick(const WideScene& sc, const Ray& ray, const Hit& h) {
     if (h.id == PT_HIT_MISS || (h.id & PT_HIT_SPHERE)) return true;
     const PrimRecord p = load_prim(sc.all.prims, h.id & PT_HIT_IDMASK & ~PT_HIT_CONTESTED);

@@ -375,20 +375,20 @@ __global__ void __launch_bounds__(WF_THREADS) k_verify_walk(const __grid_constan
         if (!ok || (h.id & PT_HIT_CONTESTED)) exactQueue[atomicAdd(exactCount, 1u)] = p;
     }
 }
-static void launch_verify(b200pt_ctx* c, int grid, int smCount, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
+static void launch_verify(b200pt_ctx* c, int grid, cudaStream_t st, const WideScene& sc, const PathArrays& A, const uint32_t* queue,
                           const uint32_t* count, uint32_t* exactQ, uint32_t* xCount, uint32_t* walkQ, uint32_t* wCount) {
     k_verify_extend<<<grid, WF_THREADS, 0, st>>>(sc, A, queue, count, A.hit, exactQ, xCount, walkQ, wCount);
     k_verify_walk<<<grid, WF_THREADS, 0, st>>>(sc, A, walkQ, wCount, A.hit, exactQ, xCount);      // a chain of dependent parent loads per ray: as many resident warps as fit
-    (void)smCount;
     c->counters[0] += 2;
 }
 static void launch_extend(b200pt_ctx* c, int grid, const WfParams& P, const WideScene& sc, const PathArrays& A, const uint32_t* queue, const uint32_t* count,
                           uint32_t* workCounter, uint32_t* exactQ, uint32_t* xCount, unsigned long long* workCnt) {
+    const bool countWork = c->countWork && workCnt;
     if (c->exactOrder) {
-        if (c->countWork) k_extend<true, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        if (countWork) k_extend<true, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
         else k_extend<false, true><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
     } else {
-        if (c->countWork) k_extend<true, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
+        if (countWork) k_extend<true, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, workCnt);
         else k_extend<false, false><<<grid, WF_THREADS, 0, c->stream>>>(P, sc, A, queue, count, workCounter, A.hit, exactQ, xCount, nullptr);
     }
 }
@@ -1017,7 +1017,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
             launch_extend(c, w->gridExtend, P, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, workE, exactQ, xCount, workCnt);
             wf_mark(c, ST_EXACT);
             if (c->exactOrder) {
-                launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, exactQ, xCount, walkQ, wCount);
+                launch_verify(c, w->gridVerify, c->stream, w->scene, w->arrays, qa, P.sharePrimary ? primaryCount : qCount, exactQ, xCount, walkQ, wCount);
                 k_exact_extend<<<gridExact, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount, w->arrays.hit, exactTotals);
             }
             for (uint32_t j = 0; j < nB; ++j) {
@@ -1040,7 +1040,7 @@ int wavefront_render_frames(b200pt_ctx* c, const ptl::PushConstants& pc, uint32_
                     }
                     if (c->exactOrder) {
                         cudaStream_t xs = exactAside ? w->exactStream : c->stream;
-                        launch_verify(c, w->gridVerify, w->smCount, xs, w->scene, w->arrays, qb, qCount + j + 1, exactQ, xCount + j + 1, walkQ, wCount + j + 1);
+                        launch_verify(c, w->gridVerify, xs, w->scene, w->arrays, qb, qCount + j + 1, exactQ, xCount + j + 1, walkQ, wCount + j + 1);
                         k_exact_extend<<<gridExact, WF_THREADS, 0, xs>>>(P, w->scene, c->ref, w->arrays, exactQ, xCount + j + 1, w->arrays.hit, exactTotals);
                     }
                     if (exactAside) WCU(cudaEventRecord(w->evX1, w->exactStream));
@@ -1121,7 +1121,7 @@ int wavefront_trace_batch(b200pt_ctx* c, const ptl::PushConstants& pc, const flo
         uint32_t* xCount = qCount + 7 * w->countSlots;
         launch_extend(c, w->gridExtend, P, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, workE, (uint32_t*)w->dExactQ.p, xCount, workCnt);
         wf_mark(c, -1);
-        if (c->exactOrder) launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, (uint32_t*)w->dExactQ.p, xCount,
+        if (c->exactOrder) launch_verify(c, w->gridVerify, c->stream, w->scene, w->arrays, (const uint32_t*)w->dQueue[0].p, qCount, (uint32_t*)w->dExactQ.p, xCount,
                                          (uint32_t*)w->dWalkQ.p, qCount + 9 * w->countSlots);
         k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, w->arrays, (const uint32_t*)w->dExactQ.p, xCount, w->arrays.hit,
                                                                    (unsigned long long*)w->dRayCounters.p + 12);
@@ -1202,12 +1202,9 @@ int wavefront_trace_batch_static(b200pt_ctx* c, const ptl::PushConstants& pc, co
     const int grid = std::min<int>(w->smCount * 8, (int)((m + WF_THREADS - 1) / WF_THREADS));
     WCU(cudaMemsetAsync(header, 0, WF_STATIC_HEADER, c->stream));
     k_load_rays<<<grid, WF_THREADS, 0, c->stream>>>((const float4*)dRays, m, A, queue, qCount);
-    const int countWork = c->countWork;
-    c->countWork = 0;
-    launch_extend(c, w->gridExtend, P, w->scene, A, queue, qCount, workE, exactQ, xCount, nullptr);
-    c->countWork = countWork;
+    launch_extend(c, w->gridExtend, P, w->scene, A, queue, qCount, workE, exactQ, xCount, nullptr);      // no work counters here
     if (c->exactOrder) {
-        launch_verify(c, w->gridVerify, w->smCount, c->stream, w->scene, A, queue, qCount, exactQ, xCount, walkQ, header + 3);
+        launch_verify(c, w->gridVerify, c->stream, w->scene, A, queue, qCount, exactQ, xCount, walkQ, header + 3);
         k_exact_extend<<<w->smCount * 4, WF_THREADS, 0, c->stream>>>(P, w->scene, c->ref, A, exactQ, xCount, A.hit, total);
     }
     k_hit_records<<<grid, WF_THREADS, 0, c->stream>>>(w->scene, A, m, dHits);
