@@ -130,7 +130,9 @@ __global__ void __launch_bounds__(WF_THREADS) k_generate(const __grid_constant__
 // divergent halves of the classic while-while loop each run with as many lanes as possible.
 // Triangle groups met while the warp is visiting nodes are postponed on the lane's stack
 // (trav_node_step). Grid = exactly the resident blocks of the device: no second wave.
+#ifndef PT_CHUNK
 #define PT_CHUNK 128u
+#endif
 #define PT_FETCH_MIN_IDLE 8        /* refill once this many lanes are idle (or all are) */
 
 struct WarpFeeder {                // warp-uniform
